@@ -1,0 +1,255 @@
+"""oracle/bindings.py -- TEST INFRASTRUCTURE ONLY.
+
+ctypes bindings for the two checker libraries:
+
+* ``oracle/_build/liboracle.so``  -- CPU restatement of src/shaders/low_res.frag
+  (oracle_render.cpp)
+* ``oracle/_ref/libref_world.so`` -- the reference's own unmodified CPU sources
+  (world builder, getBlock/putBlock, CPU picking ray), compiled by oracle/Makefile
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.  The product package never does.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "_build", "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libref_world.so")
+
+F_CROSSHAIR = 1
+F_SHADOWS = 2
+
+KIND_SKY, KIND_HIT, KIND_CAMERA_INSIDE, KIND_CROSSHAIR, KIND_HIGHLIGHT, KIND_DEBUG = range(6)
+HF_SHADOWED, HF_REFLECTED, HF_REFRACTED, HF_FACING_SUN = 1, 2, 4, 8
+
+# Byte layout shared with rc_hit (include/rc.h)
+HIT_DTYPE = np.dtype(
+    [
+        ("x", "<i4"), ("y", "<i4"), ("z", "<i4"),
+        ("steps", "<u2"), ("shadow_steps", "<u2"),
+        ("face", "u1"), ("kind", "u1"), ("flags", "u1"), ("ao_occluded", "u1"),
+    ]
+)
+assert HIT_DTYPE.itemsize == 20
+
+
+class OracleWorld(ctypes.Structure):
+    _fields_ = [
+        ("nodes", ctypes.c_void_p), ("n_nodes", ctypes.c_uint64),
+        ("arrays", ctypes.c_void_p), ("n_arrays", ctypes.c_uint64),
+        ("max_depth", ctypes.c_int32), ("_pad", ctypes.c_int32),
+    ]
+
+
+class OracleFrame(ctypes.Structure):
+    _fields_ = [
+        ("origin", ctypes.c_float * 3), ("camera_dir", ctypes.c_float * 3), ("sun_dir", ctypes.c_float * 3),
+        ("mouse_pos", ctypes.c_float * 2), ("proj_plane", ctypes.c_float * 2),
+        ("delta_time", ctypes.c_float), ("ao_strength", ctypes.c_float),
+        ("looking_at", ctypes.c_int32 * 3), ("render_pos_data", ctypes.c_int32),
+        ("width", ctypes.c_uint32), ("height", ctypes.c_uint32),
+        ("max_steps", ctypes.c_uint32), ("shadow_steps", ctypes.c_uint32),
+        ("ao_samples", ctypes.c_uint32), ("ao_steps", ctypes.c_uint32),
+        ("flags", ctypes.c_uint32), ("row_begin", ctypes.c_uint32), ("row_end", ctypes.c_uint32),
+        ("threads", ctypes.c_int32),
+    ]
+
+
+class OracleCounters(ctypes.Structure):
+    _fields_ = [
+        ("node_reads", ctypes.c_uint64 * 3), ("array_reads", ctypes.c_uint64 * 3),
+        ("dda_steps", ctypes.c_uint64 * 3), ("rays", ctypes.c_uint64 * 3),
+        ("kind_pixels", ctypes.c_uint64 * 6),
+    ]
+
+    def as_dict(self):
+        return {
+            "node_reads": list(self.node_reads), "array_reads": list(self.array_reads),
+            "dda_steps": list(self.dda_steps), "rays": list(self.rays),
+            "kind_pixels": list(self.kind_pixels),
+            "algorithmic_bytes": [16 * self.node_reads[i] + 4 * self.array_reads[i] for i in range(3)],
+        }
+
+
+def build(which=("oracle", "ref")):
+    """Runs oracle/Makefile (the ref target is a no-op when /root/reference is absent)."""
+    for target in which:
+        subprocess.run(["make", "-C", HERE, target], check=True, stdout=subprocess.DEVNULL)
+
+
+_oracle = None
+_ref = None
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        if not os.path.exists(ORACLE_SO):
+            build(("oracle",))
+        L = ctypes.CDLL(ORACLE_SO)
+        L.oracle_render.restype = ctypes.c_int
+        L.oracle_render.argtypes = [ctypes.c_void_p] * 6
+        L.oracle_get_block.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.oracle_morton.restype = ctypes.c_uint64
+        L.oracle_morton.argtypes = [ctypes.c_int32] * 4
+        L.oracle_morton_ref10.restype = ctypes.c_uint32
+        L.oracle_morton_ref10.argtypes = [ctypes.c_int32] * 3
+        L.oracle_dda_walk.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_void_p]
+        L.oracle_sinf.restype = ctypes.c_float
+        L.oracle_sinf.argtypes = [ctypes.c_float]
+        L.oracle_expf.restype = ctypes.c_float
+        L.oracle_expf.argtypes = [ctypes.c_float]
+        L.oracle_hemisphere.argtypes = [ctypes.c_uint32, ctypes.c_void_p]
+        L.oracle_set_hemisphere.argtypes = [ctypes.c_uint32, ctypes.c_void_p]
+        _oracle = L
+    return _oracle
+
+
+def ref_lib():
+    """The reference's own code. Raises FileNotFoundError if it was never built here."""
+    global _ref
+    if _ref is None:
+        if not os.path.exists(REF_SO):
+            if os.path.isdir("/root/reference/src"):
+                build(("ref",))
+            else:
+                raise FileNotFoundError(REF_SO)
+        L = ctypes.CDLL(REF_SO)
+        L.refworld_node_block.restype = ctypes.c_void_p
+        L.refworld_array_block.restype = ctypes.c_void_p
+        L.refworld_node_block.argtypes = [ctypes.c_uint32]
+        L.refworld_array_block.argtypes = [ctypes.c_uint32]
+        L.refworld_rgb_to_u64.restype = ctypes.c_uint64
+        L.refworld_noise2.restype = ctypes.c_double
+        L.refworld_noise2.argtypes = [ctypes.c_int64, ctypes.c_double, ctypes.c_double]
+        L.refworld_noise2_grid.argtypes = [ctypes.c_int64, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        L.refworld_get_block.argtypes = [ctypes.c_int] * 3 + [ctypes.c_void_p] * 3
+        L.refworld_put_block.argtypes = [ctypes.c_int] * 3 + [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float, ctypes.c_int]
+        L.refworld_delete_block.argtypes = [ctypes.c_int] * 4
+        L.refworld_pick.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.refworld_pick_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_void_p]
+        L.refworld_copy_nodes.argtypes = [ctypes.c_void_p]
+        L.refworld_copy_arrays.argtypes = [ctypes.c_void_p]
+        L.refworld_defaults.argtypes = [ctypes.c_void_p] * 3
+        L.refworld_upload_record.argtypes = [ctypes.c_uint32, ctypes.c_void_p]
+        L.refworld_upload_src.restype = ctypes.c_void_p
+        L.refworld_upload_src.argtypes = [ctypes.c_uint32]
+        _ref = L
+    return _ref
+
+
+class RefWorld:
+    """The default world exactly as the reference host builds it (src/main.cpp:181-190)."""
+
+    def __init__(self, gen_world=True):
+        L = ref_lib()
+        L.refworld_build(1 if gen_world else 0)
+        self.lib = L
+        self.block_bytes = L.refworld_block_bytes()
+        self.refresh()
+
+    def refresh(self):
+        L = self.lib
+        self.node_bytes_used = L.refworld_node_bytes_used()
+        self.array_bytes_used = L.refworld_array_bytes_used()
+        nb, ab = L.refworld_num_node_blocks(), L.refworld_num_array_blocks()
+        self.nodes = np.zeros(nb * self.block_bytes // 8, dtype=np.uint64)
+        self.arrays = np.zeros(ab * self.block_bytes // 4, dtype=np.uint32)
+        L.refworld_copy_nodes(self.nodes.ctypes.data)
+        L.refworld_copy_arrays(self.arrays.ctypes.data)
+        self.max_depth = L.refworld_max_depth()
+
+    def block_ptrs(self):
+        L = self.lib
+        nodes = [L.refworld_node_block(i) for i in range(L.refworld_num_node_blocks())]
+        arrays = [L.refworld_array_block(i) for i in range(L.refworld_num_array_blocks())]
+        return nodes, arrays
+
+    def get_block(self, x, y, z):
+        c, f, m = ctypes.c_uint64(), ctypes.c_uint32(), ctypes.c_float()
+        self.lib.refworld_get_block(x, y, z, ctypes.byref(c), ctypes.byref(f), ctypes.byref(m))
+        return c.value, f.value, m.value
+
+    def defaults(self):
+        pos, d, s = (ctypes.c_float * 3)(), (ctypes.c_float * 3)(), (ctypes.c_float * 3)()
+        self.lib.refworld_defaults(pos, d, s)
+        return (np.array(pos, dtype=np.float32), np.array(d, dtype=np.float32), np.array(s, dtype=np.float32))
+
+    def pick(self, cam_pos, cam_dir, steps=30):
+        p = np.asarray(cam_pos, dtype=np.float32)
+        d = np.asarray(cam_dir, dtype=np.float32)
+        out = np.zeros(7, dtype=np.int32)
+        self.lib.refworld_pick(p.ctypes.data, d.ctypes.data, steps, out.ctypes.data)
+        return out[0:3].copy(), out[3:6].copy(), int(out[6])
+
+
+def make_world(nodes, arrays, max_depth=6):
+    """OracleWorld over flat pool arrays (kept alive by the caller)."""
+    w = OracleWorld()
+    w.nodes = nodes.ctypes.data
+    w.n_nodes = nodes.size // 2
+    w.arrays = arrays.ctypes.data
+    w.n_arrays = arrays.size // 64
+    w.max_depth = max_depth
+    return w
+
+
+def make_frame(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
+               ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
+               render_pos_data=0, max_steps=300, shadow_steps=75, rows=None, threads=0, proj_plane=None):
+    f = OracleFrame()
+    f.origin[:] = [float(v) for v in origin]
+    f.camera_dir[:] = [float(v) for v in camera_dir]
+    f.sun_dir[:] = [float(v) for v in sun_dir]
+    flags = 0
+    if mouse_pos is not None:
+        f.mouse_pos[:] = [float(v) for v in mouse_pos]
+        flags |= F_CROSSHAIR
+    if shadows:
+        flags |= F_SHADOWS
+    if proj_plane is None:
+        proj_plane = default_proj_plane(width, height)
+    f.proj_plane[:] = [float(v) for v in proj_plane]
+    f.delta_time = delta_time
+    f.ao_strength = ao_strength
+    f.looking_at[:] = list(looking_at)
+    f.render_pos_data = render_pos_data
+    f.width, f.height = width, height
+    f.max_steps, f.shadow_steps = max_steps, shadow_steps
+    f.ao_samples, f.ao_steps = ao_samples, ao_steps
+    f.flags = flags
+    f.row_begin, f.row_end = (0, height) if rows is None else rows
+    f.threads = threads
+    return f
+
+
+def default_proj_plane(width, height):
+    """src/main.cpp:94: evaluated in double on the host, passed as two floats."""
+    import math
+
+    t = math.tan(math.radians(45.0))
+    # glm::tan(glm::radians(45.0)) * ((float)height)/width : double * float / int
+    return (np.float32(t), np.float32(t * float(np.float32(height)) / width))
+
+
+def render(world, frame, want_hits=True, want_rgba8=True, want_f32=False):
+    L = oracle_lib()
+    n = frame.width * frame.height
+    hits = np.zeros(n, dtype=HIT_DTYPE) if want_hits else None
+    rgba8 = np.zeros((frame.height, frame.width, 4), dtype=np.uint8) if want_rgba8 else None
+    f32 = np.zeros((frame.height, frame.width, 4), dtype=np.float32) if want_f32 else None
+    counters = OracleCounters()
+    rc = L.oracle_render(
+        ctypes.addressof(world), ctypes.addressof(frame),
+        hits.ctypes.data if hits is not None else None,
+        rgba8.ctypes.data if rgba8 is not None else None,
+        f32.ctypes.data if f32 is not None else None,
+        ctypes.addressof(counters),
+    )
+    if rc != 0:
+        raise RuntimeError(f"oracle_render failed: {rc}")
+    return {"hits": hits, "rgba8": rgba8, "rgba32f": f32, "counters": counters}
