@@ -1,0 +1,206 @@
+/* include/rc.h -- C-ABI of librc.so, the B200 voxel ray caster.
+ *
+ * Drop-in boundary for the render path of reedthorngag/raytracing_test.  The
+ * reference has no FFI: its host talks to the GPU through OpenGL calls.  Each
+ * entry point below replaces one group of those calls (cited as file:line of
+ * the reference) and carries exactly the information they carried.  The host
+ * (main.cpp, world_gen.cpp, input.cpp, voxel_data/, ray_caster.cpp) is kept
+ * as it is; INTEGRATION.md shows the lines a maintainer changes.
+ *
+ * Conventions
+ *  - plain C: pointers, sizes, PODs; no C++/torch types cross this boundary
+ *  - one process drives one GPU (process-global state, like the reference's GL
+ *    context and globals); not thread-safe, one caller thread
+ *  - every int-returning call returns RC_OK (0) or a negative rc_status; the
+ *    text of the last failure is rc_last_error().  Nothing ever calls exit()
+ *    (the reference does: src/globals.hpp:32-43)
+ *  - there is no CPU fallback: without a usable CUDA device rc_init fails
+ */
+#ifndef RC_H
+#define RC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RC_ABI_VERSION 1
+
+typedef enum rc_status {
+    RC_OK = 0,
+    RC_ERR_NOT_INITIALIZED = -1,
+    RC_ERR_INVALID_ARGUMENT = -2,
+    RC_ERR_CUDA = -3,
+    RC_ERR_MALFORMED_WORLD = -4,
+    RC_ERR_NO_WORLD = -5,
+    RC_ERR_NO_FRAME = -6,
+    RC_ERR_BUFFER_TOO_SMALL = -7,
+    RC_ERR_UNSUPPORTED = -8
+} rc_status;
+
+/* ---- world ------------------------------------------------------------------
+ * The host's two block pools, in the layout the shader binds as SSBOs
+ * (src/shaders/low_res.frag:33-39; src/voxel_data/types.hpp:29-47):
+ *   node pool : 16-byte nodes, index = byte offset >> 4   (binding 3)
+ *   array pool: 64 x u32 child-index arrays, index = byte offset >> 8 (binding 2)
+ * held as lists of 4 MiB malloc blocks (src/voxel_data/voxel_allocator.hpp:12-18).
+ * Exactly what updateSsboData() walks (voxel_allocator.hpp:38-78). */
+typedef struct rc_world_desc {
+    const void* const* node_blocks;   /* nodeBlocks[i].ptr */
+    const void* const* array_blocks;  /* arrayBlocks[i].ptr */
+    uint32_t n_node_blocks;
+    uint32_t n_array_blocks;
+    uint32_t block_bytes;             /* BLOCK_SIZE = 1 << 22 */
+    uint32_t root_index;              /* root.index (0) */
+    uint64_t node_bytes_used;         /* nodeNextAllocIndex */
+    uint64_t array_bytes_used;        /* arrayNextAllocIndex */
+    uint32_t max_depth;               /* maxDepth = 6 (tetrahexa_tree.hpp:6); 7 and 8 are extensions */
+    uint32_t reserved;
+} rc_world_desc;
+
+typedef struct rc_world_info {
+    uint64_t ref_nodes;       /* reachable nodes of the host tree */
+    uint64_t ref_bytes;       /* node_bytes_used + array_bytes_used */
+    uint64_t packed_nodes;    /* 16-byte packed nodes on the device */
+    uint64_t packed_voxels;   /* 4-byte voxel material words on the device */
+    uint64_t packed_materials;
+    uint64_t packed_bytes;    /* total device bytes of the flattened world */
+    uint32_t max_depth;
+    uint32_t null_children;   /* bitmap bits whose child index was 0 */
+    double flatten_ms;
+    double upload_ms;
+} rc_world_info;
+
+/* ---- frame ------------------------------------------------------------------
+ * One field per uniform of low_res.frag:16-27 as set by render()
+ * (src/main.cpp:83-95), plus the shader's compile-time constants as knobs.
+ * originMortonPos (main.cpp:86) is derived inside the library. */
+typedef struct rc_frame_params {
+    float origin[3];         /* trueOrigin     <- cameraPos            main.cpp:83 */
+    float camera_dir[3];     /* cameraDir (normalised by the host)     main.cpp:84,195 */
+    float sun_dir[3];        /* sunDir         <- sun                  main.cpp:88 */
+    float mouse_pos[2];      /* mousePos (crosshair), used with RC_F_CROSSHAIR  main.cpp:85 */
+    float proj_plane[2];     /* projPlaneSize = (tan45, tan45*h/w)     main.cpp:94 */
+    float delta_time;        /* deltaTime      <- glfwGetTime()        main.cpp:90 */
+    float ao_strength;       /* colour *= 1 - ao_strength * occluded/ao_samples */
+    int32_t looking_at[3];   /* lookingAtBlock <- castRayFromCam(30).pos  main.cpp:81,89 */
+    int32_t render_pos_data; /* renderPosData  <- sendDebugFrame       main.cpp:87 */
+    uint32_t width, height;  /* resolution                             main.cpp:93 */
+    uint32_t max_steps;      /* numSteps = 300                         low_res.frag:310 */
+    uint32_t shadow_steps;   /* 75                                     low_res.frag:382 */
+    uint32_t ao_samples;     /* 0 = AO off; 64 for BASELINE configs 3-5 (<= RC_MAX_AO_SAMPLES) */
+    uint32_t ao_steps;       /* 5                                      light_scattering.frag:231 */
+    uint32_t flags;          /* RC_F_* */
+} rc_frame_params;
+
+#define RC_F_CROSSHAIR 0x1u  /* white disc of radius 3 at mouse_pos (low_res.frag:259-262) */
+#define RC_F_SHADOWS   0x2u  /* sun shadow ray (low_res.frag:373-391) */
+#define RC_F_HITS      0x4u  /* also write the per-pixel parity records (rc_read_hits) */
+#define RC_F_RGBA32F   0x8u  /* also keep the unclamped float colour (glReadPixels GL_FLOAT, main.cpp:38) */
+
+#define RC_MAX_AO_SAMPLES 256u
+
+/* Per-pixel parity record (the "hit buffer"): precedent = the shader's debug
+ * outputs pos.round / pos.exact (low_res.frag:335-341). */
+typedef struct rc_hit {
+    int32_t x, y, z;        /* pos.round when the primary loops exit */
+    uint16_t steps;         /* nextIntersectDDA calls of the primary phase */
+    uint16_t shadow_steps;  /* nextIntersectDDA calls of the shadow ray */
+    uint8_t face;           /* lastHit: 0 x, 1 y, 2 z */
+    uint8_t kind;           /* RC_KIND_* */
+    uint8_t flags;          /* RC_HF_* */
+    uint8_t ao_occluded;    /* occluded AO rays of this pixel */
+} rc_hit;
+
+enum {
+    RC_KIND_SKY = 0,            /* low_res.frag:352-355 */
+    RC_KIND_HIT = 1,            /* low_res.frag:357-391 */
+    RC_KIND_CAMERA_INSIDE = 2,  /* low_res.frag:300-306 */
+    RC_KIND_CROSSHAIR = 3,      /* low_res.frag:259-262 */
+    RC_KIND_HIGHLIGHT = 4,      /* low_res.frag:347-350 */
+    RC_KIND_DEBUG = 5           /* low_res.frag:335-341 */
+};
+#define RC_HF_SHADOWED   0x01u
+#define RC_HF_REFLECTED  0x02u
+#define RC_HF_REFRACTED  0x04u
+#define RC_HF_FACING_SUN 0x08u
+#define RC_HF_STEPX_NEG  0x10u
+#define RC_HF_STEPY_NEG  0x20u
+#define RC_HF_STEPZ_NEG  0x40u
+
+typedef enum rc_image_format {
+    RC_RGBA8 = 0,    /* 4 B/pixel, alpha 0, row 0 = bottom (GL), what glfwSwapBuffers shows (main.cpp:216) */
+    RC_RGBA32F = 1   /* 16 B/pixel, needs RC_F_RGBA32F (glReadPixels GL_RGBA/GL_FLOAT, main.cpp:38) */
+} rc_image_format;
+
+typedef struct rc_frame_stats {
+    uint64_t primary_rays;   /* pixels that traced (all but crosshair pixels) */
+    uint64_t shadow_rays;
+    uint64_t ao_rays;
+    uint64_t hit_pixels;     /* RC_KIND_HIT */
+    uint64_t primary_steps;  /* DDA steps, summed (0 unless RC_F_HITS) */
+    uint32_t kernel_launches;/* kernels launched by the last rc_render_frame */
+    uint32_t reserved;
+    float primary_ms;        /* device time of each kernel of the last frame (CUDA events */
+    float ao_ms;             /*   on the library's stream); valid after rc_sync/rc_read_* */
+    float total_ms;
+    float reserved2;
+} rc_frame_stats;
+
+/* ---- lifetime -----------------------------------------------------------------
+ * rc_init replaces createWindow()+setupOpenGl() (src/setup.cpp:55-111,414-426):
+ * selects the CUDA device, creates the stream, loads the constant tables.
+ * rc_shutdown replaces glfwDestroyWindow/glfwTerminate (src/main.cpp:229-230). */
+int rc_init(int device);
+void rc_shutdown(void);
+const char* rc_last_error(void);
+int rc_abi_version(void);
+
+/* Launch on a caller-owned cudaStream_t (e.g. torch's current stream) instead of
+ * the library's own; NULL restores the internal stream. */
+int rc_set_stream(void* cuda_stream);
+
+/* Image-tile sharding for one-process-per-GPU rendering: this
+ * process renders the 32x32 tiles with tile_id % world_size == rank and leaves
+ * the others untouched.  (0,1) = whole frame. */
+int rc_set_shard(uint32_t rank, uint32_t world_size);
+
+/* ---- world upload -------------------------------------------------------------
+ * Replaces initVoxelDataAllocator()+updateSsboData()
+ * (src/voxel_data/voxel_allocator.hpp:38-91; called at src/main.cpp:182,212).
+ * Copies out of the host blocks (the host keeps ownership), flattens the two
+ * pools into the packed device format and uploads it.  Call again after the
+ * host edited blocks (putBlock/deleteBlock set BlockPtr.modified). */
+int rc_upload_world(const rc_world_desc* desc);
+int rc_world_info_get(rc_world_info* out);
+
+/* ---- render -------------------------------------------------------------------
+ * Replaces the glUniform* block + glDrawArrays of render() (src/main.cpp:83-107).
+ * Asynchronous: enqueues the kernels and returns. */
+int rc_render_frame(const rc_frame_params* params);
+
+/* Replaces glfwSwapBuffers / glReadPixels (src/main.cpp:216,38): waits for the
+ * frame and copies it to host memory.  dst_bytes >= width*height*(4|16). */
+int rc_read_image(void* dst, size_t dst_bytes, int format);
+
+/* Parity records of the last frame rendered with RC_F_HITS; n >= width*height. */
+int rc_read_hits(rc_hit* dst, size_t n);
+
+int rc_sync(void);
+int rc_frame_stats_get(rc_frame_stats* out);
+
+/* Device-side views of the last frame for host code that composes frames across
+ * GPUs (NCCL gather over NVLink) without a host round trip. NULL if absent. */
+void* rc_device_image(int format);
+void* rc_device_hits(void);
+
+/* The hemisphere direction table the AO kernel uses: gen_hemisphare_distrib.py:4-12
+ * with num_pts = n, as 3*n floats (x, y, up) in tangent space. */
+int rc_hemisphere_table(uint32_t n, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RC_H */

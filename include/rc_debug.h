@@ -1,0 +1,42 @@
+/* include/rc_debug.h -- test hooks exported by librc.so next to the rc.h ABI.
+ *
+ * Not part of the drop-in boundary: nothing in the reference corresponds to
+ * these.  They let the parity tests reach inside the library (the flattened
+ * world, the device lookup routine, the deterministic sin/exp) through the same
+ * shared object the host links.
+ */
+#ifndef RC_DEBUG_H
+#define RC_DEBUG_H
+
+#include "rc.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Flatten on the host only (no CUDA device needed, rc_init not required): the
+ * flattener half of rc_upload_world.  Result is kept for rc_debug_lookup_host(1,..). */
+int rc_debug_flatten_host(const rc_world_desc* desc, rc_world_info* info);
+
+/* Lookup in a host copy of the packed world. which: 0 = the world uploaded with
+ * rc_upload_world, 1 = the result of rc_debug_flatten_host.
+ * out_word: material word (0 = empty); out_shift: log2 edge of the uniform cell;
+ * out_leaf[4]: the reference Leaf {u64 packedColor, u32 flags, f32 metadata} when solid. */
+int rc_debug_lookup_host(int which, int32_t x, int32_t y, int32_t z, uint32_t* out_word, int32_t* out_shift,
+                         uint32_t* out_leaf);
+int rc_debug_lookup_host_batch(int which, const int32_t* xyz, uint64_t n, uint32_t* out_words, int32_t* out_shifts,
+                               uint32_t* out_leaves);
+
+/* The same lookup executed by the device routine the kernels use. Host pointers. */
+int rc_debug_lookup_device(const int32_t* xyz, uint32_t n, uint32_t* out_words, int32_t* out_shifts);
+
+/* Palette entry of a material word of the uploaded world. */
+int rc_debug_palette(uint32_t word, uint32_t* out_leaf);
+
+/* Device det_sin / det_exp (DESIGN.md "deterministic transcendentals"). Host pointers. */
+int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RC_DEBUG_H */

@@ -94,6 +94,7 @@ def oracle_lib():
         L.oracle_render.restype = ctypes.c_int
         L.oracle_render.argtypes = [ctypes.c_void_p] * 6
         L.oracle_get_block.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+        L.oracle_get_block_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
         L.oracle_morton.restype = ctypes.c_uint64
         L.oracle_morton.argtypes = [ctypes.c_int32] * 4
         L.oracle_morton_ref10.restype = ctypes.c_uint32
@@ -128,6 +129,7 @@ def ref_lib():
         L.refworld_noise2.argtypes = [ctypes.c_int64, ctypes.c_double, ctypes.c_double]
         L.refworld_noise2_grid.argtypes = [ctypes.c_int64, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
         L.refworld_get_block.argtypes = [ctypes.c_int] * 3 + [ctypes.c_void_p] * 3
+        L.refworld_get_block_batch.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
         L.refworld_put_block.argtypes = [ctypes.c_int] * 3 + [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float, ctypes.c_int]
         L.refworld_delete_block.argtypes = [ctypes.c_int] * 4
         L.refworld_pick.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
@@ -173,6 +175,13 @@ class RefWorld:
         c, f, m = ctypes.c_uint64(), ctypes.c_uint32(), ctypes.c_float()
         self.lib.refworld_get_block(x, y, z, ctypes.byref(c), ctypes.byref(f), ctypes.byref(m))
         return c.value, f.value, m.value
+
+    def get_blocks(self, xyz):
+        """Reference getBlock for n voxels -> (n,2) u64 {color, flags | metadata<<32}."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.int32).reshape(-1, 3)
+        out = np.zeros((len(xyz), 2), dtype=np.uint64)
+        self.lib.refworld_get_block_batch(xyz.ctypes.data, len(xyz), out.ctypes.data)
+        return out
 
     def defaults(self):
         pos, d, s = (ctypes.c_float * 3)(), (ctypes.c_float * 3)(), (ctypes.c_float * 3)()
@@ -253,3 +262,11 @@ def render(world, frame, want_hits=True, want_rgba8=True, want_f32=False):
     if rc != 0:
         raise RuntimeError(f"oracle_render failed: {rc}")
     return {"hits": hits, "rgba8": rgba8, "rgba32f": f32, "counters": counters}
+
+
+def get_blocks(world, xyz):
+    """Oracle getBlock (shader semantics) for n voxels -> (n,2) u64 {block.x, block.y}."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.int32).reshape(-1, 3)
+    out = np.zeros((len(xyz), 2), dtype=np.uint64)
+    oracle_lib().oracle_get_block_batch(ctypes.addressof(world), xyz.ctypes.data, len(xyz), out.ctypes.data)
+    return out

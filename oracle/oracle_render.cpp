@@ -685,6 +685,10 @@ void oracle_get_block(const OracleWorld* world, int32_t x, int32_t y, int32_t z,
     out[1] = P.blockY;
 }
 
+void oracle_get_block_batch(const OracleWorld* world, const int32_t* xyz, uint64_t n, uint64_t* out) {
+    for (uint64_t i = 0; i < n; i++) oracle_get_block(world, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], out + 2 * i);
+}
+
 uint64_t oracle_morton(int32_t x, int32_t y, int32_t z, int32_t max_depth) {
     int groups = max_depth - 1;
     return spreadAxis(x, groups) | (spreadAxis(y, groups) << 2) | (spreadAxis(z, groups) << 4);

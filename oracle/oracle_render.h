@@ -104,6 +104,8 @@ int oracle_render(const OracleWorld* world, const OracleFrame* frame, OracleHit*
 /* getBlock of the shader (stateless form: fresh stack per call). out = {block.x, block.y}. */
 void oracle_get_block(const OracleWorld* world, int32_t x, int32_t y, int32_t z, uint64_t* out);
 
+void oracle_get_block_batch(const OracleWorld* world, const int32_t* xyz, uint64_t n, uint64_t* out);
+
 /* getMortonPos (src/main.cpp:45-66) generalised to max_depth-1 two-bit groups per axis. */
 uint64_t oracle_morton(int32_t x, int32_t y, int32_t z, int32_t max_depth);
 

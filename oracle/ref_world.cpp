@@ -131,6 +131,17 @@ void refworld_get_block(int x, int y, int z, uint64_t* color, uint32_t* flags, f
     *metadata = b.metadata;
 }
 
+// Batch getBlock: xyz = 3*n ints, out = 2*n u64 {color, flags | metadata bits << 32}.
+void refworld_get_block_batch(const int* xyz, uint64_t n, uint64_t* out) {
+    for (uint64_t i = 0; i < n; i++) {
+        Block b = getBlock(Pos{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]});
+        uint32_t mbits;
+        memcpy(&mbits, &b.metadata, 4);
+        out[2 * i] = b.color;
+        out[2 * i + 1] = (uint64_t)b.flags | ((uint64_t)mbits << 32);
+    }
+}
+
 void refworld_put_block(int x, int y, int z, uint32_t flags, uint64_t color, float metadata, int level) {
     StdoutMute mute;  // deleteChildren prints unconditionally (tetrahexa_tree.cpp:160)
     putBlock(Pos{x, y, z}, Block{flags, color, metadata}, level);

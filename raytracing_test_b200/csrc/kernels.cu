@@ -1,0 +1,806 @@
+// kernels.cu -- hand-written sm_100a traversal kernels of the voxel ray caster.
+//
+// What the reference does per pixel (src/shaders/low_res.frag:256-393): a 3-D DDA
+// that advances ONE voxel per step (nextIntersectDDA, :446-491) and asks the tree
+// for the new voxel after EVERY step (getBlock, :493-532: a 16-byte node read per
+// level still shared with the previous voxel + a 4-byte child-index read per level
+// descended).  Hit voxel, face and step count depend on the exact sequence of fp32
+// additions `deltaPos[a] += absDelta[a]`, so that arithmetic is kept as is, in
+// registers, with explicit round-to-nearest intrinsics (no FMA contraction).
+//
+// What is redesigned is the memory side:
+//   * the world is the packed breadth-first form of packed_world.h: one 128-bit
+//     __ldg per level, popcount child addressing, 4^3 bricks at the bottom;
+//   * the tree is consulted only when the ray LEAVES the uniform cell it is in.
+//     A lookup that answers "empty" also answers "empty for the whole 4^k cell",
+//     so the kernel counts down the voxels left to each face of that cell and
+//     steps in registers until one counter hits zero (the reference re-reads
+//     nodes[stack[depth]] on every step: ~178 node reads per primary ray in the
+//     default scene, of which only ~7.5 are real descents);
+//   * a re-descent starts from the deepest cached node that still contains the
+//     voxel (the reference's stack, collapsed to one cached node in registers);
+//   * pos.exact (needed only to seed the shadow/AO ray and for refraction) is
+//     carried with the same per-step arithmetic as the shader.
+//
+// Rays are issued in 8x4-pixel warp tiles (coherent neighbours share cells, so
+// their lookups hit the same L1 lines).
+#include "kernels.h"
+
+#include "packed_world.h"
+
+namespace rc {
+
+// ---------------------------------------------------------------------------
+// exact fp32 helpers: one IEEE round-to-nearest operation each, never contracted
+// ---------------------------------------------------------------------------
+#define FADD(a, b) __fadd_rn((a), (b))
+#define FSUB(a, b) __fsub_rn((a), (b))
+#define FMUL(a, b) __fmul_rn((a), (b))
+#define FDIV(a, b) __fdiv_rn((a), (b))
+#define FSQRT(a) __fsqrt_rn((a))
+
+__constant__ float c_hemi[3 * RC_MAX_AO_SAMPLES];      // (x, y, up) per sample
+__constant__ float c_hemi_inv[3 * RC_MAX_AO_SAMPLES];  // (1/x, 1/y, 1/up)
+
+struct F3 {
+    float x, y, z;
+};
+struct I3v {
+    int x, y, z;
+};
+
+__device__ __forceinline__ float sel3(int a, float x, float y, float z) { return a == 0 ? x : (a == 1 ? y : z); }
+__device__ __forceinline__ int sel3i(int a, int x, int y, int z) { return a == 0 ? x : (a == 1 ? y : z); }
+
+__device__ __forceinline__ float glsl_min(float a, float b) { return b < a ? b : a; }
+__device__ __forceinline__ float glsl_max(float a, float b) { return a < b ? b : a; }
+__device__ __forceinline__ float glsl_clamp(float x, float lo, float hi) { return glsl_min(glsl_max(x, lo), hi); }
+
+__device__ __forceinline__ float dot3(F3 a, F3 b) { return FADD(FADD(FMUL(a.x, b.x), FMUL(a.y, b.y)), FMUL(a.z, b.z)); }
+__device__ __forceinline__ F3 cross3(F3 a, F3 b) {
+    F3 r;
+    r.x = FSUB(FMUL(a.y, b.z), FMUL(b.y, a.z));
+    r.y = FSUB(FMUL(a.z, b.x), FMUL(b.z, a.x));
+    r.z = FSUB(FMUL(a.x, b.y), FMUL(b.x, a.y));
+    return r;
+}
+__device__ __forceinline__ F3 scale3(F3 a, float s) { return F3{FMUL(a.x, s), FMUL(a.y, s), FMUL(a.z, s)}; }
+__device__ __forceinline__ F3 add3(F3 a, F3 b) { return F3{FADD(a.x, b.x), FADD(a.y, b.y), FADD(a.z, b.z)}; }
+__device__ __forceinline__ F3 normalize3(F3 v) { return scale3(v, FDIV(1.0f, FSQRT(dot3(v, v)))); }
+
+// Deterministic sin / exp: the same sequence of fp32 operations as the oracle's
+// detSin / detExp (DESIGN.md "deterministic transcendentals").
+__device__ __forceinline__ float det_sin(float x) {
+    if (!(fabsf(x) <= 1.0e6f)) return 0.0f;
+    float k = floorf(FADD(FMUL(x, 0.15915494309189535f), 0.5f));
+    float r = FSUB(x, FMUL(k, 6.28125f));
+    r = FSUB(r, FMUL(k, 1.9350051879882812e-3f));
+    r = FSUB(r, FMUL(k, 3.0199160691085e-7f));
+    const float pi = 3.14159265358979f;
+    const float halfPi = 1.57079632679490f;
+    if (r > halfPi) r = FSUB(pi, r);
+    if (r < -halfPi) r = FSUB(-pi, r);
+    float s = FMUL(r, r);
+    float p = -2.5052108385441720e-08f;
+    p = FADD(FMUL(p, s), 2.7557319223985893e-06f);
+    p = FADD(FMUL(p, s), -1.9841269841269841e-04f);
+    p = FADD(FMUL(p, s), 8.3333333333333332e-03f);
+    p = FADD(FMUL(p, s), -1.6666666666666666e-01f);
+    return FADD(r, FMUL(FMUL(r, s), p));
+}
+
+__device__ __forceinline__ float det_exp(float x) {
+    if (x != x) return x;
+    if (x > 88.0f) x = 88.0f;
+    if (x < -87.0f) x = -87.0f;
+    float k = floorf(FADD(FMUL(x, 1.44269504088896341f), 0.5f));
+    float r = FSUB(x, FMUL(k, 0.693359375f));
+    r = FSUB(r, FMUL(k, -2.12194440e-4f));
+    float p = 1.9875691500e-4f;
+    p = FADD(FMUL(p, r), 1.3981999507e-3f);
+    p = FADD(FMUL(p, r), 8.3334519073e-3f);
+    p = FADD(FMUL(p, r), 4.1665795894e-2f);
+    p = FADD(FMUL(p, r), 1.6666665459e-1f);
+    p = FADD(FMUL(p, r), 5.0000001201e-1f);
+    float e = FADD(FADD(FMUL(p, FMUL(r, r)), r), 1.0f);
+    int ki = (int)k;
+    return FMUL(e, __int_as_float((ki + 127) << 23));
+}
+
+// ---------------------------------------------------------------------------
+// Tree cursor: one cached PackedNode (never a PK_LEAF) + the last voxel looked up.
+// ---------------------------------------------------------------------------
+struct Cursor {
+    unsigned long long mask;
+    uint32_t base;
+    uint32_t kind;
+    int shift;       // cell shift of the cached node's children
+    int lx, ly, lz;  // wrapped coordinates of a voxel inside the cached node
+};
+
+__device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c) {
+    uint4 n = __ldg(&W.nodes[0]);
+    c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+    c.base = n.z;
+    c.kind = n.w;
+    c.shift = W.root_shift;
+    c.lx = c.ly = c.lz = 0;
+}
+
+// Material word of voxel (x,y,z) (0 = empty) and the shift of the uniform cell it
+// lies in. Equivalent of getBlock (low_res.frag:493-532) on the packed form.
+__device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int x, int y, int z, int& cellShift) {
+    const int wx = x & (int)W.wrap, wy = y & (int)W.wrap, wz = z & (int)W.wrap;
+    if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
+        uint4 n = __ldg(&W.nodes[0]);
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift = W.root_shift;
+    }
+    c.lx = wx;
+    c.ly = wy;
+    c.lz = wz;
+    for (;;) {
+        const int idx = (((wz >> c.shift) & 3) << 4) | (((wy >> c.shift) & 3) << 2) | ((wx >> c.shift) & 3);
+        if (!((c.mask >> idx) & 1ull)) {
+            cellShift = c.shift;
+            return 0u;
+        }
+        const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
+        if (c.kind == PK_BRICK) {
+            cellShift = 0;
+            return __ldg(&W.voxels[c.base + rank]);
+        }
+        const uint4 n = __ldg(&W.nodes[c.base + rank]);
+        if (n.w == PK_LEAF) {
+            cellShift = c.shift;
+            return n.z;
+        }
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift -= 2;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Ray + position state (the shader's `ray` and `pos` globals)
+// ---------------------------------------------------------------------------
+struct Ray {
+    float dx, dy, dz;     // ray.dir
+    int sx, sy, sz;       // ray.step
+    float adx, ady, adz;  // ray.absDelta
+    float ddx, ddy, ddz;  // ray.delta
+    // ratios columns (low_res.frag:75-91): ratios[a] = dir / dir[a], diagonal = 1
+    float r0y, r0z, r1x, r1z, r2x, r2y;
+};
+
+struct Pos {
+    int x, y, z;       // pos.round
+    float ex, ey, ez;  // pos.exact
+    float tx, ty, tz;  // pos.deltaPos
+};
+
+// low_res.frag:61-97
+__device__ __forceinline__ void build_ray(Ray& r, float dx, float dy, float dz, bool withRatios) {
+    r.dx = dx;
+    r.dy = dy;
+    r.dz = dz;
+    r.sx = dx < 0.0f ? -1 : 1;
+    r.sy = dy < 0.0f ? -1 : 1;
+    r.sz = dz < 0.0f ? -1 : 1;
+    if (withRatios) {
+        r.r0y = FDIV(dy, dx);
+        r.r0z = FDIV(dz, dx);
+        r.r1x = FDIV(dx, dy);
+        r.r1z = FDIV(dz, dy);
+        r.r2x = FDIV(dx, dz);
+        r.r2y = FDIV(dy, dz);
+    }
+    r.ddx = FDIV(1.0f, dx);
+    r.ddy = FDIV(1.0f, dy);
+    r.ddz = FDIV(1.0f, dz);
+    r.adx = fabsf(r.ddx);
+    r.ady = fabsf(r.ddy);
+    r.adz = fabsf(r.ddz);
+}
+
+// pos.deltaPos = ray.absDelta - (pos.exact - pos.round) * ray.delta   (low_res.frag:296,379)
+__device__ __forceinline__ void init_delta_pos(const Ray& r, Pos& p) {
+    p.tx = FSUB(r.adx, FMUL(FSUB(p.ex, (float)p.x), r.ddx));
+    p.ty = FSUB(r.ady, FMUL(FSUB(p.ey, (float)p.y), r.ddy));
+    p.tz = FSUB(r.adz, FMUL(FSUB(p.ez, (float)p.z), r.ddz));
+}
+
+// Steps left before the ray leaves the aligned 2^shift cell around (x,y,z), per axis.
+struct CellCount {
+    int nx, ny, nz;
+};
+__device__ __forceinline__ void count_cell(CellCount& n, const Ray& r, const Pos& p, int shift) {
+    const int m = (1 << shift) - 1;
+    const int fx = p.x & m, fy = p.y & m, fz = p.z & m;
+    n.nx = r.sx > 0 ? (m + 1 - fx) : (fx + 1);
+    n.ny = r.sy > 0 ? (m + 1 - fy) : (fy + 1);
+    n.nz = r.sz > 0 ? (m + 1 - fz) : (fz + 1);
+}
+
+// nextIntersectDDA (low_res.frag:446-491). Returns the axis stepped.
+// TRACK_EXACT: also advance pos.exact (only the primary ray needs it).
+template <bool TRACK_EXACT>
+__device__ __forceinline__ int dda_step(const Ray& r, Pos& p, CellCount& n, bool& left) {
+    int a;
+    if (p.tx < p.ty && p.tx < p.tz) {
+        if (TRACK_EXACT) {
+            const float dst = FSUB((float)r.sx, FSUB(p.ex, (float)p.x));
+            p.ex = FADD(p.ex, dst);
+            p.ey = FADD(p.ey, FMUL(dst, r.r0y));
+            p.ez = FADD(p.ez, FMUL(dst, r.r0z));
+        }
+        p.x += r.sx;
+        p.tx = FADD(p.tx, r.adx);
+        left = (--n.nx == 0);
+        a = 0;
+    } else if (p.ty < p.tz) {
+        if (TRACK_EXACT) {
+            const float dst = FSUB((float)r.sy, FSUB(p.ey, (float)p.y));
+            p.ex = FADD(p.ex, FMUL(dst, r.r1x));
+            p.ey = FADD(p.ey, dst);
+            p.ez = FADD(p.ez, FMUL(dst, r.r1z));
+        }
+        p.y += r.sy;
+        p.ty = FADD(p.ty, r.ady);
+        left = (--n.ny == 0);
+        a = 1;
+    } else {
+        if (TRACK_EXACT) {
+            const float dst = FSUB((float)r.sz, FSUB(p.ez, (float)p.z));
+            p.ex = FADD(p.ex, FMUL(dst, r.r2x));
+            p.ey = FADD(p.ey, FMUL(dst, r.r2y));
+            p.ez = FADD(p.ez, dst);
+        }
+        p.z += r.sz;
+        p.tz = FADD(p.tz, r.adz);
+        left = (--n.nz == 0);
+        a = 2;
+    }
+    return a;
+}
+
+// After a lookup: refresh the countdown. A solid voxel forces a lookup on the next step.
+__device__ __forceinline__ void after_lookup(CellCount& n, const Ray& r, const Pos& p, uint32_t word, int cellShift) {
+    if (word == 0u) {
+        count_cell(n, r, p, cellShift);
+    } else {
+        n.nx = n.ny = n.nz = 1;
+    }
+}
+
+__device__ __forceinline__ uint32_t word_flags(uint32_t word) { return word >> MATERIAL_FLAG_SHIFT; }
+
+// low_res.frag:137-147
+__device__ __forceinline__ F3 decode_color(unsigned long long color) {
+    const float s = 1.0f / 2097152.0f;
+    F3 c;
+    c.x = FMUL((float)(uint32_t)(color >> 42), s);
+    c.y = FMUL((float)(uint32_t)((color >> 21) & 0x1FFFFFull), s);
+    c.z = FMUL((float)(uint32_t)(color & 0x1FFFFFull), s);
+    return c;
+}
+
+__device__ __forceinline__ unsigned char to_unorm8(float c) {
+    const float cl = c > 0.0f ? (c < 1.0f ? c : 1.0f) : 0.0f;
+    return (unsigned char)floorf(FADD(FMUL(cl, 255.0f), 0.5f));
+}
+
+// low_res.frag:153-155
+__device__ __forceinline__ float sigmoid(float x, float scale, float steep) {
+    return FMUL(FDIV(1.0f, FADD(1.0f, det_exp(FMUL(-x, steep)))), scale);
+}
+
+// low_res.frag:157-168 (dirY is ray.dir.y, which the function scales in place)
+__device__ __forceinline__ F3 gen_sky(float dirX, float dirY, float dirZ, F3 sun) {
+    if (dirY < 0.0f) dirY = FMUL(dirY, 1.4f);
+    const float haze = FADD(FMUL(FSUB(0.1f, fabsf(glsl_clamp(dirY, -.3f, .3f))), 0.8f), 0.1f);
+    const float modifier = glsl_clamp(sigmoid(FSUB(1.0f, FMUL(haze, 2.0f)), 1.0f, 2.0f), 0.0f, 1.0f);
+    const F3 d = F3{FSUB(dirX, sun.x), FSUB(dirY, sun.y), FSUB(dirZ, sun.z)};
+    const float b = FMUL(FSQRT(dot3(d, d)), 50.0f);
+    const float s = sigmoid(FSUB(1.5f, b), 1.0f, 1.6f);
+    const float h3 = FMUL(glsl_clamp(haze, 0.0f, 1.0f), 3.0f);
+    F3 out;
+    out.x = FADD(FMUL(FADD(0.2f, h3), modifier), FMUL(1.0f, s));
+    out.y = FADD(FMUL(FADD(0.4f, h3), modifier), FMUL(1.0f, s));
+    out.z = FADD(FMUL(FADD(1.0f, h3), modifier), FMUL(0.0f, s));
+    return out;
+}
+
+struct PixelResult {
+    F3 color;
+    rc_hit hit;
+    bool traced;
+    bool shadowRay;
+    bool aoSeed;
+    float sx_, sy_, sz_;  // un-biased exact at the hit (AO seed)
+};
+
+// One pixel of low_res.frag main() (:256-393).
+__device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uint32_t py, PixelResult& out) {
+    const rc_frame_params& P = A.p;
+    const DeviceWorld& W = A.world;
+    out.color = F3{0.0f, 0.0f, 0.0f};
+    out.hit.x = out.hit.y = out.hit.z = 0;
+    out.hit.steps = out.hit.shadow_steps = 0;
+    out.hit.face = out.hit.kind = out.hit.flags = out.hit.ao_occluded = 0;
+    out.traced = false;
+    out.shadowRay = false;
+    out.aoSeed = false;
+
+    const float fragX = FADD((float)px, 0.5f), fragY = FADD((float)py, 0.5f);
+
+    // :259-262
+    if ((P.flags & RC_F_CROSSHAIR) && P.render_pos_data == 0) {
+        const float mx = FSUB(fragX, P.mouse_pos[0]), my = FSUB(fragY, P.mouse_pos[1]);
+        if (FSQRT(FADD(FMUL(mx, mx), FMUL(my, my))) <= 3.0f) {
+            out.color = F3{1.0f, 1.0f, 1.0f};
+            out.hit.kind = RC_KIND_CROSSHAIR;
+            return;
+        }
+    }
+    out.traced = true;
+
+    // :264-265
+    const float fcx = FMUL(fragX, FDIV(1.0f, (float)P.width));
+    const float fcy = FMUL(fragY, FDIV(1.0f, (float)P.height));
+
+    const F3 origin = F3{P.origin[0], P.origin[1], P.origin[2]};
+    const F3 camDir = F3{P.camera_dir[0], P.camera_dir[1], P.camera_dir[2]};
+    const F3 sun = F3{P.sun_dir[0], P.sun_dir[1], P.sun_dir[2]};
+
+    // :279-285
+    const F3 left = cross3(camDir, F3{0.0f, 1.0f, 0.0f});
+    const F3 t1 = scale3(left, -FMUL(P.proj_plane[0], FSUB(fcx, 0.5f)));
+    const F3 t2 = scale3(scale3(cross3(camDir, left), FADD(-fcy, 0.5f)), P.proj_plane[1]);
+    const F3 dir = normalize3(add3(add3(camDir, t1), t2));
+
+    // :275,288-296
+    Ray ray;
+    build_ray(ray, dir.x, dir.y, dir.z, true);
+    Pos pos;
+    pos.x = (int)floorf(origin.x);
+    pos.y = (int)floorf(origin.y);
+    pos.z = (int)floorf(origin.z);
+    pos.ex = ray.sx < 0 ? FSUB(origin.x, 1.0f) : origin.x;
+    pos.ey = ray.sy < 0 ? FSUB(origin.y, 1.0f) : origin.y;
+    pos.ez = ray.sz < 0 ? FSUB(origin.z, 1.0f) : origin.z;
+    init_delta_pos(ray, pos);
+
+    Cursor cur;
+    cursor_reset(W, cur);
+    CellCount cnt;
+    int cellShift;
+    int face = 0;
+    F3 colorMod = F3{1.0f, 1.0f, 1.0f};
+    bool reflected = false;
+    float refrIndex = 1.0f;
+
+    // :299-307
+    uint32_t word = lookup(W, cur, pos.x, pos.y, pos.z, cellShift);
+    if (word != 0u) {
+        if (word_flags(word) & 0x4u) {
+            refrIndex = 1.1f;
+        } else {
+            const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
+            out.color = decode_color((unsigned long long)pe.x | ((unsigned long long)pe.y << 32));
+            out.hit.kind = RC_KIND_CAMERA_INSIDE;
+            out.hit.x = pos.x;
+            out.hit.y = pos.y;
+            out.hit.z = pos.z;
+            return;
+        }
+    }
+    after_lookup(cnt, ray, pos, word, cellShift);
+
+    // :309-315  loop A
+    uint32_t i = 0;
+    uint32_t steps = 0;
+    const uint32_t numSteps = P.max_steps;
+    while (word == 0u && i++ < numSteps) {
+        bool leftCell;
+        face = dda_step<true>(ray, pos, cnt, leftCell);
+        steps++;
+        if (leftCell) {
+            word = lookup(W, cur, pos.x, pos.y, pos.z, cellShift);
+            after_lookup(cnt, ray, pos, word, cellShift);
+        }
+    }
+    // :317-333  loop B
+    while (i++ < numSteps) {
+        if (word != 0u) {
+            const uint32_t fl = word_flags(word);
+            if ((fl & 0x7u) == 0x3u) {
+                // reflectRay :178-194
+                if (face == 0) {
+                    pos.tx = FSUB(pos.tx, ray.adx);
+                    ray.sx = -ray.sx;
+                    ray.dx = -ray.dx;
+                } else if (face == 1) {
+                    pos.ty = FSUB(pos.ty, ray.ady);
+                    ray.sy = -ray.sy;
+                    ray.dy = -ray.dy;
+                } else {
+                    pos.tz = FSUB(pos.tz, ray.adz);
+                    ray.sz = -ray.sz;
+                    ray.dz = -ray.dz;
+                }
+                colorMod = scale3(colorMod, 0.94f);
+                reflected = true;
+            } else if ((fl & 0x7u) == 0x5u) {
+                // refractRay :212-240
+                const bool liquid = (fl & 0x10u) != 0u;
+                if (liquid) {
+                    colorMod.x = FMUL(colorMod.x, 0.94f);
+                    colorMod.y = FMUL(colorMod.y, 0.97f);
+                    colorMod.z = FMUL(colorMod.z, 1.0f);
+                } else {
+                    colorMod = scale3(colorMod, 0.95f);
+                }
+                if (refrIndex != 1.1f) {
+                    if (face != 0 && ray.sx < 0) pos.ex = FADD(pos.ex, 1.0f);
+                    if (face != 1 && ray.sy < 0) pos.ey = FADD(pos.ey, 1.0f);
+                    if (face != 2 && ray.sz < 0) pos.ez = FADD(pos.ez, 1.0f);
+                    F3 nrm = F3{0.0f, 0.0f, 0.0f};
+                    if (face == 0) nrm.x = (float)ray.sx;
+                    else if (face == 1) nrm.y = (float)ray.sy;
+                    else nrm.z = (float)ray.sz;
+                    if (liquid) {
+                        const float arg = FMUL(FSUB(FADD(P.delta_time, FMUL(pos.ex, 0.2f)), FMUL(pos.ez, 0.1f)), 10.0f);
+                        nrm.x = FADD(nrm.x, FMUL(det_sin(arg), 0.2f));
+                        nrm = normalize3(nrm);
+                    }
+                    // refractRay(vec3,vec3,float,float) :198-210
+                    const F3 rd = F3{ray.dx, ray.dy, ray.dz};
+                    const float rr = FDIV(refrIndex, 1.1f);
+                    float c1 = dot3(nrm, rd);
+                    if (c1 < 0.0f) {
+                        nrm = F3{-nrm.x, -nrm.y, -nrm.z};
+                        c1 = dot3(nrm, rd);
+                    }
+                    const float c2 = FSQRT(FSUB(1.0f, FMUL(FMUL(rr, rr), FSUB(1.0f, FMUL(c1, c1)))));
+                    const float k2 = FSUB(FMUL(rr, c1), c2);
+                    const F3 nd = add3(scale3(rd, rr), scale3(nrm, k2));
+                    build_ray(ray, nd.x, nd.y, nd.z, true);
+                    pos.ex = FADD(pos.ex, ray.sx < 0 ? -1.0f : 0.0f);
+                    pos.ey = FADD(pos.ey, ray.sy < 0 ? -1.0f : 0.0f);
+                    pos.ez = FADD(pos.ez, ray.sz < 0 ? -1.0f : 0.0f);
+                    init_delta_pos(ray, pos);
+                    refrIndex = 1.1f;
+                }
+            } else {
+                break;
+            }
+            cnt.nx = cnt.ny = cnt.nz = 1;  // step signs may have changed: re-derive after the next lookup
+        }
+        bool leftCell;
+        face = dda_step<true>(ray, pos, cnt, leftCell);
+        steps++;
+        if (leftCell) {
+            word = lookup(W, cur, pos.x, pos.y, pos.z, cellShift);
+            after_lookup(cnt, ray, pos, word, cellShift);
+        }
+    }
+
+    out.hit.x = pos.x;
+    out.hit.y = pos.y;
+    out.hit.z = pos.z;
+    out.hit.steps = (uint16_t)steps;
+    out.hit.face = (uint8_t)face;
+    out.hit.flags = (uint8_t)((reflected ? RC_HF_REFLECTED : 0u) | (refrIndex != 1.0f ? RC_HF_REFRACTED : 0u) |
+                              (ray.sx < 0 ? RC_HF_STEPX_NEG : 0u) | (ray.sy < 0 ? RC_HF_STEPY_NEG : 0u) |
+                              (ray.sz < 0 ? RC_HF_STEPZ_NEG : 0u));
+
+    // :335-341
+    if (P.render_pos_data == 1) {
+        out.color = F3{pos.ex, pos.ey, pos.ez};
+        out.hit.kind = RC_KIND_DEBUG;
+        return;
+    } else if (P.render_pos_data == 2) {
+        out.color = F3{(float)pos.x, (float)pos.y, (float)pos.z};
+        out.hit.kind = RC_KIND_DEBUG;
+        return;
+    }
+
+    // :343-345
+    if (face != 0 && ray.sx < 0) pos.ex = FADD(pos.ex, 1.0f);
+    if (face != 1 && ray.sy < 0) pos.ey = FADD(pos.ey, 1.0f);
+    if (face != 2 && ray.sz < 0) pos.ez = FADD(pos.ez, 1.0f);
+
+    unsigned long long packedColor = ~0ull;
+    if (word != 0u) {
+        const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
+        packedColor = (unsigned long long)pe.x | ((unsigned long long)pe.y << 32);
+    }
+
+    // :347-350
+    if (P.looking_at[0] == pos.x && P.looking_at[1] == pos.y && P.looking_at[2] == pos.z) {
+        const F3 c = decode_color(packedColor);
+        out.color = F3{FADD(FMUL(c.x, 2.0f), 0.3f), FADD(FMUL(c.y, 2.0f), 0.3f), FADD(FMUL(c.z, 2.0f), 0.3f)};
+        out.hit.kind = RC_KIND_HIGHLIGHT;
+        return;
+    }
+
+    // :352-355
+    if (word == 0u) {
+        const F3 sky = gen_sky(ray.dx, ray.dy, ray.dz, sun);
+        out.color = F3{FMUL(sky.x, colorMod.x), FMUL(sky.y, colorMod.y), FMUL(sky.z, colorMod.z)};
+        out.hit.kind = RC_KIND_SKY;
+        return;
+    }
+
+    // :357-371
+    out.hit.kind = RC_KIND_HIT;
+    const F3 color = decode_color(packedColor);
+    const float sunA = sel3(face, sun.x, sun.y, sun.z);
+    const int stepA = sel3i(face, ray.sx, ray.sy, ray.sz);
+    const float facingTerm = FMUL(sunA, (float)(-stepA));
+    const bool facing = facingTerm > 0.0f;
+    {
+        const float mod = facing ? 0.15f : 0.0f;
+        const float intensity = glsl_min(FADD(FADD(glsl_max(0.0f, facingTerm), 0.4f), mod), 1.0f);
+        out.color = F3{FMUL(FMUL(color.x, intensity), colorMod.x), FMUL(FMUL(color.y, intensity), colorMod.y),
+                       FMUL(FMUL(color.z, intensity), colorMod.z)};
+    }
+    const F3 dim = F3{FMUL(FMUL(color.x, 0.3f), colorMod.x), FMUL(FMUL(color.y, 0.3f), colorMod.y),
+                      FMUL(FMUL(color.z, 0.3f), colorMod.z)};
+    out.aoSeed = P.ao_samples > 0;
+    out.sx_ = pos.ex;
+    out.sy_ = pos.ey;
+    out.sz_ = pos.ez;
+    // normal sign for AO = -step[face] of the primary ray
+    out.hit.ao_occluded = 0;
+
+    bool done = reflected;
+    if (!done && !facing) {
+        out.color = dim;
+        done = true;
+    }
+    if (!done) out.hit.flags |= RC_HF_FACING_SUN;
+
+    // :373-391 shadow ray
+    if (!done && (P.flags & RC_F_SHADOWS)) {
+        out.shadowRay = true;
+        Ray sr;
+        build_ray(sr, sun.x, sun.y, sun.z, false);
+        Pos sp;
+        sp.x = pos.x;
+        sp.y = pos.y;
+        sp.z = pos.z;
+        sp.ex = sr.sx < 0 ? FSUB(pos.ex, 1.0f) : pos.ex;
+        sp.ey = sr.sy < 0 ? FSUB(pos.ey, 1.0f) : pos.ey;
+        sp.ez = sr.sz < 0 ? FSUB(pos.ez, 1.0f) : pos.ez;
+        init_delta_pos(sr, sp);
+        if (face == 0) sp.tx = FSUB(sp.tx, sr.adx);
+        else if (face == 1) sp.ty = FSUB(sp.ty, sr.ady);
+        else sp.tz = FSUB(sp.tz, sr.adz);
+        uint32_t k = P.shadow_steps;
+        uint32_t sw = 0u;       // block = (-1,-1): "empty"
+        uint32_t ssteps = 0;
+        CellCount sc;
+        sc.nx = sc.ny = sc.nz = 1;
+        while ((sw == 0u || (word_flags(sw) & 0x10u)) && k-- != 0u) {
+            bool leftCell;
+            dda_step<false>(sr, sp, sc, leftCell);
+            ssteps++;
+            if (leftCell) {
+                sw = lookup(W, cur, sp.x, sp.y, sp.z, cellShift);
+                after_lookup(sc, sr, sp, sw, cellShift);
+            }
+        }
+        out.hit.shadow_steps = (uint16_t)ssteps;
+        if (sw != 0u) {
+            out.color = dim;
+            out.hit.flags |= RC_HF_SHADOWED;
+        }
+    }
+}
+
+// Pixel (px,py) of the frame -> index into this rank's compact buffers, or -1 if
+// the row belongs to another rank.
+__device__ __forceinline__ uint32_t local_index(const FrameArgs& A, uint32_t px, uint32_t localRow) {
+    return localRow * A.p.width + px;
+}
+
+__device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, F3 c) {
+    A.rgba8[idx] = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+    if (A.rgba32f) A.rgba32f[idx] = make_float4(c.x, c.y, c.z, 0.0f);
+}
+
+// grid.x = ceil(width/16), grid.y = local_rows/8 ; block = 128 threads = 4 warps,
+// each warp an 8x4 pixel tile, the block a 16x8 tile.
+__global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ FrameArgs A) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t localRow = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    // local band -> global row
+    const uint32_t band = (localRow / BAND_ROWS) * A.world_size + A.rank;
+    const uint32_t py = band * BAND_ROWS + (localRow % BAND_ROWS);
+    const bool active = px < A.p.width && py < A.p.height && localRow < A.local_rows;
+
+    PixelResult R;
+    R.traced = false;
+    R.shadowRay = false;
+    R.aoSeed = false;
+    R.hit.kind = RC_KIND_SKY;
+    R.hit.steps = 0;
+    if (active) {
+        shade_pixel(A, px, py, R);
+        const uint32_t idx = local_index(A, px, localRow);
+        // AO pixels get their final colour from the AO kernel
+        if (!(R.aoSeed)) store_pixel(A, idx, R.color);
+        if (A.hits) A.hits[idx] = R.hit;
+    }
+
+    // AO seeds: warp-aggregated append
+    const bool seed = active && R.aoSeed;
+    const unsigned seedMask = __ballot_sync(0xffffffffu, seed);
+    if (seedMask) {
+        unsigned base = 0;
+        const int leader = __ffs(seedMask) - 1;
+        if ((int)lane == leader) base = atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (seed) {
+            AoSeed s;
+            s.ex = R.sx_;
+            s.ey = R.sy_;
+            s.ez = R.sz_;
+            s.x = R.hit.x;
+            s.y = R.hit.y;
+            s.z = R.hit.z;
+            s.r = R.color.x;
+            s.g = R.color.y;
+            s.b = R.color.z;
+            s.pixel = local_index(A, px, localRow);
+            const uint32_t sneg = R.hit.face == 0 ? (R.hit.flags & RC_HF_STEPX_NEG)
+                                                  : (R.hit.face == 1 ? (R.hit.flags & RC_HF_STEPY_NEG) : (R.hit.flags & RC_HF_STEPZ_NEG));
+            // normal sign = -step[face]: negative normal iff the step was positive
+            s.face_sign = (uint32_t)R.hit.face | (sneg ? 0u : 4u);
+            s.pad = 0;
+            A.ao_seeds[base + __popc(seedMask & ((1u << lane) - 1u))] = s;
+        }
+    }
+
+    // frame statistics: one atomic per warp per counter
+    const unsigned tracedMask = __ballot_sync(0xffffffffu, active && R.traced);
+    const unsigned shadowMask = __ballot_sync(0xffffffffu, active && R.shadowRay);
+    const unsigned hitMask = __ballot_sync(0xffffffffu, active && R.hit.kind == RC_KIND_HIT);
+    unsigned stepSum = active ? (unsigned)R.hit.steps : 0u;
+    for (int o = 16; o > 0; o >>= 1) stepSum += __shfl_xor_sync(0xffffffffu, stepSum, o);
+    if (lane == 0) {
+        if (tracedMask) atomicAdd(&A.counters->primary_rays, (unsigned long long)__popc(tracedMask));
+        if (shadowMask) atomicAdd(&A.counters->shadow_rays, (unsigned long long)__popc(shadowMask));
+        if (hitMask) atomicAdd(&A.counters->hit_pixels, (unsigned long long)__popc(hitMask));
+        if (stepSum) atomicAdd(&A.counters->primary_steps, (unsigned long long)stepSum);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// AO kernel (semantics = oracle castAo): one thread per hit pixel,
+// all lanes of a warp walk the same table entry at the same time, so the
+// direction comes from __constant__ memory as a broadcast.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) ao_kernel(const __grid_constant__ FrameArgs A) {
+    const uint32_t nSeeds = A.counters->ao_seed_count;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nSeeds) return;
+    const rc_frame_params& P = A.p;
+    const DeviceWorld& W = A.world;
+    const AoSeed s = A.ao_seeds[t];
+    const int face = (int)(s.face_sign & 3u);
+    const bool negNormal = (s.face_sign & 4u) != 0u;
+
+    Cursor cur;
+    cursor_reset(W, cur);
+    uint32_t occluded = 0;
+    for (uint32_t k = 0; k < P.ao_samples; k++) {
+        const float tx = c_hemi[3 * k + 0], ty = c_hemi[3 * k + 1], up = c_hemi[3 * k + 2];
+        const float itx = c_hemi_inv[3 * k + 0], ity = c_hemi_inv[3 * k + 1], iup = c_hemi_inv[3 * k + 2];
+        // d[face] = sg*up, d[(face+1)%3] = tx, d[(face+2)%3] = ty ; 1/(-up) == -(1/up) exactly
+        const float su = negNormal ? -up : up, siu = negNormal ? -iup : iup;
+        Ray r;
+        float dx, dy, dz, ix, iy, iz;
+        if (face == 0) {
+            dx = su; dy = tx; dz = ty; ix = siu; iy = itx; iz = ity;
+        } else if (face == 1) {
+            dy = su; dz = tx; dx = ty; iy = siu; iz = itx; ix = ity;
+        } else {
+            dz = su; dx = tx; dy = ty; iz = siu; ix = itx; iy = ity;
+        }
+        r.dx = dx; r.dy = dy; r.dz = dz;
+        r.sx = dx < 0.0f ? -1 : 1;
+        r.sy = dy < 0.0f ? -1 : 1;
+        r.sz = dz < 0.0f ? -1 : 1;
+        r.ddx = ix; r.ddy = iy; r.ddz = iz;
+        r.adx = fabsf(ix); r.ady = fabsf(iy); r.adz = fabsf(iz);
+        Pos p;
+        p.x = s.x; p.y = s.y; p.z = s.z;
+        p.ex = r.sx < 0 ? FSUB(s.ex, 1.0f) : s.ex;
+        p.ey = r.sy < 0 ? FSUB(s.ey, 1.0f) : s.ey;
+        p.ez = r.sz < 0 ? FSUB(s.ez, 1.0f) : s.ez;
+        init_delta_pos(r, p);
+        if (face == 0) p.tx = FSUB(p.tx, r.adx);
+        else if (face == 1) p.ty = FSUB(p.ty, r.ady);
+        else p.tz = FSUB(p.tz, r.adz);
+        uint32_t i = P.ao_steps;
+        uint32_t w = 0u;
+        CellCount c;
+        c.nx = c.ny = c.nz = 1;
+        int cellShift;
+        while ((w == 0u || (word_flags(w) & 0x10u)) && i-- != 0u) {
+            bool leftCell;
+            dda_step<false>(r, p, c, leftCell);
+            if (leftCell) {
+                w = lookup(W, cur, p.x, p.y, p.z, cellShift);
+                after_lookup(c, r, p, w, cellShift);
+            }
+        }
+        if (w != 0u) occluded++;
+    }
+    const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
+    store_pixel(A, s.pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
+    if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
+}
+
+__global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    Cursor cur;
+    cursor_reset(W, cur);
+    int shift = -1;
+    outWords[t] = lookup(W, cur, xyz[3 * t], xyz[3 * t + 1], xyz[3 * t + 2], shift);
+    outShift[t] = shift;
+}
+
+__global__ void detmath_kernel(const float* in, uint32_t n, float* outSin, float* outExp) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    outSin[t] = det_sin(in[t]);
+    outExp[t] = det_exp(in[t]);
+}
+
+cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream) {
+    if (n > RC_MAX_AO_SAMPLES) return cudaErrorInvalidValue;
+    float inv[3 * RC_MAX_AO_SAMPLES];
+    for (uint32_t i = 0; i < 3 * n; i++) inv[i] = 1.0f / dirs[i];  // IEEE division, as the oracle's buildRay does per ray
+    cudaError_t e = cudaMemcpyToSymbolAsync(c_hemi, dirs, 3 * n * sizeof(float), 0, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyToSymbolAsync(c_hemi_inv, inv, 3 * n * sizeof(float), 0, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(stream);  // inv[] lives on this stack frame
+}
+
+cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
+    dim3 grid((args.p.width + 15u) / 16u, (args.local_rows + 7u) / 8u);
+    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
+    primary_kernel<<<grid, 128, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
+    if (maxSeeds == 0) return cudaSuccess;
+    ao_kernel<<<(maxSeeds + 127u) / 128u, 128, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift,
+                          cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    lookup_kernel<<<(n + 127u) / 128u, 128, 0, stream>>>(world, xyz, n, outWords, outShift);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_detmath(const float* in, uint32_t n, float* outSin, float* outExp, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    detmath_kernel<<<(n + 127u) / 128u, 128, 0, stream>>>(in, n, outSin, outExp);
+    return cudaGetLastError();
+}
+
+}  // namespace rc

@@ -1,0 +1,75 @@
+// kernels.h -- launch interface between the C-ABI layer (rc_api.cu) and the
+// sm_100a kernels (kernels.cu). Device pointers + PODs only.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rc.h"
+
+namespace rc {
+
+// Rows of the image are dealt to ranks in bands of RC_BAND_ROWS rows:
+// band b belongs to rank b % world_size and is stored at local band b / world_size
+// of that rank's (compact) frame buffers. world_size 1 => plain bottom-up frame.
+constexpr uint32_t BAND_ROWS = 16;
+
+struct DeviceWorld {
+    const uint4* nodes;      // PackedNode[]
+    const uint32_t* voxels;  // material words
+    const uint4* palette;    // PaletteEntry[]
+    uint32_t n_nodes;
+    uint32_t n_top;          // BFS prefix staged in shared memory by the persistent kernel
+    int root_shift;          // cell shift of the root's children: 2*(max_depth-2)
+    uint32_t wrap;           // (1 << 2*(max_depth-1)) - 1
+};
+
+// Per-hit-pixel record handed from the primary kernel to the AO kernel.
+struct AoSeed {
+    float ex, ey, ez;   // un-biased pos.exact at the hit (low_res.frag:343-345)
+    int x, y, z;        // hit voxel
+    float r, g, b;      // shaded colour before AO
+    uint32_t pixel;     // index into the (compact) frame buffers
+    uint32_t face_sign; // bits 0-1 face, bit 2: normal sign negative
+    uint32_t pad;
+};
+
+struct FrameCounters {
+    unsigned long long primary_rays;
+    unsigned long long shadow_rays;
+    unsigned long long hit_pixels;
+    unsigned long long primary_steps;
+    unsigned int ao_seed_count;
+    unsigned int tile_cursor;  // persistent-kernel work queue
+    unsigned int pad[2];
+};
+
+struct FrameArgs {
+    rc_frame_params p;
+    DeviceWorld world;
+    uint32_t rank, world_size;
+    uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
+    uint32_t n_local_bands;
+    uchar4* rgba8;           // [local_rows][width]
+    float4* rgba32f;         // optional
+    rc_hit* hits;            // optional
+    AoSeed* ao_seeds;        // optional (ao_samples > 0)
+    FrameCounters* counters;
+};
+
+// Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory.
+cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream);
+
+// Primary + shading + shadow kernel. Returns the launch error.
+cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream);
+
+// AO kernel over the seeds appended by the primary kernel.
+cudaError_t launch_ao(const FrameArgs& args, uint32_t max_seeds, cudaStream_t stream);
+
+// Single-voxel lookups through the same device code path the kernels use (tests).
+cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,
+                          cudaStream_t stream);
+
+// Device versions of the deterministic sin/exp (tests compare them with the oracle's).
+cudaError_t launch_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp, cudaStream_t stream);
+
+}  // namespace rc

@@ -1,0 +1,531 @@
+// rc_api.cu -- the C-ABI of include/rc.h: process-global context, world upload
+// (flatten + copy), frame launch, read-back.  Host logic only; the kernels are in
+// kernels.cu.  There is deliberately no CPU rendering path in this library.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <chrono>
+#include <string>
+#include <vector>
+
+#include "../../include/rc.h"
+#include "../../include/rc_debug.h"
+#include "kernels.h"
+#include "packed_world.h"
+
+namespace {
+
+using namespace rc;
+
+struct Context {
+    bool initialized = false;
+    int device = -1;
+    cudaStream_t ownStream = nullptr;
+    cudaStream_t stream = nullptr;
+    uint32_t rank = 0, worldSize = 1;
+
+    // world
+    bool haveWorld = false;
+    uint4* dNodes = nullptr;
+    uint32_t* dVoxels = nullptr;
+    uint4* dPalette = nullptr;
+    DeviceWorld world{};
+    rc_world_info info{};
+    PackedWorld packed;       // host copy of the uploaded world (debug lookups)
+    PackedWorld debugPacked;  // result of rc_debug_flatten_host (CPU-only tests)
+
+    // frame buffers (grown on demand)
+    size_t pixelCapacity = 0;
+    uchar4* dRgba8 = nullptr;
+    float4* dRgba32f = nullptr;
+    rc_hit* dHits = nullptr;
+    AoSeed* dSeeds = nullptr;
+    size_t f32Capacity = 0, hitCapacity = 0, seedCapacity = 0;
+    FrameCounters* dCounters = nullptr;
+    FrameCounters* hCounters = nullptr;  // pinned
+
+    // last frame
+    bool haveFrame = false;
+    rc_frame_params frame{};
+    uint32_t localRows = 0, localBands = 0;
+    bool frameHasHits = false, frameHasF32 = false;
+    uint32_t hemiLoaded = 0;
+    uint32_t launches = 0;
+    cudaEvent_t evStart = nullptr, evPrimary = nullptr, evEnd = nullptr;
+
+    std::string lastError;
+};
+
+Context g;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g.lastError = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) return fail(RC_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e)); \
+    } while (0)
+
+void freeWorld() {
+    if (g.dNodes) cudaFree(g.dNodes);
+    if (g.dVoxels) cudaFree(g.dVoxels);
+    if (g.dPalette) cudaFree(g.dPalette);
+    g.dNodes = nullptr;
+    g.dVoxels = nullptr;
+    g.dPalette = nullptr;
+    g.haveWorld = false;
+}
+
+void freeFrameBuffers() {
+    if (g.dRgba8) cudaFree(g.dRgba8);
+    if (g.dRgba32f) cudaFree(g.dRgba32f);
+    if (g.dHits) cudaFree(g.dHits);
+    if (g.dSeeds) cudaFree(g.dSeeds);
+    g.dRgba8 = nullptr;
+    g.dRgba32f = nullptr;
+    g.dHits = nullptr;
+    g.dSeeds = nullptr;
+    g.pixelCapacity = g.f32Capacity = g.hitCapacity = g.seedCapacity = 0;
+    g.haveFrame = false;
+}
+
+// gen_hemisphare_distrib.py:4-12 with num_pts = n, in double, rounded to fp32;
+// stored (x, y, up): the script prints (x, z, y) and the shader reads it back
+// with .xzy (light_scattering.frag:230).
+void hemisphereTable(uint32_t n, float* out) {
+    const double pi = 3.141592653589793;
+    for (uint32_t i = 0; i < n; i++) {
+        const double idx = (double)i + 0.5;
+        const double phi = acos(1.0 - idx * 0.85 / (double)n);
+        const double theta = pi * (1.0 + sqrt(5.0)) * idx;
+        out[3 * i + 0] = (float)(cos(theta) * sin(phi));
+        out[3 * i + 1] = (float)(sin(theta) * sin(phi));
+        out[3 * i + 2] = (float)cos(phi);
+    }
+}
+
+template <typename T>
+int growBuffer(T*& ptr, size_t& capacity, size_t need) {
+    if (need <= capacity) return RC_OK;
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    capacity = 0;
+    CUDA_TRY(cudaMalloc((void**)&ptr, need * sizeof(T)));
+    capacity = need;
+    return RC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rc_abi_version(void) { return RC_ABI_VERSION; }
+
+const char* rc_last_error(void) { return g.lastError.c_str(); }
+
+int rc_init(int device) {
+    if (g.initialized) rc_shutdown();
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(RC_ERR_CUDA, "rc_init: no CUDA device (%s); this library has no CPU path",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(RC_ERR_INVALID_ARGUMENT, "rc_init: device %d of %d", device, count);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(RC_ERR_UNSUPPORTED, "rc_init: device %d is sm_%d%d; librc is built for sm_100a only", device, prop.major,
+                    prop.minor);
+    CUDA_TRY(cudaStreamCreateWithFlags(&g.ownStream, cudaStreamNonBlocking));
+    g.stream = g.ownStream;
+    CUDA_TRY(cudaMalloc((void**)&g.dCounters, sizeof(FrameCounters)));
+    CUDA_TRY(cudaMallocHost((void**)&g.hCounters, sizeof(FrameCounters)));
+    memset(g.hCounters, 0, sizeof(FrameCounters));
+    CUDA_TRY(cudaEventCreate(&g.evStart));
+    CUDA_TRY(cudaEventCreate(&g.evPrimary));
+    CUDA_TRY(cudaEventCreate(&g.evEnd));
+    g.device = device;
+    g.rank = 0;
+    g.worldSize = 1;
+    g.hemiLoaded = 0;
+    g.initialized = true;
+    g.lastError.clear();
+    return RC_OK;
+}
+
+void rc_shutdown(void) {
+    if (!g.initialized) return;
+    cudaSetDevice(g.device);
+    cudaStreamSynchronize(g.stream);
+    freeWorld();
+    freeFrameBuffers();
+    if (g.dCounters) cudaFree(g.dCounters);
+    if (g.hCounters) cudaFreeHost(g.hCounters);
+    g.dCounters = nullptr;
+    g.hCounters = nullptr;
+    if (g.evStart) cudaEventDestroy(g.evStart);
+    if (g.evPrimary) cudaEventDestroy(g.evPrimary);
+    if (g.evEnd) cudaEventDestroy(g.evEnd);
+    g.evStart = g.evPrimary = g.evEnd = nullptr;
+    if (g.ownStream) cudaStreamDestroy(g.ownStream);
+    g.ownStream = g.stream = nullptr;
+    g.packed = PackedWorld();
+    g.initialized = false;
+}
+
+int rc_set_stream(void* cuda_stream) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_set_stream: call rc_init first");
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    g.stream = cuda_stream ? (cudaStream_t)cuda_stream : g.ownStream;
+    return RC_OK;
+}
+
+int rc_set_shard(uint32_t rank, uint32_t world_size) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_set_shard: call rc_init first");
+    if (world_size == 0 || rank >= world_size)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_set_shard: rank %u of %u", rank, world_size);
+    g.rank = rank;
+    g.worldSize = world_size;
+    g.haveFrame = false;
+    return RC_OK;
+}
+
+int rc_upload_world(const rc_world_desc* desc) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_upload_world: call rc_init first");
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_upload_world: null desc");
+    CUDA_TRY(cudaSetDevice(g.device));
+    auto t0 = std::chrono::steady_clock::now();
+    PackedWorld pw;
+    std::string err;
+    int rcode = flatten_world(*desc, pw, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    auto t1 = std::chrono::steady_clock::now();
+
+    CUDA_TRY(cudaStreamSynchronize(g.stream));  // no frame may still read the old world
+    freeWorld();
+    const size_t nodeBytes = pw.nodes.size() * sizeof(PackedNode);
+    const size_t voxBytes = (pw.voxels.size() ? pw.voxels.size() : 1) * sizeof(uint32_t);
+    const size_t palBytes = (pw.palette.size() ? pw.palette.size() : 1) * sizeof(PaletteEntry);
+    CUDA_TRY(cudaMalloc((void**)&g.dNodes, nodeBytes));
+    CUDA_TRY(cudaMalloc((void**)&g.dVoxels, voxBytes));
+    CUDA_TRY(cudaMalloc((void**)&g.dPalette, palBytes));
+    CUDA_TRY(cudaMemcpyAsync(g.dNodes, pw.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, g.stream));
+    if (!pw.voxels.empty())
+        CUDA_TRY(cudaMemcpyAsync(g.dVoxels, pw.voxels.data(), pw.voxels.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                 g.stream));
+    if (!pw.palette.empty())
+        CUDA_TRY(cudaMemcpyAsync(g.dPalette, pw.palette.data(), pw.palette.size() * sizeof(PaletteEntry),
+                                 cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    auto t2 = std::chrono::steady_clock::now();
+
+    g.world.nodes = g.dNodes;
+    g.world.voxels = g.dVoxels;
+    g.world.palette = g.dPalette;
+    g.world.n_nodes = (uint32_t)pw.nodes.size();
+    g.world.n_top = 0;
+    g.world.root_shift = 2 * ((int)pw.max_depth - 2);
+    g.world.wrap = (1u << (2 * (pw.max_depth - 1))) - 1u;
+
+    memset(&g.info, 0, sizeof(g.info));
+    g.info.ref_nodes = pw.ref_nodes;
+    g.info.ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+    g.info.packed_nodes = pw.nodes.size();
+    g.info.packed_voxels = pw.voxels.size();
+    g.info.packed_materials = pw.palette.size();
+    g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
+    g.info.max_depth = pw.max_depth;
+    g.info.null_children = pw.null_children;
+    g.info.flatten_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    g.info.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
+    g.packed = std::move(pw);
+    g.haveWorld = true;
+    return RC_OK;
+}
+
+int rc_world_info_get(rc_world_info* out) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_world_info_get: call rc_init first");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_world_info_get: no world uploaded");
+    if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_world_info_get: null out");
+    *out = g.info;
+    return RC_OK;
+}
+
+int rc_render_frame(const rc_frame_params* params) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_render_frame: call rc_init first");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_render_frame: call rc_upload_world first");
+    if (!params) return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame: null params");
+    const rc_frame_params& p = *params;
+    if (p.width == 0 || p.height == 0 || p.width > 65536 || p.height > 65536)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame: resolution %ux%u", p.width, p.height);
+    if (p.ao_samples > RC_MAX_AO_SAMPLES)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame: ao_samples %u > %u", p.ao_samples, RC_MAX_AO_SAMPLES);
+    if (p.max_steps > 65535 || p.shadow_steps > 65535)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame: step limits above 65535 do not fit rc_hit");
+    CUDA_TRY(cudaSetDevice(g.device));
+
+    // rows owned by this rank: bands b with b % world == rank
+    const uint32_t totalBands = (p.height + BAND_ROWS - 1) / BAND_ROWS;
+    const uint32_t localBands = totalBands > g.rank ? (totalBands - g.rank + g.worldSize - 1) / g.worldSize : 0;
+    const uint32_t localRows = localBands * BAND_ROWS;
+    const size_t pixels = (size_t)(localRows ? localRows : 1) * p.width;
+
+    int rcode;
+    if ((rcode = growBuffer(g.dRgba8, g.pixelCapacity, pixels)) != RC_OK) return rcode;
+    if (p.flags & RC_F_RGBA32F)
+        if ((rcode = growBuffer(g.dRgba32f, g.f32Capacity, pixels)) != RC_OK) return rcode;
+    if (p.flags & RC_F_HITS)
+        if ((rcode = growBuffer(g.dHits, g.hitCapacity, pixels)) != RC_OK) return rcode;
+    if (p.ao_samples > 0) {
+        if ((rcode = growBuffer(g.dSeeds, g.seedCapacity, pixels)) != RC_OK) return rcode;
+        if (g.hemiLoaded != p.ao_samples) {
+            std::vector<float> tab(3 * (size_t)p.ao_samples);
+            hemisphereTable(p.ao_samples, tab.data());
+            CUDA_TRY(upload_hemisphere(tab.data(), p.ao_samples, g.stream));
+            g.hemiLoaded = p.ao_samples;
+        }
+    }
+
+    FrameArgs a;
+    memset(&a, 0, sizeof(a));
+    a.p = p;
+    a.world = g.world;
+    a.rank = g.rank;
+    a.world_size = g.worldSize;
+    a.local_rows = localRows;
+    a.n_local_bands = localBands;
+    a.rgba8 = g.dRgba8;
+    a.rgba32f = (p.flags & RC_F_RGBA32F) ? g.dRgba32f : nullptr;
+    a.hits = (p.flags & RC_F_HITS) ? g.dHits : nullptr;
+    a.ao_seeds = p.ao_samples > 0 ? g.dSeeds : nullptr;
+    a.counters = g.dCounters;
+
+    g.launches = 0;
+    CUDA_TRY(cudaMemsetAsync(g.dCounters, 0, sizeof(FrameCounters), g.stream));
+    CUDA_TRY(cudaEventRecord(g.evStart, g.stream));
+    CUDA_TRY(launch_primary(a, g.stream));
+    g.launches++;
+    CUDA_TRY(cudaEventRecord(g.evPrimary, g.stream));
+    if (p.ao_samples > 0 && localRows > 0) {
+        CUDA_TRY(launch_ao(a, (uint32_t)pixels, g.stream));
+        g.launches++;
+    }
+    CUDA_TRY(cudaEventRecord(g.evEnd, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.hCounters, g.dCounters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, g.stream));
+
+    g.frame = p;
+    g.localRows = localRows;
+    g.localBands = localBands;
+    g.frameHasHits = (p.flags & RC_F_HITS) != 0;
+    g.frameHasF32 = (p.flags & RC_F_RGBA32F) != 0;
+    g.haveFrame = true;
+    return RC_OK;
+}
+
+int rc_sync(void) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_sync: call rc_init first");
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    return RC_OK;
+}
+
+// Copies this rank's rows into their place in a full bottom-up frame at dst.
+// (world_size 1: one contiguous copy.)
+static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel) {
+    const rc_frame_params& p = g.frame;
+    const size_t rowBytes = (size_t)p.width * bytesPerPixel;
+    if (g.worldSize == 1) {
+        CUDA_TRY(cudaMemcpyAsync(dst, src, rowBytes * p.height, cudaMemcpyDeviceToHost, g.stream));
+    } else {
+        for (uint32_t lb = 0; lb < g.localBands; lb++) {
+            const uint32_t band = lb * g.worldSize + g.rank;
+            const uint32_t row0 = band * BAND_ROWS;
+            if (row0 >= p.height) break;
+            const uint32_t rows = (row0 + BAND_ROWS <= p.height) ? BAND_ROWS : (p.height - row0);
+            CUDA_TRY(cudaMemcpyAsync((uint8_t*)dst + (size_t)row0 * rowBytes,
+                                     (const uint8_t*)src + (size_t)lb * BAND_ROWS * rowBytes, rows * rowBytes,
+                                     cudaMemcpyDeviceToHost, g.stream));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    return RC_OK;
+}
+
+int rc_read_image(void* dst, size_t dst_bytes, int format) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_image: call rc_init first");
+    if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_read_image: no frame rendered");
+    if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: null dst");
+    const size_t pixels = (size_t)g.frame.width * g.frame.height;
+    if (format == RC_RGBA8) {
+        if (dst_bytes < pixels * 4) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_image: need %zu bytes", pixels * 4);
+        return copyRowsToHost(dst, g.dRgba8, 4);
+    } else if (format == RC_RGBA32F) {
+        if (!g.frameHasF32) return fail(RC_ERR_NO_FRAME, "rc_read_image: frame was rendered without RC_F_RGBA32F");
+        if (dst_bytes < pixels * 16) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_image: need %zu bytes", pixels * 16);
+        return copyRowsToHost(dst, g.dRgba32f, 16);
+    }
+    return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: unknown format %d", format);
+}
+
+int rc_read_hits(rc_hit* dst, size_t n) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_hits: call rc_init first");
+    if (!g.haveFrame || !g.frameHasHits) return fail(RC_ERR_NO_FRAME, "rc_read_hits: no frame rendered with RC_F_HITS");
+    if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_hits: null dst");
+    const size_t pixels = (size_t)g.frame.width * g.frame.height;
+    if (n < pixels) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_hits: need %zu records", pixels);
+    return copyRowsToHost(dst, g.dHits, sizeof(rc_hit));
+}
+
+int rc_frame_stats_get(rc_frame_stats* out) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_stats_get: call rc_init first");
+    if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_frame_stats_get: no frame rendered");
+    if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_stats_get: null out");
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    memset(out, 0, sizeof(*out));
+    out->primary_rays = g.hCounters->primary_rays;
+    out->shadow_rays = g.hCounters->shadow_rays;
+    out->hit_pixels = g.hCounters->hit_pixels;
+    out->ao_rays = (uint64_t)g.hCounters->ao_seed_count * g.frame.ao_samples;
+    out->primary_steps = g.hCounters->primary_steps;
+    out->kernel_launches = g.launches;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g.evStart, g.evPrimary) == cudaSuccess) out->primary_ms = ms;
+    if (cudaEventElapsedTime(&ms, g.evPrimary, g.evEnd) == cudaSuccess) out->ao_ms = ms;
+    if (cudaEventElapsedTime(&ms, g.evStart, g.evEnd) == cudaSuccess) out->total_ms = ms;
+    return RC_OK;
+}
+
+void* rc_device_image(int format) {
+    if (!g.initialized || !g.haveFrame) return nullptr;
+    if (format == RC_RGBA8) return g.dRgba8;
+    if (format == RC_RGBA32F && g.frameHasF32) return g.dRgba32f;
+    return nullptr;
+}
+
+void* rc_device_hits(void) {
+    if (!g.initialized || !g.haveFrame || !g.frameHasHits) return nullptr;
+    return g.dHits;
+}
+
+int rc_hemisphere_table(uint32_t n, float* out) {
+    if (n == 0 || n > RC_MAX_AO_SAMPLES || !out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_hemisphere_table: n=%u", n);
+    hemisphereTable(n, out);
+    return RC_OK;
+}
+
+// ---- debug / test entry points (declared in include/rc_debug.h) -----------------
+
+// Packed-form lookup on a host copy: which = 0 the uploaded world, 1 the result of
+// rc_debug_flatten_host. out_word = material word (0 empty), out_shift = uniform
+// cell shift, out_leaf[4] = palette entry (the reference Leaf verbatim) when solid.
+int rc_debug_lookup_host(int which, int32_t x, int32_t y, int32_t z, uint32_t* out_word, int32_t* out_shift,
+                         uint32_t* out_leaf) {
+    const PackedWorld& pw = which ? g.debugPacked : g.packed;
+    if (pw.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_lookup_host: no world (which=%d)", which);
+    int shift = 0;
+    uint32_t w = packed_lookup(pw, x, y, z, &shift);
+    if (out_word) *out_word = w;
+    if (out_shift) *out_shift = shift;
+    if (w && out_leaf) memcpy(out_leaf, &pw.palette[w & MATERIAL_INDEX_MASK], 16);
+    return RC_OK;
+}
+
+// Batch form: xyz = 3*n ints; out_words[n]; out_leaves[4*n] (zeros when empty).
+int rc_debug_lookup_host_batch(int which, const int32_t* xyz, uint64_t n, uint32_t* out_words, int32_t* out_shifts,
+                               uint32_t* out_leaves) {
+    const PackedWorld& pw = which ? g.debugPacked : g.packed;
+    if (pw.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_lookup_host_batch: no world (which=%d)", which);
+    for (uint64_t i = 0; i < n; i++) {
+        int shift = 0;
+        uint32_t w = packed_lookup(pw, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], &shift);
+        out_words[i] = w;
+        if (out_shifts) out_shifts[i] = shift;
+        if (out_leaves) {
+            if (w) memcpy(out_leaves + 4 * i, &pw.palette[w & MATERIAL_INDEX_MASK], 16);
+            else memset(out_leaves + 4 * i, 0, 16);
+        }
+    }
+    return RC_OK;
+}
+
+// Same lookup through the device code path, for n voxels (xyz: 3*n ints, host memory).
+int rc_debug_lookup_device(const int32_t* xyz, uint32_t n, uint32_t* out_words, int32_t* out_shifts) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_lookup_device: call rc_init first");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_debug_lookup_device: no world");
+    int *dXyz = nullptr, *dShift = nullptr;
+    uint32_t* dWords = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&dXyz, (size_t)n * 12));
+    CUDA_TRY(cudaMalloc((void**)&dShift, (size_t)n * 4));
+    CUDA_TRY(cudaMalloc((void**)&dWords, (size_t)n * 4));
+    CUDA_TRY(cudaMemcpyAsync(dXyz, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(launch_lookup(g.world, dXyz, n, dWords, dShift, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(out_words, dWords, (size_t)n * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(out_shifts, dShift, (size_t)n * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    cudaFree(dXyz);
+    cudaFree(dShift);
+    cudaFree(dWords);
+    return RC_OK;
+}
+
+// Palette entry (Leaf verbatim) of a material word of the uploaded world.
+int rc_debug_palette(uint32_t word, uint32_t* out_leaf) {
+    if (g.packed.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_palette: no world");
+    const uint32_t idx = word & MATERIAL_INDEX_MASK;
+    if (idx >= g.packed.palette.size()) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_palette: index %u", idx);
+    memcpy(out_leaf, &g.packed.palette[idx], 16);
+    return RC_OK;
+}
+
+// Host-only flatten (no CUDA needed): lets CPU tests exercise the flattener.
+int rc_debug_flatten_host(const rc_world_desc* desc, rc_world_info* info) {
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_flatten_host: null desc");
+    PackedWorld pw;
+    std::string err;
+    int rcode = flatten_world(*desc, pw, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    if (info) {
+        memset(info, 0, sizeof(*info));
+        info->ref_nodes = pw.ref_nodes;
+        info->ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+        info->packed_nodes = pw.nodes.size();
+        info->packed_voxels = pw.voxels.size();
+        info->packed_materials = pw.palette.size();
+        info->packed_bytes = pw.nodes.size() * 16 + pw.voxels.size() * 4 + pw.palette.size() * 16;
+        info->max_depth = pw.max_depth;
+        info->null_children = pw.null_children;
+    }
+    g.debugPacked = std::move(pw);
+    return RC_OK;
+}
+
+// Device det_sin / det_exp over n floats (host pointers).
+int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_detmath: call rc_init first");
+    float *dIn = nullptr, *dS = nullptr, *dE = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&dIn, (size_t)n * 4));
+    CUDA_TRY(cudaMalloc((void**)&dS, (size_t)n * 4));
+    CUDA_TRY(cudaMalloc((void**)&dE, (size_t)n * 4));
+    CUDA_TRY(cudaMemcpyAsync(dIn, in, (size_t)n * 4, cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(launch_detmath(dIn, n, dS, dE, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(out_sin, dS, (size_t)n * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(out_exp, dE, (size_t)n * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    cudaFree(dIn);
+    cudaFree(dS);
+    cudaFree(dE);
+    return RC_OK;
+}
+
+}  // extern "C"

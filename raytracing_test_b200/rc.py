@@ -1,0 +1,309 @@
+"""ctypes binding of librc.so (include/rc.h) -- plumbing for tests and bench.py.
+
+The product is the shared library; this module only marshals numpy buffers into
+the C-ABI the reference's C++ host would call.  It fails loudly when the library
+is missing or when no CUDA device is usable: there is no CPU fallback.
+"""
+import ctypes
+import math
+import os
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "librc.so")
+
+RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F = 1, 2, 4, 8
+RC_RGBA8, RC_RGBA32F = 0, 1
+KIND_SKY, KIND_HIT, KIND_CAMERA_INSIDE, KIND_CROSSHAIR, KIND_HIGHLIGHT, KIND_DEBUG = range(6)
+HF_SHADOWED, HF_REFLECTED, HF_REFRACTED, HF_FACING_SUN = 1, 2, 4, 8
+BAND_ROWS = 16
+
+HIT_DTYPE = np.dtype(
+    [
+        ("x", "<i4"), ("y", "<i4"), ("z", "<i4"),
+        ("steps", "<u2"), ("shadow_steps", "<u2"),
+        ("face", "u1"), ("kind", "u1"), ("flags", "u1"), ("ao_occluded", "u1"),
+    ]
+)
+
+
+class RcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"librc error {code}: {message}")
+        self.code = code
+
+
+class WorldDesc(ctypes.Structure):
+    _fields_ = [
+        ("node_blocks", ctypes.POINTER(ctypes.c_void_p)),
+        ("array_blocks", ctypes.POINTER(ctypes.c_void_p)),
+        ("n_node_blocks", ctypes.c_uint32), ("n_array_blocks", ctypes.c_uint32),
+        ("block_bytes", ctypes.c_uint32), ("root_index", ctypes.c_uint32),
+        ("node_bytes_used", ctypes.c_uint64), ("array_bytes_used", ctypes.c_uint64),
+        ("max_depth", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+    ]
+
+
+class WorldInfo(ctypes.Structure):
+    _fields_ = [
+        ("ref_nodes", ctypes.c_uint64), ("ref_bytes", ctypes.c_uint64),
+        ("packed_nodes", ctypes.c_uint64), ("packed_voxels", ctypes.c_uint64),
+        ("packed_materials", ctypes.c_uint64), ("packed_bytes", ctypes.c_uint64),
+        ("max_depth", ctypes.c_uint32), ("null_children", ctypes.c_uint32),
+        ("flatten_ms", ctypes.c_double), ("upload_ms", ctypes.c_double),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class FrameParams(ctypes.Structure):
+    _fields_ = [
+        ("origin", ctypes.c_float * 3), ("camera_dir", ctypes.c_float * 3), ("sun_dir", ctypes.c_float * 3),
+        ("mouse_pos", ctypes.c_float * 2), ("proj_plane", ctypes.c_float * 2),
+        ("delta_time", ctypes.c_float), ("ao_strength", ctypes.c_float),
+        ("looking_at", ctypes.c_int32 * 3), ("render_pos_data", ctypes.c_int32),
+        ("width", ctypes.c_uint32), ("height", ctypes.c_uint32),
+        ("max_steps", ctypes.c_uint32), ("shadow_steps", ctypes.c_uint32),
+        ("ao_samples", ctypes.c_uint32), ("ao_steps", ctypes.c_uint32),
+        ("flags", ctypes.c_uint32),
+    ]
+
+
+class FrameStats(ctypes.Structure):
+    _fields_ = [
+        ("primary_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64), ("ao_rays", ctypes.c_uint64),
+        ("hit_pixels", ctypes.c_uint64), ("primary_steps", ctypes.c_uint64),
+        ("kernel_launches", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+        ("primary_ms", ctypes.c_float), ("ao_ms", ctypes.c_float), ("total_ms", ctypes.c_float),
+        ("reserved2", ctypes.c_float),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("reserved")}
+
+
+# name -> (restype, argtypes); every symbol include/rc.h and include/rc_debug.h declare
+ABI = {
+    "rc_init": (ctypes.c_int, [ctypes.c_int]),
+    "rc_shutdown": (None, []),
+    "rc_last_error": (ctypes.c_char_p, []),
+    "rc_abi_version": (ctypes.c_int, []),
+    "rc_set_stream": (ctypes.c_int, [ctypes.c_void_p]),
+    "rc_set_shard": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32]),
+    "rc_upload_world": (ctypes.c_int, [ctypes.POINTER(WorldDesc)]),
+    "rc_world_info_get": (ctypes.c_int, [ctypes.POINTER(WorldInfo)]),
+    "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
+    "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
+    "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
+    "rc_sync": (ctypes.c_int, []),
+    "rc_frame_stats_get": (ctypes.c_int, [ctypes.POINTER(FrameStats)]),
+    "rc_device_image": (ctypes.c_void_p, [ctypes.c_int]),
+    "rc_device_hits": (ctypes.c_void_p, []),
+    "rc_hemisphere_table": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
+    # rc_debug.h
+    "rc_debug_flatten_host": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.POINTER(WorldInfo)]),
+    "rc_debug_lookup_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "rc_debug_lookup_host_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p,
+                                                   ctypes.c_void_p, ctypes.c_void_p]),
+    "rc_debug_lookup_device": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
+    "rc_debug_palette": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_debug_detmath": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
+}
+
+_lib = None
+
+
+def load_library(path=LIB_PATH):
+    """Loads librc.so and types every exported symbol. Raises if the library is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). There is no CPU fallback."
+            )
+        lib = ctypes.CDLL(path)
+        for name, (restype, argtypes) in ABI.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is missing
+            fn.restype = restype
+            fn.argtypes = argtypes
+        _lib = lib
+    return _lib
+
+
+def _check(lib, code):
+    if code != 0:
+        raise RcError(code, lib.rc_last_error().decode("utf-8", "replace"))
+
+
+def make_world_desc(node_block_ptrs, array_block_ptrs, node_bytes_used, array_bytes_used, *, block_bytes=1 << 22,
+                    root_index=0, max_depth=6):
+    """rc_world_desc over raw host block pointers (ints). Keeps the pointer arrays alive on the struct."""
+    d = WorldDesc()
+    nb = (ctypes.c_void_p * len(node_block_ptrs))(*node_block_ptrs)
+    ab = (ctypes.c_void_p * len(array_block_ptrs))(*array_block_ptrs)
+    d._keep = (nb, ab)
+    d.node_blocks = ctypes.cast(nb, ctypes.POINTER(ctypes.c_void_p))
+    d.array_blocks = ctypes.cast(ab, ctypes.POINTER(ctypes.c_void_p))
+    d.n_node_blocks, d.n_array_blocks = len(node_block_ptrs), len(array_block_ptrs)
+    d.block_bytes, d.root_index = block_bytes, root_index
+    d.node_bytes_used, d.array_bytes_used = node_bytes_used, array_bytes_used
+    d.max_depth = max_depth
+    return d
+
+
+def world_desc_from_flat(nodes_u64, arrays_u32, node_bytes_used=None, array_bytes_used=None, *, block_bytes=1 << 22,
+                         max_depth=6):
+    """rc_world_desc over flat numpy pools (the SSBO view) by slicing them into blocks."""
+    nbytes, abytes = nodes_u64.nbytes, arrays_u32.nbytes
+    nptr, aptr = nodes_u64.ctypes.data, arrays_u32.ctypes.data
+    node_blocks = [nptr + o for o in range(0, max(nbytes, 1), block_bytes)]
+    array_blocks = [aptr + o for o in range(0, max(abytes, 1), block_bytes)]
+    d = make_world_desc(node_blocks, array_blocks,
+                        nbytes if node_bytes_used is None else node_bytes_used,
+                        abytes if array_bytes_used is None else array_bytes_used,
+                        block_bytes=block_bytes, max_depth=max_depth)
+    d._keep = d._keep + (nodes_u64, arrays_u32)
+    return d
+
+
+def default_proj_plane(width, height):
+    """projPlaneSize as render() computes it (src/main.cpp:94): double maths, passed as floats."""
+    t = math.tan(math.radians(45.0))
+    return (float(np.float32(t)), float(np.float32(t * float(np.float32(height)) / width)))
+
+
+def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
+                 ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
+                 render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None):
+    p = FrameParams()
+    p.origin[:] = [float(v) for v in origin]
+    p.camera_dir[:] = [float(v) for v in camera_dir]
+    p.sun_dir[:] = [float(v) for v in sun_dir]
+    flags = 0
+    if mouse_pos is not None:
+        p.mouse_pos[:] = [float(v) for v in mouse_pos]
+        flags |= RC_F_CROSSHAIR
+    if shadows:
+        flags |= RC_F_SHADOWS
+    if hits:
+        flags |= RC_F_HITS
+    if rgba32f:
+        flags |= RC_F_RGBA32F
+    pp = default_proj_plane(width, height) if proj_plane is None else proj_plane
+    p.proj_plane[:] = [float(pp[0]), float(pp[1])]
+    p.delta_time, p.ao_strength = delta_time, ao_strength
+    p.looking_at[:] = list(looking_at)
+    p.render_pos_data = render_pos_data
+    p.width, p.height = width, height
+    p.max_steps, p.shadow_steps = max_steps, shadow_steps
+    p.ao_samples, p.ao_steps = ao_samples, ao_steps
+    p.flags = flags
+    return p
+
+
+class RayCaster:
+    """The reference host's view of the library: init -> upload_world -> render_frame -> read_image."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        _check(self.lib, self.lib.rc_init(device))
+        self.device = device
+        self._last = None
+
+    def close(self):
+        if self.lib is not None:
+            self.lib.rc_shutdown()
+            self.lib = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def set_stream(self, cuda_stream):
+        _check(self.lib, self.lib.rc_set_stream(cuda_stream))
+
+    def set_shard(self, rank, world_size):
+        _check(self.lib, self.lib.rc_set_shard(rank, world_size))
+
+    def upload_world(self, desc):
+        _check(self.lib, self.lib.rc_upload_world(ctypes.byref(desc)))
+        return self.world_info()
+
+    def world_info(self):
+        info = WorldInfo()
+        _check(self.lib, self.lib.rc_world_info_get(ctypes.byref(info)))
+        return info
+
+    def render_frame(self, params):
+        _check(self.lib, self.lib.rc_render_frame(ctypes.byref(params)))
+        self._last = (params.width, params.height)
+
+    def sync(self):
+        _check(self.lib, self.lib.rc_sync())
+
+    def read_image(self, out=None, fmt=RC_RGBA8):
+        w, h = self._last
+        if out is None:
+            out = np.zeros((h, w, 4), dtype=np.uint8 if fmt == RC_RGBA8 else np.float32)
+        _check(self.lib, self.lib.rc_read_image(out.ctypes.data, out.nbytes, fmt))
+        return out
+
+    def read_hits(self, out=None):
+        w, h = self._last
+        if out is None:
+            out = np.zeros(w * h, dtype=HIT_DTYPE)
+        _check(self.lib, self.lib.rc_read_hits(out.ctypes.data, out.size))
+        return out
+
+    def stats(self):
+        s = FrameStats()
+        _check(self.lib, self.lib.rc_frame_stats_get(ctypes.byref(s)))
+        return s
+
+    def hemisphere_table(self, n):
+        out = np.zeros((n, 3), dtype=np.float32)
+        _check(self.lib, self.lib.rc_hemisphere_table(n, out.ctypes.data))
+        return out
+
+    def device_image_ptr(self, fmt=RC_RGBA8):
+        return self.lib.rc_device_image(fmt)
+
+    # ---- rc_debug.h ----
+    def lookup_device(self, xyz):
+        xyz = np.ascontiguousarray(xyz, dtype=np.int32).reshape(-1, 3)
+        words = np.zeros(len(xyz), dtype=np.uint32)
+        shifts = np.zeros(len(xyz), dtype=np.int32)
+        _check(self.lib, self.lib.rc_debug_lookup_device(xyz.ctypes.data, len(xyz), words.ctypes.data, shifts.ctypes.data))
+        return words, shifts
+
+    def detmath(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        s, e = np.zeros_like(x), np.zeros_like(x)
+        _check(self.lib, self.lib.rc_debug_detmath(x.ctypes.data, x.size, s.ctypes.data, e.ctypes.data))
+        return s, e
+
+
+def flatten_host(desc):
+    """CPU-only: the flattener half of rc_upload_world (no device needed)."""
+    lib = load_library()
+    info = WorldInfo()
+    _check(lib, lib.rc_debug_flatten_host(ctypes.byref(desc), ctypes.byref(info)))
+    return info
+
+
+def lookup_host(xyz, which=1):
+    """Packed-form lookups on the host copy. Returns (words, shifts, leaves[n,4] u32)."""
+    lib = load_library()
+    xyz = np.ascontiguousarray(xyz, dtype=np.int32).reshape(-1, 3)
+    words = np.zeros(len(xyz), dtype=np.uint32)
+    shifts = np.zeros(len(xyz), dtype=np.int32)
+    leaves = np.zeros((len(xyz), 4), dtype=np.uint32)
+    _check(lib, lib.rc_debug_lookup_host_batch(which, xyz.ctypes.data, len(xyz), words.ctypes.data, shifts.ctypes.data,
+                                               leaves.ctypes.data))
+    return words, shifts, leaves

@@ -1,0 +1,161 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle.
+
+Bar (BASELINE.json north_star): hit voxel, face, step counts, flags bit-exact;
+RGBA8 within 1/255 per channel (in practice identical: the deterministic sin/exp
+make the shading bit-exact too, which the tests report)."""
+import numpy as np
+import pytest
+
+from conftest import camera_dir
+
+pytestmark = pytest.mark.gpu
+
+HIT_FIELDS = ["x", "y", "z", "steps", "shadow_steps", "face", "kind", "flags", "ao_occluded"]
+
+
+def render_both(ob, rcmod, caster, oracle_world, w, h, pos, d, sun, **kw):
+    ao = kw.get("ao_samples", 0)
+    if ao:
+        tab = caster.hemisphere_table(ao)
+        ob.oracle_lib().oracle_set_hemisphere(ao, tab.ctypes.data)
+    okw = dict(kw)
+    fo = ob.make_frame(w, h, pos, d, sun, **okw)
+    ref = ob.render(oracle_world, fo, want_f32=True)
+    fp = rcmod.frame_params(w, h, pos, d, sun, hits=True, rgba32f=True, **kw)
+    caster.render_frame(fp)
+    got = {"rgba8": caster.read_image(), "rgba32f": caster.read_image(fmt=rcmod.RC_RGBA32F), "hits": caster.read_hits(),
+           "stats": caster.stats()}
+    return ref, got
+
+
+def assert_parity(ref, got, label=""):
+    for f in HIT_FIELDS:
+        a, b = ref["hits"][f], got["hits"][f]
+        if not np.array_equal(a, b):
+            bad = np.flatnonzero(a != b)
+            i = bad[0]
+            raise AssertionError(f"{label}: hit field {f} differs at {len(bad)} pixels; first idx {i}: "
+                                 f"oracle {ref['hits'][i]} cuda {got['hits'][i]}")
+    diff = np.abs(ref["rgba8"].astype(np.int16) - got["rgba8"].astype(np.int16))
+    assert diff.max() <= 1, f"{label}: RGBA8 differs by {diff.max()} (> 1/255) at {np.argwhere(diff > 1)[:4]}"
+    return int((diff != 0).sum())
+
+
+def test_config1_720p_primary_only(ob, rcmod, caster, oracle_world, defaults):
+    pos, d, sun = defaults
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 1280, 720, pos, d, sun, shadows=False)
+    n_off = assert_parity(ref, got, "config1")
+    c = ref["counters"]
+    st = got["stats"]
+    assert st.primary_rays == 1280 * 720 and st.shadow_rays == 0
+    assert st.primary_steps == c.dda_steps[0]
+    assert st.hit_pixels == c.kind_pixels[ob.KIND_HIT]
+    assert n_off == 0  # stronger than required: shading is bit-exact too
+    assert np.array_equal(ref["rgba32f"].view(np.uint32), got["rgba32f"].view(np.uint32))
+
+
+def test_config2_1080p_shadow(ob, rcmod, caster, oracle_world, defaults):
+    pos, d, sun = defaults
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 1920, 1080, pos, d, sun, shadows=True)
+    assert_parity(ref, got, "config2")
+    assert got["stats"].shadow_rays == ref["counters"].rays[1]
+    assert np.array_equal(ref["rgba8"], got["rgba8"])
+
+
+def test_config3_1080p_ao64(ob, rcmod, caster, oracle_world, defaults):
+    pos, d, sun = defaults
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 1920, 1080, pos, d, sun, shadows=True, ao_samples=64)
+    assert_parity(ref, got, "config3")
+    assert got["stats"].ao_rays == ref["counters"].rays[2]
+    assert np.array_equal(ref["rgba8"], got["rgba8"])
+
+
+CAMERAS = [
+    # (origin, yaw, pitch): views over the terrain, through the mirror / refractor test blocks,
+    # from inside water, across the torus seam; none looks into [768,1023]^3
+    ((35.0, 50.0, 35.0), 45.0, 0.0),
+    ((35.0, 50.0, 35.0), -135.0, 10.0),
+    ((100.5, 60.25, 100.5), 0.0, 60.0),
+    ((100.5, 60.25, 100.5), 180.0, 45.0),
+    ((100.5, 45.5, 100.5), 90.0, -30.0),
+    ((8.5, 101.5, 4.5), 15.0, 5.0),        # black 1^3 mirror at (10,100,10)
+    ((21.5, 13.5, 195.5), 0.0, 20.0),      # 4^3 refractor at (20..23,8..11,200..203)
+    ((150.3, 30.7, 20.1), -60.0, 25.0),
+    ((2.5, 40.5, 2.5), -135.0, 20.0),      # leaves the world over the seam (wraps to 1023)
+    ((199.5, 35.5, 199.5), 45.0, -10.0),
+    ((60.2, 25.9, 140.8), 120.0, 35.0),
+    ((35.0, 50.0, 35.0), 45.0, -89.0),
+    ((35.0, 50.0, 35.0), 45.0, 89.0),
+]
+
+
+@pytest.mark.parametrize("cam", range(len(CAMERAS)))
+def test_camera_sweep(ob, rcmod, caster, oracle_world, defaults, cam):
+    origin, yaw, pitch = CAMERAS[cam]
+    _, _, sun = defaults
+    d = camera_dir(yaw, pitch)
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 640, 360, origin, d, sun, shadows=True, ao_samples=20,
+                           delta_time=1.25, mouse_pos=(320.0, 180.0))
+    assert_parity(ref, got, f"camera {cam}")
+
+
+def test_looking_at_highlight_and_debug_modes(ob, rcmod, caster, oracle_world, defaults, ref_world):
+    pos, d, sun = defaults
+    # the block under a pixel a little below the screen centre (the host would pass castRayFromCam(30).pos)
+    probe = ob.render(oracle_world, ob.make_frame(320, 200, pos, d, sun))["hits"][60 * 320 + 160]
+    assert probe["kind"] == ob.KIND_HIT
+    look = (int(probe["x"]), int(probe["y"]), int(probe["z"]))
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 320, 200, pos, d, sun, looking_at=look)
+    assert_parity(ref, got, "highlight")
+    assert (got["hits"]["kind"] == ob.KIND_HIGHLIGHT).sum() > 0
+    # and the voxel the reference's own CPU picker reports (src/main.cpp:81,89), hit or miss
+    look, _, _ = ref_world.pick(pos, d, 30)
+    ref, got = render_both(ob, rcmod, caster, oracle_world, 320, 200, pos, d, sun, looking_at=tuple(int(v) for v in look))
+    assert_parity(ref, got, "highlight(castRayFromCam)")
+    for mode in (1, 2):
+        ref, got = render_both(ob, rcmod, caster, oracle_world, 320, 200, pos, d, sun, render_pos_data=mode)
+        assert_parity(ref, got, f"debug mode {mode}")
+        assert np.array_equal(ref["rgba32f"].view(np.uint32), got["rgba32f"].view(np.uint32))
+
+
+def test_ragged_resolutions(ob, rcmod, caster, oracle_world, defaults):
+    pos, d, sun = defaults
+    for (w, h) in [(1, 1), (7, 3), (33, 17), (130, 75), (257, 129)]:
+        ref, got = render_both(ob, rcmod, caster, oracle_world, w, h, pos, d, sun, shadows=True, ao_samples=8)
+        assert_parity(ref, got, f"{w}x{h}")
+
+
+def test_step_limits(ob, rcmod, caster, oracle_world, defaults):
+    pos, d, sun = defaults
+    for (ms, ss, aos) in [(0, 0, 0), (1, 1, 1), (17, 3, 2), (300, 75, 32), (1000, 200, 9)]:
+        ref, got = render_both(ob, rcmod, caster, oracle_world, 200, 120, pos, d, sun, max_steps=ms, shadow_steps=ss,
+                               ao_samples=16, ao_steps=aos)
+        assert_parity(ref, got, f"limits {ms}/{ss}/{aos}")
+
+
+def test_device_lookup_matches_reference_getblock(ob, rcmod, caster, ref_world):
+    rng = np.random.default_rng(7)
+    xyz = np.concatenate([
+        rng.integers(0, 256, size=(200000, 3)),
+        rng.integers(0, 768, size=(50000, 3)),
+        np.array([[35, 20, 35], [10, 100, 10], [21, 9, 201], [24, 9, 201], [35, 50, 35]]),
+    ]).astype(np.int32)
+    words, _ = caster.lookup_device(xyz)
+    refb = ref_world.get_blocks(xyz)
+    solid = words != 0
+    assert np.array_equal(solid, refb[:, 0] != np.uint64(0xFFFFFFFFFFFFFFFF))
+    hw, _, leaves = rcmod.lookup_host(xyz, which=0)
+    assert np.array_equal(hw, words)
+    leaf = leaves.view(np.uint64).reshape(-1, 2)
+    assert np.array_equal(leaf[solid], refb[solid])
+
+
+def test_device_detmath_matches_oracle(ob, caster):
+    L = ob.oracle_lib()
+    x = np.concatenate([np.linspace(-100, 100, 20001), np.linspace(-3000, 3000, 20001),
+                        np.array([0.0, -0.0, 1e-30, 88.5, -87.5, 1e7, np.inf, -np.inf])]).astype(np.float32)
+    s, e = caster.detmath(x)
+    so = np.array([L.oracle_sinf(float(v)) for v in x], dtype=np.float32)
+    eo = np.array([L.oracle_expf(float(v)) for v in x], dtype=np.float32)
+    assert np.array_equal(s.view(np.uint32), so.view(np.uint32))
+    assert np.array_equal(e.view(np.uint32), eo.view(np.uint32))
