@@ -56,6 +56,7 @@ class OracleFrame(ctypes.Structure):
         ("ao_samples", ctypes.c_uint32), ("ao_steps", ctypes.c_uint32),
         ("flags", ctypes.c_uint32), ("row_begin", ctypes.c_uint32), ("row_end", ctypes.c_uint32),
         ("threads", ctypes.c_int32),
+        ("band_rows", ctypes.c_uint32), ("band_stride", ctypes.c_uint32), ("band_offset", ctypes.c_uint32),
     ]
 
 
@@ -209,7 +210,8 @@ def make_world(nodes, arrays, max_depth=6):
 
 def make_frame(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
                ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
-               render_pos_data=0, max_steps=300, shadow_steps=75, rows=None, threads=0, proj_plane=None):
+               render_pos_data=0, max_steps=300, shadow_steps=75, rows=None, threads=0, proj_plane=None,
+               bands=None):
     f = OracleFrame()
     f.origin[:] = [float(v) for v in origin]
     f.camera_dir[:] = [float(v) for v in camera_dir]
@@ -233,6 +235,8 @@ def make_frame(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_s
     f.flags = flags
     f.row_begin, f.row_end = (0, height) if rows is None else rows
     f.threads = threads
+    if bands is not None:  # (band_rows, stride, offset)
+        f.band_rows, f.band_stride, f.band_offset = bands
     return f
 
 

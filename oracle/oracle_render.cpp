@@ -628,6 +628,9 @@ int oracle_render(const OracleWorld* world, const OracleFrame* frame, OracleHit*
 #pragma omp for schedule(dynamic, 2)
 #endif
         for (int64_t py = (int64_t)y0; py < (int64_t)y1; py++) {
+            if (frame->band_stride > 1 && frame->band_rows > 0 &&
+                ((u32)py / frame->band_rows) % frame->band_stride != frame->band_offset)
+                continue;
             for (u32 px = 0; px < frame->width; px++) {
                 Pixel P;
                 P.w = world;

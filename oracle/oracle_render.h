@@ -53,6 +53,9 @@ typedef struct OracleFrame {
     uint32_t flags;         /* ORACLE_F_* */
     uint32_t row_begin, row_end; /* rows [row_begin,row_end) are rendered (bounded samples) */
     int32_t threads;        /* OpenMP threads, <=0: all */
+    uint32_t band_rows;     /* with band_stride > 1: only rows with (row / band_rows) % band_stride == band_offset */
+    uint32_t band_stride;   /* 0 or 1: every row (multi-GPU band sharding / bounded CPU samples) */
+    uint32_t band_offset;
 } OracleFrame;
 
 #define ORACLE_F_CROSSHAIR 1u  /* evaluate the crosshair test (low_res.frag:259-262) */
