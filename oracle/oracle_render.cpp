@@ -122,8 +122,20 @@ float detExp(float x) {
 // Only the low 2*(max_depth-1) bits of each coordinate survive => torus.
 // ---------------------------------------------------------------------------
 inline u64 spreadAxis(int v, int groups) {
-    u64 n = 0;
     u32 u = (u32)v;
+    if (groups == 5) {
+        // the reference's literal bit spread (low_res.frag:454-459, main.cpp:48-51). Its first mask
+        // 0x030000FF also keeps bits 24-25 of the RAW value, so for a negative coordinate (two's
+        // complement: those bits are 1) the top group reads 3 whatever bits 8-9 are: x < 0 maps to
+        // 768 | (x & 255), not to x & 1023.  Non-negative coordinates below 2^24 wrap modulo 1024.
+        u32 n = u;
+        n = (n | (n << 16)) & 0x030000FFu;
+        n = (n | (n << 8)) & 0x0300F00Fu;
+        n = (n | (n << 4)) & 0x030C30C3u;
+        return n;
+    }
+    // declared extension (max_depth != 6): plain torus of 2*(max_depth-1) bits per axis
+    u64 n = 0;
     for (int g = 0; g < groups; g++) n |= (u64)((u >> (2 * g)) & 3u) << (6 * g);
     return n;
 }

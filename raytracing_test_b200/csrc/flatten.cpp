@@ -229,7 +229,12 @@ int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err)
 uint32_t packed_lookup(const PackedWorld& w, int32_t x, int32_t y, int32_t z, int* cell_shift) {
     const int D = (int)w.max_depth;
     const uint32_t wrap = (1u << (2 * (D - 1))) - 1;
-    const uint32_t ux = (uint32_t)x & wrap, uy = (uint32_t)y & wrap, uz = (uint32_t)z & wrap;
+    // max_depth 6: bits 24-25 of the raw coordinate leak into bits 8-9, as in the reference's bit
+    // spread (low_res.frag:454-459; see kernels.cu wrap_coord)
+    const uint32_t leak = D == 6 ? 0x300u : 0u;
+    const uint32_t ux = ((uint32_t)x & wrap) | (((uint32_t)x >> 16) & leak);
+    const uint32_t uy = ((uint32_t)y & wrap) | (((uint32_t)y >> 16) & leak);
+    const uint32_t uz = ((uint32_t)z & wrap) | (((uint32_t)z >> 16) & leak);
     int shift = 2 * (D - 2);
     const PackedNode* n = &w.nodes[0];
     for (;;) {

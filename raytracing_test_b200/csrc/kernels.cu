@@ -127,10 +127,20 @@ __device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c) {
     c.lx = c.ly = c.lz = 0;
 }
 
+// Voxel coordinate -> tree coordinate. The reference spreads a coordinate into its Morton code with
+// n = (n | n << 16) & 0x030000FF ... (low_res.frag:454-459): bits 0-9 survive (a 1024-torus), and
+// bits 24-25 of the RAW value are OR-ed onto bits 8-9, so a negative coordinate lands in
+// 768 | (x & 255).  W.leak = 0x300 reproduces that for max_depth 6; deeper trees (extension) use a
+// plain torus (leak 0).  The low 8 bits are never touched, so aligned cells up to the root's
+// children (256^3) keep their extent in raw coordinates and the countdown of count_cell holds.
+__device__ __forceinline__ int wrap_coord(const DeviceWorld& W, int v) {
+    return (v & (int)W.wrap) | ((int)((unsigned)v >> 16) & (int)W.leak);
+}
+
 // Material word of voxel (x,y,z) (0 = empty) and the shift of the uniform cell it
 // lies in. Equivalent of getBlock (low_res.frag:493-532) on the packed form.
 __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int x, int y, int z, int& cellShift) {
-    const int wx = x & (int)W.wrap, wy = y & (int)W.wrap, wz = z & (int)W.wrap;
+    const int wx = wrap_coord(W, x), wy = wrap_coord(W, y), wz = wrap_coord(W, z);
     if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
         uint4 n = __ldg(&W.nodes[0]);
         c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);

@@ -21,6 +21,7 @@ struct DeviceWorld {
     uint32_t n_top;          // BFS prefix staged in shared memory by the persistent kernel
     int root_shift;          // cell shift of the root's children: 2*(max_depth-2)
     uint32_t wrap;           // (1 << 2*(max_depth-1)) - 1
+    uint32_t leak;           // 0x300 for max_depth 6 (the reference's Morton-spread quirk), else 0
 };
 
 // Per-hit-pixel record handed from the primary kernel to the AO kernel.

@@ -238,6 +238,7 @@ int rc_upload_world(const rc_world_desc* desc) {
     g.world.n_top = 0;
     g.world.root_shift = 2 * ((int)pw.max_depth - 2);
     g.world.wrap = (1u << (2 * (pw.max_depth - 1))) - 1u;
+    g.world.leak = pw.max_depth == 6 ? 0x300u : 0u;
 
     memset(&g.info, 0, sizeof(g.info));
     g.info.ref_nodes = pw.ref_nodes;

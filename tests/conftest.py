@@ -84,3 +84,26 @@ def camera_dir(yaw_deg, pitch_deg):
     c, s = f(np.cos(y)), f(np.sin(y))
     v = np.array([f(f(v[0] * c) + f(v[2] * s)), v[1], f(f(-v[0] * s) + f(v[2] * c))], dtype=np.float32)  # rotateY
     return norm(v)
+
+
+# (origin, yaw, pitch) poses for parity sweeps; what each one exercises was checked with the
+# oracle (kinds / reflected / refracted / shadowed pixel counts).  None looks into
+# [768,1023]^3.
+CAMERAS = [
+    ((35.0, 50.0, 35.0), 45.0, 0.0),        # the default view
+    ((35.0, 50.0, 35.0), -135.0, 10.0),     # away from the terrain: all sky, 300 steps, wraps the torus
+    ((100.5, 60.25, 100.5), 0.0, 60.0),     # steep look down: short rays, most cast shadow rays
+    ((100.5, 60.25, 100.5), 180.0, 45.0),
+    ((100.5, 45.5, 100.5), 90.0, -30.0),
+    ((8.5, 101.5, 4.5), 15.0, 5.0),         # black 1^3 mirror at (10,100,10): ~6 % reflected pixels
+    ((21.5, 12.5, 210.5), 180.0, 10.0),     # 4^3 refractor at (20..23,8..11,200..203) in front of the terrain edge
+    ((150.5, 30.5, 140.5), 45.0, 45.0),     # down onto the lake: every ray refracts through animated water
+    ((162.5, 19.5, 128.5), 30.0, -20.0),    # camera INSIDE water (10 deep) looking up: starts with n = 1.1
+    ((162.5, 19.5, 128.5), 30.0, 30.0),     # camera inside water looking at the lake bed
+    ((-20.5, 45.5, -20.5), 45.0, 10.0),     # starts at negative coordinates (= 1003 on the torus), enters the world
+    ((2.5, 40.5, 2.5), -135.0, 20.0),       # leaves the world over the seam
+    ((199.5, 35.5, 199.5), 45.0, -10.0),
+    ((60.2, 25.9, 140.8), 120.0, 35.0),
+    ((35.0, 50.0, 35.0), 45.0, -89.0),      # near-vertical rays: huge deltas on two axes
+    ((35.0, 50.0, 35.0), 45.0, 89.0),
+]

@@ -6,7 +6,7 @@ make the shading bit-exact too, which the tests report)."""
 import numpy as np
 import pytest
 
-from conftest import camera_dir
+from conftest import CAMERAS, camera_dir
 
 pytestmark = pytest.mark.gpu
 
@@ -70,23 +70,6 @@ def test_config3_1080p_ao64(ob, rcmod, caster, oracle_world, defaults):
     assert np.array_equal(ref["rgba8"], got["rgba8"])
 
 
-CAMERAS = [
-    # (origin, yaw, pitch): views over the terrain, through the mirror / refractor test blocks,
-    # from inside water, across the torus seam; none looks into [768,1023]^3
-    ((35.0, 50.0, 35.0), 45.0, 0.0),
-    ((35.0, 50.0, 35.0), -135.0, 10.0),
-    ((100.5, 60.25, 100.5), 0.0, 60.0),
-    ((100.5, 60.25, 100.5), 180.0, 45.0),
-    ((100.5, 45.5, 100.5), 90.0, -30.0),
-    ((8.5, 101.5, 4.5), 15.0, 5.0),        # black 1^3 mirror at (10,100,10)
-    ((21.5, 13.5, 195.5), 0.0, 20.0),      # 4^3 refractor at (20..23,8..11,200..203)
-    ((150.3, 30.7, 20.1), -60.0, 25.0),
-    ((2.5, 40.5, 2.5), -135.0, 20.0),      # leaves the world over the seam (wraps to 1023)
-    ((199.5, 35.5, 199.5), 45.0, -10.0),
-    ((60.2, 25.9, 140.8), 120.0, 35.0),
-    ((35.0, 50.0, 35.0), 45.0, -89.0),
-    ((35.0, 50.0, 35.0), 45.0, 89.0),
-]
 
 
 @pytest.mark.parametrize("cam", range(len(CAMERAS)))
