@@ -36,6 +36,10 @@ int rc_debug_palette(uint32_t word, uint32_t* out_leaf);
 /* Device det_sin / det_exp (DESIGN.md "deterministic transcendentals"). Host pointers. */
 int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp);
 
+/* sizeof of the ABI structs as the library was compiled: rc_world_desc, rc_world_info,
+ * rc_frame_params, rc_hit, rc_frame_stats (bindings check their layouts against it). */
+int rc_debug_struct_sizes(uint32_t out[5]);
+
 #ifdef __cplusplus
 }
 #endif

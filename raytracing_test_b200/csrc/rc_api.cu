@@ -511,6 +511,16 @@ int rc_debug_flatten_host(const rc_world_desc* desc, rc_world_info* info) {
     return RC_OK;
 }
 
+int rc_debug_struct_sizes(uint32_t out[5]) {
+    if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_struct_sizes: null out");
+    out[0] = (uint32_t)sizeof(rc_world_desc);
+    out[1] = (uint32_t)sizeof(rc_world_info);
+    out[2] = (uint32_t)sizeof(rc_frame_params);
+    out[3] = (uint32_t)sizeof(rc_hit);
+    out[4] = (uint32_t)sizeof(rc_frame_stats);
+    return RC_OK;
+}
+
 // Device det_sin / det_exp over n floats (host pointers).
 int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_detmath: call rc_init first");

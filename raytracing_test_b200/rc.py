@@ -110,6 +110,7 @@ ABI = {
                                                    ctypes.c_void_p, ctypes.c_void_p]),
     "rc_debug_lookup_device": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
     "rc_debug_palette": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_debug_struct_sizes": (ctypes.c_int, [ctypes.c_void_p]),
     "rc_debug_detmath": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
 }
 
