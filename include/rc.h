@@ -167,6 +167,19 @@ int rc_set_stream(void* cuda_stream);
  * the others untouched.  (0,1) = whole frame. */
 int rc_set_shard(uint32_t rank, uint32_t world_size);
 
+/* Layout of a sharded frame: how many rows this rank renders (local_rows, bands of 16 rows dealt
+ * round-robin, the last band of the frame may be partial) and how many rows every rank's buffers
+ * hold (padded_rows = the largest per-rank count rounded up to whole bands; equal on all ranks so a
+ * gather can use equal-size messages). Needs no device. */
+int rc_shard_layout(uint32_t height, uint32_t rank, uint32_t world_size, uint32_t* local_rows, uint32_t* padded_rows);
+
+/* After a gather of every rank's rc_device_image / rc_device_hits (rank-major, world_size buffers
+ * of padded_rows * width elements, DEVICE memory): de-interleave the bands into the bottom-up
+ * frame at dst (DEVICE memory, width * height elements). bytes_per_element: 4 (RC_RGBA8),
+ * 16 (RC_RGBA32F) or 20 (rc_hit). One kernel on the library's stream. */
+int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t world_size,
+                     uint32_t bytes_per_element);
+
 /* ---- world upload -------------------------------------------------------------
  * Replaces initVoxelDataAllocator()+updateSsboData()
  * (src/voxel_data/voxel_allocator.hpp:38-91; called at src/main.cpp:182,212).

@@ -759,6 +759,23 @@ __global__ void __launch_bounds__(128) ao_kernel(const __grid_constant__ FrameAr
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
 }
 
+// Frame composition after the NCCL gather: row y of the frame lives in rank (y/16) % world,
+// local row ((y/16) / world) * 16 + y % 16. One thread per 16-byte (or 4-byte) word of the frame:
+// coalesced reads of whole rows, coalesced writes.
+template <typename WordT>
+__global__ void __launch_bounds__(256) compose_kernel(const WordT* __restrict__ gathered, WordT* __restrict__ dst,
+                                                      uint32_t wordsPerRow, uint32_t height, uint32_t worldSize,
+                                                      uint32_t paddedRows) {
+    const uint64_t total = (uint64_t)wordsPerRow * height;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t y = (uint32_t)(i / wordsPerRow), xw = (uint32_t)(i % wordsPerRow);
+        const uint32_t band = y / BAND_ROWS;
+        const uint32_t rank = band % worldSize;
+        const uint32_t srcRow = (band / worldSize) * BAND_ROWS + (y % BAND_ROWS);
+        dst[i] = gathered[((uint64_t)rank * paddedRows + srcRow) * wordsPerRow + xw];
+    }
+}
+
 __global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -797,6 +814,23 @@ cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
 cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
     if (maxSeeds == 0) return cudaSuccess;
     ao_kernel<<<(maxSeeds + 127u) / 128u, 128, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t worldSize,
+                           uint32_t paddedRows, uint32_t bytesPerElement, cudaStream_t stream) {
+    const uint64_t rowBytes = (uint64_t)width * bytesPerElement;
+    if (rowBytes == 0 || height == 0) return cudaSuccess;
+    const bool wide = rowBytes % 16 == 0 && ((uintptr_t)gathered % 16 == 0) && ((uintptr_t)dst % 16 == 0);
+    const uint64_t words = rowBytes / (wide ? 16 : 4) * height;
+    uint64_t blocks = (words + 255) / 256;
+    if (blocks > 148ull * 32) blocks = 148ull * 32;  // grid-stride: 32 CTAs of 256 threads per SM
+    if (wide)
+        compose_kernel<uint4><<<(unsigned)blocks, 256, 0, stream>>>((const uint4*)gathered, (uint4*)dst,
+                                                                    (uint32_t)(rowBytes / 16), height, worldSize, paddedRows);
+    else
+        compose_kernel<uint32_t><<<(unsigned)blocks, 256, 0, stream>>>((const uint32_t*)gathered, (uint32_t*)dst,
+                                                                       (uint32_t)(rowBytes / 4), height, worldSize, paddedRows);
     return cudaGetLastError();
 }
 

@@ -66,6 +66,10 @@ cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream);
 // AO kernel over the seeds appended by the primary kernel.
 cudaError_t launch_ao(const FrameArgs& args, uint32_t max_seeds, cudaStream_t stream);
 
+// De-interleave gathered per-rank band buffers into a bottom-up frame (see rc_compose_frame).
+cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t world_size,
+                           uint32_t padded_rows, uint32_t bytes_per_element, cudaStream_t stream);
+
 // Single-voxel lookups through the same device code path the kernels use (tests).
 cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,
                           cudaStream_t stream);

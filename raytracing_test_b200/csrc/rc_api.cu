@@ -202,6 +202,41 @@ int rc_set_shard(uint32_t rank, uint32_t world_size) {
     return RC_OK;
 }
 
+static void shardLayout(uint32_t height, uint32_t rank, uint32_t worldSize, uint32_t* localBands, uint32_t* paddedBands) {
+    const uint32_t totalBands = (height + BAND_ROWS - 1) / BAND_ROWS;
+    *localBands = totalBands > rank ? (totalBands - rank + worldSize - 1) / worldSize : 0;
+    *paddedBands = (totalBands + worldSize - 1) / worldSize;
+}
+
+int rc_shard_layout(uint32_t height, uint32_t rank, uint32_t world_size, uint32_t* local_rows, uint32_t* padded_rows) {
+    if (world_size == 0 || rank >= world_size || height == 0)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_shard_layout: height %u, rank %u of %u", height, rank, world_size);
+    uint32_t lb, pb;
+    shardLayout(height, rank, world_size, &lb, &pb);
+    // rows really rendered: the frame's last band may be partial
+    uint32_t rows = 0;
+    for (uint32_t b = 0; b < lb; b++) {
+        const uint32_t row0 = (b * world_size + rank) * BAND_ROWS;
+        rows += row0 + BAND_ROWS <= height ? BAND_ROWS : height - row0;
+    }
+    if (local_rows) *local_rows = rows;
+    if (padded_rows) *padded_rows = pb * BAND_ROWS;
+    return RC_OK;
+}
+
+int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t world_size,
+                     uint32_t bytes_per_element) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_compose_frame: call rc_init first");
+    if (!gathered || !dst || width == 0 || height == 0 || world_size == 0 || bytes_per_element == 0 ||
+        bytes_per_element % 4 != 0)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_compose_frame: bad arguments");
+    uint32_t lb, pb;
+    shardLayout(height, 0, world_size, &lb, &pb);
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(launch_compose(gathered, dst, width, height, world_size, pb * BAND_ROWS, bytes_per_element, g.stream));
+    return RC_OK;
+}
+
 int rc_upload_world(const rc_world_desc* desc) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_upload_world: call rc_init first");
     if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_upload_world: null desc");
@@ -278,10 +313,11 @@ int rc_render_frame(const rc_frame_params* params) {
     CUDA_TRY(cudaSetDevice(g.device));
 
     // rows owned by this rank: bands b with b % world == rank
-    const uint32_t totalBands = (p.height + BAND_ROWS - 1) / BAND_ROWS;
-    const uint32_t localBands = totalBands > g.rank ? (totalBands - g.rank + g.worldSize - 1) / g.worldSize : 0;
+    uint32_t localBands, paddedBands;
+    shardLayout(p.height, g.rank, g.worldSize, &localBands, &paddedBands);
     const uint32_t localRows = localBands * BAND_ROWS;
-    const size_t pixels = (size_t)(localRows ? localRows : 1) * p.width;
+    // every rank's buffers hold paddedBands bands, so the frame gather can use equal-size messages
+    const size_t pixels = (size_t)paddedBands * BAND_ROWS * p.width;
 
     int rcode;
     if ((rcode = growBuffer(g.dRgba8, g.pixelCapacity, pixels)) != RC_OK) return rcode;
@@ -320,7 +356,7 @@ int rc_render_frame(const rc_frame_params* params) {
     g.launches++;
     CUDA_TRY(cudaEventRecord(g.evPrimary, g.stream));
     if (p.ao_samples > 0 && localRows > 0) {
-        CUDA_TRY(launch_ao(a, (uint32_t)pixels, g.stream));
+        CUDA_TRY(launch_ao(a, (uint32_t)((size_t)localRows * p.width), g.stream));
         g.launches++;
     }
     CUDA_TRY(cudaEventRecord(g.evEnd, g.stream));

@@ -92,6 +92,9 @@ ABI = {
     "rc_abi_version": (ctypes.c_int, []),
     "rc_set_stream": (ctypes.c_int, [ctypes.c_void_p]),
     "rc_set_shard": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32]),
+    "rc_shard_layout": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
+    "rc_compose_frame": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32,
+                                         ctypes.c_uint32]),
     "rc_upload_world": (ctypes.c_int, [ctypes.POINTER(WorldDesc)]),
     "rc_world_info_get": (ctypes.c_int, [ctypes.POINTER(WorldInfo)]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
@@ -275,6 +278,12 @@ class RayCaster:
     def device_image_ptr(self, fmt=RC_RGBA8):
         return self.lib.rc_device_image(fmt)
 
+    def device_hits_ptr(self):
+        return self.lib.rc_device_hits()
+
+    def compose_frame(self, gathered_ptr, dst_ptr, width, height, world_size, bytes_per_element=4):
+        _check(self.lib, self.lib.rc_compose_frame(gathered_ptr, dst_ptr, width, height, world_size, bytes_per_element))
+
     # ---- rc_debug.h ----
     def lookup_device(self, xyz):
         xyz = np.ascontiguousarray(xyz, dtype=np.int32).reshape(-1, 3)
@@ -288,6 +297,24 @@ class RayCaster:
         s, e = np.zeros_like(x), np.zeros_like(x)
         _check(self.lib, self.lib.rc_debug_detmath(x.ctypes.data, x.size, s.ctypes.data, e.ctypes.data))
         return s, e
+
+
+def shard_layout(height, rank, world_size):
+    """(rows this rank renders, rows every rank's buffers hold) for a frame sharded in 16-row bands."""
+    lib = load_library()
+    a, b = ctypes.c_uint32(), ctypes.c_uint32()
+    _check(lib, lib.rc_shard_layout(height, rank, world_size, ctypes.byref(a), ctypes.byref(b)))
+    return a.value, b.value
+
+
+def band_rows_of_rank(height, rank, world_size):
+    """Global row indices a rank renders, in the order its compact buffers store them."""
+    rows = []
+    band = rank
+    while band * BAND_ROWS < height:
+        rows.extend(range(band * BAND_ROWS, min((band + 1) * BAND_ROWS, height)))
+        band += world_size
+    return rows
 
 
 def flatten_host(desc):
