@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 voxel ray caster (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+A "step" is one frame: rc_render_frame over one batch of W x H synthetic camera rays through the
+default generated world (initTetraHexaTree + genWorld: seeds 42/64/100, 200 x 200 columns).
+  N = 1 : BASELINE.json configs[2] -- 1920x1080, primary + sun shadow + 64-sample hemisphere AO
+          (the configuration `metric` is quoted on).
+  N > 1 : BASELINE.json configs[4] -- 7680x4320, same passes, 16-row bands dealt round-robin to the
+          ranks, NCCL gather of the finished RGBA8 bands to rank 0 + one compose kernel; strong scaling.
+One JSON line on stdout (rank 0). `value` = rays cast by all ranks / device time (max over ranks) with
+everything resident in HBM; `e2e` = the same through the C-ABI with the frame read back into pinned
+host memory every step (rc_render_frame + rc_read_image).
+`--impl reference` times the reference algorithm's CPU restatement (oracle/, all host threads) on a
+bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (primary+AO) at 1920x1080 per B200"
+UNIT = "Mrays/s"
+
+WORKLOADS = {
+    # name: (width, height, shadows, ao_samples, golden case holding the oracle's algorithmic byte counts)
+    "config1_720p_primary": (1280, 720, False, 0, "config1_720p_primary"),
+    "config2_1080p_shadow": (1920, 1080, True, 0, "config2_1080p_shadow"),
+    "config3_1080p_ao64": (1920, 1080, True, 64, "config3_1080p_ao64"),
+    "config4_4k_ao64_world2048": (3840, 2160, True, 64, "config4_4k_ao64_world2048"),
+    "config5_8k_ao64": (7680, 4320, True, 64, "config5_8k_ao64"),
+}
+HBM_FALLBACK_GBS = 6650.0  # B200_PROFILING.md, used only when MEASURED_PEAKS.json is absent
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
+    return ap.parse_args()
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md)"
+
+
+def golden_counters(case):
+    """Algorithmic bytes of the reference algorithm for exactly this frame, counted by the oracle when
+    tests/golden was generated (tools/make_golden.py): 16 B per nodes[] read + 4 B per child-index read."""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "frames.json")) as f:
+            return json.load(f)["cases"][case]["counters"]
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the benchmark runs (B200_PROFILING.md clocks line)."""
+
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,utilization.gpu,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        time.sleep(0.06)
+        self.proc.terminate()
+        rows = [r for (t, r) in self.rows if len(r) >= 9 and (t0 is None or t0 - 0.05 <= t <= t1 + 0.05)]
+        if not rows:
+            rows = [r for (_, r) in self.rows if len(r) >= 9]
+        sm = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        busy = [float(r[1]) for r in rows if r[4].isdigit() and int(r[4]) > 0 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[5 + i].lower().startswith("active") for r in rows)]
+        return {
+            "sm_mhz": float(np.median(busy if busy else sm)) if sm else None,
+            "sm_max_mhz": float(rows[0][2]) if rows and rows[0][2].replace(".", "").isdigit() else None,
+            "power_w_max": max((float(r[3]) for r in rows if r[3].replace(".", "").isdigit()), default=None),
+            "reasons": reasons, "samples": len(rows),
+        }
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference algorithm restated on the CPU (oracle/), used ONLY as a timed baseline
+# ---------------------------------------------------------------------------------------------
+def build_host_world(workload):
+    """The synthetic world, in the reference's pool wire format, from the host stand-in."""
+    from raytracing_test_b200 import voxel_host as vh
+
+    if workload.startswith("config4"):
+        return vh.World.default(width=2048, length=2048, max_depth=7), 7
+    return vh.World.default(), 6
+
+
+def cpu_render_sample(workload, stride, threads=0, world_cache={}):
+    """One bounded sample of the workload on the host cores: every stride-th 16-row band of the frame,
+    all passes. Returns (rays, seconds, algorithmic bytes by phase)."""
+    from oracle import bindings as ob  # the checker, timed here as the CPU baseline only
+    from raytracing_test_b200 import voxel_host as vh
+
+    w, h, shadows, ao, _ = WORKLOADS[workload]
+    if workload not in world_cache:
+        host, depth = build_host_world(workload)
+        nodes, arrays = host.pools()
+        world_cache[workload] = (ob.make_world(nodes, arrays, depth), nodes, arrays)
+        if ao:
+            tab = np.zeros((ao, 3), dtype=np.float32)
+            ob.oracle_lib().oracle_hemisphere(ao, tab.ctypes.data)
+            ob.oracle_lib().oracle_set_hemisphere(ao, tab.ctypes.data)
+    ow = world_cache[workload][0]
+    pos, d, sun = vh.default_camera()
+    frame = ob.make_frame(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, threads=threads,
+                          bands=(16, stride, 0) if stride > 1 else None)
+    t = time.perf_counter()
+    r = ob.render(ow, frame, want_hits=False, want_rgba8=True)
+    dt = time.perf_counter() - t
+    c = r["counters"]
+    return int(sum(c.rays)), dt, c.as_dict()["algorithmic_bytes"]
+
+
+def run_reference_arm(args, workload):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w, h, shadows, ao, _ = WORKLOADS[workload]
+    cores = os.cpu_count() or 1
+    stride = max(1, (w * h) // (1920 * 1080) * 8)
+    # keep the whole run within a few minutes whatever K is
+    rays, dt, _ = cpu_render_sample(workload, stride)
+    while dt * (args.steps + args.warmup) > 150.0 and stride < 64:
+        stride *= 2
+        rays, dt, _ = cpu_render_sample(workload, stride)
+    for _ in range(max(0, args.warmup - 1)):
+        cpu_render_sample(workload, stride)
+    total_rays, total_s = 0, 0.0
+    for _ in range(args.steps):
+        rays, dt, _ = cpu_render_sample(workload, stride)
+        total_rays += rays
+        total_s += dt
+    value = total_rays / total_s / 1e6
+    sample = f"every {stride}th 16-row band of the {w}x{h} frame per step ({rays} rays/step), all passes, OpenMP x{cores}"
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao,
+                   "world": "default generated world (seeds 42/64/100, 200x200)", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference renders frames only in GLSL (unavailable on this box); this is its traversal restated in "
+                "C++ (oracle/oracle_render.cpp, IEEE fp32) on all host threads",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_leg(workload):
+    """cpu_baseline object of the default arm: about 10-30 s of CPU work on rank 0."""
+    w, h, shadows, ao, _ = WORKLOADS[workload]
+    cores = os.cpu_count() or 1
+    stride = max(1, (w * h) // (1920 * 1080))
+    cpu_render_sample(workload, 64)  # builds the world, warms the caches
+    best, spent, reps, rays = None, 0.0, 0, 0
+    while reps < 5 and (spent < 10.0 or reps < 2):
+        rays, dt, _ = cpu_render_sample(workload, stride)
+        best = dt if best is None else min(best, dt)
+        spent += dt
+        reps += 1
+    one_rays, one_dt, _ = cpu_render_sample(workload, max(stride, 4), threads=1)
+    return {
+        "value": rays / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": f"{'whole' if stride == 1 else f'every {stride}th 16-row band of the'} {w}x{h} frame, all passes, "
+                  f"best of {reps} ({best * 1e3:.0f} ms), OpenMP x{cores}",
+        "frame_ms": best * 1e3 * stride, "single_thread_value": one_rays / one_dt / 1e6,
+    }
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200_arm(args, workload):
+    import torch
+    import torch.distributed as dist
+
+    from raytracing_test_b200 import frame_gather as fg
+    from raytracing_test_b200 import rc, voxel_host as vh
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    if world_size != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world_size}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; librc has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    w, h, shadows, ao, golden_case = WORKLOADS[workload]
+    host, depth = build_host_world(workload)
+    pos, d, sun = vh.default_camera()
+    look, _, _ = host.pick(pos, d, 30)  # src/main.cpp:81: the host's picking ray feeds lookingAtBlock
+
+    sc = fg.ShardedRayCaster(local_rank, rank, world_size)
+    info = sc.upload_world(host.describe())
+    params = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+
+    # ---- warm-up ----
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        sc.render(params)
+    barrier()
+    st = sc.stats()
+    local_rays = int(st.primary_rays + st.shadow_rays + st.ao_rays)
+    launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0) else 0)
+
+    # ---- timed: K steps, device time by CUDA events on the launching stream, L2 flushed between steps ----
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kern_ms = {"primary": 0.0, "ao": 0.0}
+    barrier()
+    t_begin = time.time()
+    for i in range(args.steps):
+        flush.zero_()
+        ev[i][0].record()
+        sc.render(params)
+        ev[i][1].record()
+    barrier()
+    t_end = time.time()
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = float(sum(step_ms))
+
+    # per-kernel device times (librc's events around each kernel), measured on separate frames after the timed loop
+    k_primary, k_ao = [], []
+    for _ in range(min(args.steps, 20)):
+        flush.zero_()
+        sc.render(params)
+        s = sc.stats()  # synchronises
+        k_primary.append(s.primary_ms)
+        k_ao.append(s.ao_ms)
+    kern_ms["primary"] = float(np.mean(k_primary))
+    kern_ms["ao"] = float(np.mean(k_ao))
+
+    # max over ranks (time) / sum over ranks (rays)
+    if world_size > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+        r = torch.tensor([local_rays], dtype=torch.int64, device=dev)
+        dist.all_reduce(r, op=dist.ReduceOp.SUM)
+        frame_rays = int(r.item())
+    else:
+        frame_rays = local_rays
+    ms_per_step = total_ms / args.steps
+    value = frame_rays / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e: through the C-ABI with HOST buffers: params in, RGBA8 frame out into pinned memory, every step ----
+    e2e = None
+    if not args.no_e2e:
+        pinned = torch.empty((h, w, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
+        host_img = pinned.numpy() if rank == 0 else None
+
+        def e2e_step():
+            if world_size == 1:
+                sc.caster.render_frame(params)
+                sc.caster.read_image(host_img)  # rc_read_image: D2H + stream sync
+            else:
+                sc.render(params)
+                if rank == 0:
+                    pinned.copy_(sc.frame(), non_blocking=True)
+                torch.cuda.synchronize(dev)
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        if world_size > 1:
+            t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = float(t.item())
+        e2e = {"value": frame_rays * args.steps / e2e_s / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": 104, "d2h_bytes_per_step": w * h * 4,
+               "ms_per_step": e2e_s / args.steps * 1e3,
+               "what": "rc_render_frame(host params) + rc_read_image into pinned host memory, synchronous, every step"
+                       + ("; includes the NCCL band gather + compose on rank 0" if world_size > 1 else "")}
+        if rank == 0:
+            assert host_img.any(), "e2e frame is empty"
+
+    clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
+    if rank != 0:
+        sc.close()
+        if world_size > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel ----
+    peak, peak_src = hbm_peak()
+    counters = golden_counters(golden_case)
+    roof, roof_all = None, {}
+    if counters and world_size == 1:
+        ab = counters["algorithmic_bytes"]  # [primary, shadow, ao]
+        per_kernel = {"primary_kernel": ((ab[0] + ab[1]), kern_ms["primary"]), "ao_kernel": (ab[2], kern_ms["ao"])}
+        for name, (bytes_, ms) in per_kernel.items():
+            if ms > 0:
+                ach = bytes_ / (ms * 1e-3) / 1e9
+                roof_all[name] = {"algorithmic_bytes_per_launch": bytes_, "ms": ms, "achieved": ach, "frac": ach / peak}
+        dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
+        if dom:
+            roof = {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
+                    "frac": roof_all[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": roof_all[dom]["algorithmic_bytes_per_launch"],
+                    "launch_ms": roof_all[dom]["ms"],
+                    "note": "algorithmic bytes = what the REFERENCE algorithm fetches for this frame (16 B per nodes[] read + "
+                            "4 B per child index, counted by the oracle); the kernel's cell caching avoids most of them, so "
+                            "frac can exceed 1; real DRAM traffic: see profiles/"}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world_size > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao, "ao_steps": 5,
+                   "max_steps": 300, "shadow_steps": 75,
+                   "world": "default generated world (initTetraHexaTree + genWorld, seeds 42/64/100, 200x200 columns)"
+                            if depth == 6 else "generated world 2048x2048 columns, tree depth 7 (extension)",
+                   "world_bytes": {"reference_format": int(info.ref_bytes), "packed": int(info.packed_bytes)},
+                   "camera": "default (35,50,35) dir normalize(1,0,1)", "rays_per_step": frame_rays,
+                   "l2": "flushed between steps (256 MB memset, outside the timed events)",
+                   "sharding": f"16-row bands round-robin over {world_size} GPUs, NCCL gather to rank 0 + compose kernel"
+                               if world_size > 1 else "none"},
+        "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "kernel_ms": kern_ms,
+        "roofline": roof, "roofline_kernels": roof_all, "clocks": clocks,
+    }
+    if world_size == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_leg(workload)
+    sc.close()
+    if world_size > 1:
+        dist.destroy_process_group()
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    workload = args.workload or ("config3_1080p_ao64" if args.gpus == 1 else "config5_8k_ao64")
+    if args.impl == "reference":
+        run_reference_arm(args, workload)
+    else:
+        run_b200_arm(args, workload)
+
+
+if __name__ == "__main__":
+    main()
