@@ -246,6 +246,8 @@ def run_b200_arm(args, workload):
     info = sc.upload_world(host.describe())
     params = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = sc.stream  # librc's kernels, the NCCL gather, the flush and the timing events all go on this stream
+    torch.cuda.set_stream(stream)
 
     def barrier():
         if world_size > 1:

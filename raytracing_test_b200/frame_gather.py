@@ -70,8 +70,10 @@ class ShardedRayCaster:
         self.device = torch.device("cuda", device_index)
         self.caster = rc.RayCaster(device_index)
         self.caster.set_shard(self.rank, self.world)
-        # kernels, the gather and the compose all go on torch's current stream: no cross-stream syncs
-        self.caster.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        # kernels, the gather and the compose are all ordered on ONE non-default torch stream (torch's
+        # default stream has handle 0, which rc_set_stream reads as "use the library's own stream")
+        self.stream = torch.cuda.Stream(self.device)
+        self.caster.set_stream(self.stream.cuda_stream)
         self._frame = None
         self._gathered = None
         self._dims = None
@@ -83,7 +85,11 @@ class ShardedRayCaster:
         return self.caster.upload_world(desc)  # replicated: every rank uploads the same host world
 
     def render(self, params):
-        """Enqueue: local bands -> gather to rank 0 -> compose. Asynchronous on the current stream."""
+        """Enqueue: local bands -> gather to rank 0 -> compose. Asynchronous on self.stream."""
+        with torch.cuda.stream(self.stream):
+            self._render(params)
+
+    def _render(self, params):
         w, h = params.width, params.height
         self.caster.render_frame(params)
         pr = padded_rows(h, self.world)
