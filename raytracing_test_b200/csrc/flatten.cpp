@@ -143,7 +143,7 @@ int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err)
         // inner root with 64 uniform cells so the kernel's cached node is never a leaf.
         uint32_t w = palette.word(rootNode);
         out.nodes[0] = PackedNode{~0ull, 1, PK_INNER};
-        for (int i = 0; i < 64; i++) out.nodes.push_back(PackedNode{0, w, PK_LEAF});
+        for (int i = 0; i < 64; i++) out.nodes.push_back(PackedNode{0, w, PK_LEAF | ((rootNode.flags & 0x10u) ? PK_HAS_LIQUID : 0u)});
         out.level_begin = {0, 1, 65};
         out.ref_nodes = 1;
         return RC_OK;
@@ -165,7 +165,7 @@ int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err)
                 err = "rc_upload_world: more than 2^24 distinct materials";
                 return RC_ERR_UNSUPPORTED;
             }
-            out.nodes[qi] = PackedNode{0, w, PK_LEAF};
+            out.nodes[qi] = PackedNode{0, w, PK_LEAF | ((n.flags & 0x10u) ? PK_HAS_LIQUID : 0u)};
             continue;
         }
         if (n.word3 >= pools.n_arrays) {
@@ -176,6 +176,7 @@ int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err)
         uint64_t mask = 0;
         if (cur.depth == brickDepth) {
             const uint64_t voxBase = out.voxels.size();
+            uint32_t liquid = 0;
             for (int i = 0; i < 64; i++) {
                 if (!((n.word0 >> i) & 1)) continue;
                 uint32_t c = pools.child(arr, i);
@@ -195,13 +196,14 @@ int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err)
                 }
                 out.ref_nodes++;
                 out.voxels.push_back(w);
+                if (leaf.flags & 0x10u) liquid = PK_HAS_LIQUID;
                 mask |= 1ull << i;
             }
             if (out.voxels.size() > 0xFFFFFFF0ull) {
                 err = "rc_upload_world: more than 2^32 voxels";
                 return RC_ERR_UNSUPPORTED;
             }
-            out.nodes[qi] = PackedNode{mask, (uint32_t)voxBase, PK_BRICK};
+            out.nodes[qi] = PackedNode{mask, (uint32_t)voxBase, PK_BRICK | liquid};
         } else {
             const uint64_t childBase = out.nodes.size();
             for (int i = 0; i < 64; i++) {
@@ -244,12 +246,12 @@ uint32_t packed_lookup(const PackedWorld& w, int32_t x, int32_t y, int32_t z, in
             return 0;
         }
         uint32_t rank = (uint32_t)__builtin_popcountll(n->mask & ((1ull << idx) - 1));
-        if (n->kind == PK_BRICK) {
+        if ((n->kind & PK_KIND_MASK) == PK_BRICK) {
             if (cell_shift) *cell_shift = 0;
             return w.voxels[n->base + rank];
         }
         const PackedNode* c = &w.nodes[n->base + rank];
-        if (c->kind == PK_LEAF) {
+        if ((c->kind & PK_KIND_MASK) == PK_LEAF) {
             if (cell_shift) *cell_shift = shift;
             return c->base;
         }

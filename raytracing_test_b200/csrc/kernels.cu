@@ -158,12 +158,12 @@ __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int 
             return 0u;
         }
         const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
-        if (c.kind == PK_BRICK) {
+        if ((c.kind & PK_KIND_MASK) == PK_BRICK) {
             cellShift = 0;
             return __ldg(&W.voxels[c.base + rank]);
         }
         const uint4 n = __ldg(&W.nodes[c.base + rank]);
-        if (n.w == PK_LEAF) {
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
             cellShift = c.shift;
             return n.z;
         }
@@ -696,63 +696,181 @@ __global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ Fr
 // AO kernel (semantics = oracle castAo): one thread per hit pixel,
 // all lanes of a warp walk the same table entry at the same time, so the
 // direction comes from __constant__ memory as a broadcast.
+//
+// The 64 rays of a pixel take <= ao_steps steps each from the SAME voxel: together
+// they visit at most a few dozen 4^3 bricks, over and over.  So the tree is not
+// walked per step: each thread keeps the occupancy of the brick it is in
+// (64-bit mask) in registers, and the bricks it has seen in a private,
+// direct-mapped cache in shared memory ([slot][thread] columns: bank = lane, no
+// conflicts whatever the slots).  A step inside the current brick costs a bit
+// test; a step into a cached brick one 16-byte shared-memory read; only a miss
+// descends the packed tree (from the deepest cached node that contains it).
+// The DDA arithmetic is the shader's, operation for operation.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) ao_kernel(const __grid_constant__ FrameArgs A) {
+constexpr int AO_THREADS = 128;
+constexpr int AO_SLOTS = 16;
+constexpr uint32_t AO_KEY_MASK = 0x3FFFFFFFu;   // 10 bits of brick coordinate per axis (max_depth <= 7)
+constexpr uint32_t BR_UNIFORM = 0x40000000u;    // the whole 4^3 cell is one material, base = its word
+constexpr uint32_t BR_LIQUID = 0x80000000u;     // some voxel of the cell is LIQUID: the word decides
+
+struct Brick {
+    unsigned long long mask;  // occupancy of the 4^3 cell, bit z<<4|y<<2|x
+    uint32_t base;            // voxels[base + rank], or the material word (BR_UNIFORM)
+    uint32_t info;            // BR_* | key
+};
+
+// The 4^3 cell around wrapped voxel (wx,wy,wz): occupancy + where its words live.
+__device__ __forceinline__ void fetch_brick(const DeviceWorld& W, Cursor& c, int wx, int wy, int wz, Brick& b) {
+    if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
+        uint4 n = __ldg(&W.nodes[0]);
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift = W.root_shift;
+    }
+    c.lx = wx;
+    c.ly = wy;
+    c.lz = wz;
+    for (;;) {
+        if (c.shift == 0) {  // max_depth 2: the root itself is the only brick
+            b.mask = c.mask;
+            b.base = c.base;
+            b.info = (c.kind & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
+            return;
+        }
+        const int idx = (((wz >> c.shift) & 3) << 4) | (((wy >> c.shift) & 3) << 2) | ((wx >> c.shift) & 3);
+        if (!((c.mask >> idx) & 1ull)) {
+            b.mask = 0ull;
+            b.base = 0u;
+            b.info = 0u;
+            return;
+        }
+        const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
+        const uint4 n = __ldg(&W.nodes[c.base + rank]);
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+            b.mask = ~0ull;
+            b.base = n.z;
+            b.info = BR_UNIFORM | ((word_flags(n.z) & 0x10u) ? BR_LIQUID : 0u);
+            return;
+        }
+        if (c.shift == 2) {  // n is the brick node of this cell
+            b.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+            b.base = n.z;
+            b.info = (n.w & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
+            return;
+        }
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift -= 2;
+    }
+}
+
+__global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ FrameArgs A) {
+    __shared__ uint32_t sInfo[AO_SLOTS][AO_THREADS];
+    __shared__ uint32_t sBase[AO_SLOTS][AO_THREADS];
+    __shared__ uint2 sMask[AO_SLOTS][AO_THREADS];
+
     const uint32_t nSeeds = A.counters->ao_seed_count;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= nSeeds) return;
+    const uint32_t tid = threadIdx.x;
     const rc_frame_params& P = A.p;
     const DeviceWorld& W = A.world;
     const AoSeed s = A.ao_seeds[t];
     const int face = (int)(s.face_sign & 3u);
     const bool negNormal = (s.face_sign & 4u) != 0u;
+    const bool f0 = face == 0, f1 = face == 1;
+    const bool cacheable = W.wrap <= 4095u;  // brick coordinates fit 10 bits per axis
+
+    // Empty slots hold a key that can never be looked up there: brick (1023,1023,1023) maps to slot
+    // 15, brick (0,0,0) to slot 0.
+#pragma unroll
+    for (int k = 0; k < AO_SLOTS; k++) sInfo[k][tid] = (k == AO_SLOTS - 1) ? 0u : 0xFFFFFFFFu;
 
     Cursor cur;
     cursor_reset(W, cur);
+    Brick br;
+    br.mask = 0ull;
+    br.base = 0u;
+    br.info = 0u;
+    int cx = s.x ^ 0x40000000, cy = s.y, cz = s.z;  // a voxel of the brick held in br: none yet (far away)
+
+    const float fx = (float)s.x, fy = (float)s.y, fz = (float)s.z;
     uint32_t occluded = 0;
-    for (uint32_t k = 0; k < P.ao_samples; k++) {
+    const uint32_t nSamples = P.ao_samples, nSteps = P.ao_steps;
+    for (uint32_t k = 0; k < nSamples; k++) {
         const float tx = c_hemi[3 * k + 0], ty = c_hemi[3 * k + 1], up = c_hemi[3 * k + 2];
         const float itx = c_hemi_inv[3 * k + 0], ity = c_hemi_inv[3 * k + 1], iup = c_hemi_inv[3 * k + 2];
         // d[face] = sg*up, d[(face+1)%3] = tx, d[(face+2)%3] = ty ; 1/(-up) == -(1/up) exactly
         const float su = negNormal ? -up : up, siu = negNormal ? -iup : iup;
-        Ray r;
-        float dx, dy, dz, ix, iy, iz;
-        if (face == 0) {
-            dx = su; dy = tx; dz = ty; ix = siu; iy = itx; iz = ity;
-        } else if (face == 1) {
-            dy = su; dz = tx; dx = ty; iy = siu; iz = itx; ix = ity;
-        } else {
-            dz = su; dx = tx; dy = ty; iz = siu; ix = itx; iy = ity;
-        }
-        r.dx = dx; r.dy = dy; r.dz = dz;
-        r.sx = dx < 0.0f ? -1 : 1;
-        r.sy = dy < 0.0f ? -1 : 1;
-        r.sz = dz < 0.0f ? -1 : 1;
-        r.ddx = ix; r.ddy = iy; r.ddz = iz;
-        r.adx = fabsf(ix); r.ady = fabsf(iy); r.adz = fabsf(iz);
-        Pos p;
-        p.x = s.x; p.y = s.y; p.z = s.z;
-        p.ex = r.sx < 0 ? FSUB(s.ex, 1.0f) : s.ex;
-        p.ey = r.sy < 0 ? FSUB(s.ey, 1.0f) : s.ey;
-        p.ez = r.sz < 0 ? FSUB(s.ez, 1.0f) : s.ez;
-        init_delta_pos(r, p);
-        if (face == 0) p.tx = FSUB(p.tx, r.adx);
-        else if (face == 1) p.ty = FSUB(p.ty, r.ady);
-        else p.tz = FSUB(p.tz, r.adz);
-        uint32_t i = P.ao_steps;
-        uint32_t w = 0u;
-        CellCount c;
-        c.nx = c.ny = c.nz = 1;
-        int cellShift;
-        while ((w == 0u || (word_flags(w) & 0x10u)) && i-- != 0u) {
-            bool leftCell;
-            dda_step<false>(r, p, c, leftCell);
-            if (leftCell) {
-                w = lookup(W, cur, p.x, p.y, p.z, cellShift);
-                after_lookup(c, r, p, w, cellShift);
+        const float dx = f0 ? su : (f1 ? ty : tx), ix = f0 ? siu : (f1 ? ity : itx);
+        const float dy = f1 ? su : (f0 ? tx : ty), iy = f1 ? siu : (f0 ? itx : ity);
+        const float dz = f0 ? ty : (f1 ? tx : su), iz = f0 ? ity : (f1 ? itx : siu);
+        const bool nx = dx < 0.0f, ny = dy < 0.0f, nz = dz < 0.0f;
+        const int sx = nx ? -1 : 1, sy = ny ? -1 : 1, sz = nz ? -1 : 1;
+        const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
+        // pos.exact re-biased for the new signs; deltaPos = absDelta - (exact - round) * delta
+        const float ex = nx ? FSUB(s.ex, 1.0f) : s.ex;
+        const float ey = ny ? FSUB(s.ey, 1.0f) : s.ey;
+        const float ez = nz ? FSUB(s.ez, 1.0f) : s.ez;
+        float px = FSUB(adx, FMUL(FSUB(ex, fx), ix));
+        float py = FSUB(ady, FMUL(FSUB(ey, fy), iy));
+        float pz = FSUB(adz, FMUL(FSUB(ez, fz), iz));
+        if (f0) px = FSUB(px, adx);
+        else if (f1) py = FSUB(py, ady);
+        else pz = FSUB(pz, adz);
+        int x = s.x, y = s.y, z = s.z;
+
+        // while ((block empty || LIQUID) && i-- != 0) { DDA step; getBlock }  -- state: 0 empty, 1 liquid, 2 opaque
+        uint32_t state = 0u;
+        uint32_t i = nSteps;
+        while (state != 2u && i-- != 0u) {
+            // nextIntersectDDA (low_res.frag:446-491), branch-free
+            const bool bx = px < py && px < pz;
+            const bool by = !bx && py < pz;
+            const bool bz = !bx && !by;
+            if (bx) { x += sx; px = FADD(px, adx); }
+            if (by) { y += sy; py = FADD(py, ady); }
+            if (bz) { z += sz; pz = FADD(pz, adz); }
+
+            if ((((x ^ cx) | (y ^ cy) | (z ^ cz)) >> 2) != 0) {
+                cx = x;
+                cy = y;
+                cz = z;
+                const int wx = wrap_coord(W, x), wy = wrap_coord(W, y), wz = wrap_coord(W, z);
+                const uint32_t bxk = (uint32_t)wx >> 2, byk = (uint32_t)wy >> 2, bzk = (uint32_t)wz >> 2;
+                const uint32_t key = bxk | (byk << 10) | (bzk << 20);
+                const uint32_t slot = (bxk & 1u) | ((byk & 1u) << 1) | ((bzk & 1u) << 2) | ((((bxk ^ byk ^ bzk) >> 1) & 1u) << 3);
+                const uint32_t info = sInfo[slot][tid];
+                if (cacheable && (info & AO_KEY_MASK) == key) {
+                    const uint2 m = sMask[slot][tid];
+                    br.mask = (unsigned long long)m.x | ((unsigned long long)m.y << 32);
+                    br.base = sBase[slot][tid];
+                    br.info = info;
+                } else {
+                    fetch_brick(W, cur, wx, wy, wz, br);
+                    br.info |= key;
+                    if (cacheable) {
+                        sInfo[slot][tid] = br.info;
+                        sBase[slot][tid] = br.base;
+                        sMask[slot][tid] = make_uint2((uint32_t)br.mask, (uint32_t)(br.mask >> 32));
+                    }
+                }
+            }
+            const int idx = ((z & 3) << 4) | ((y & 3) << 2) | (x & 3);
+            if (!((br.mask >> idx) & 1ull)) {
+                state = 0u;
+            } else if (!(br.info & BR_LIQUID)) {
+                state = 2u;
+            } else {
+                const uint32_t w = (br.info & BR_UNIFORM)
+                                       ? br.base
+                                       : __ldg(&W.voxels[br.base + (uint32_t)__popcll(br.mask & ((1ull << idx) - 1ull))]);
+                state = (word_flags(w) & 0x10u) ? 1u : 2u;
             }
         }
-        if (w != 0u) occluded++;
+        if (state != 0u) occluded++;
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
     store_pixel(A, s.pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
@@ -813,7 +931,7 @@ cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
 
 cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
     if (maxSeeds == 0) return cudaSuccess;
-    ao_kernel<<<(maxSeeds + 127u) / 128u, 128, 0, stream>>>(args);
+    ao_kernel<<<(maxSeeds + AO_THREADS - 1u) / AO_THREADS, AO_THREADS, 0, stream>>>(args);
     return cudaGetLastError();
 }
 

@@ -39,6 +39,12 @@
 namespace rc {
 
 enum : uint32_t { PK_INNER = 0, PK_BRICK = 1, PK_LEAF = 2 };
+// kind = PK_* in the low byte, flags above it
+constexpr uint32_t PK_KIND_MASK = 0xFFu;
+// PK_BRICK: at least one voxel of the brick is LIQUID (0x10, src/globals.hpp:72); PK_LEAF: the material is.
+// Shadow / AO rays pass through liquid (low_res.frag:384): where the flag is clear an occupancy bit
+// alone says "opaque" and no material word has to be fetched.
+constexpr uint32_t PK_HAS_LIQUID = 0x100u;
 
 struct PackedNode {
     uint64_t mask;
