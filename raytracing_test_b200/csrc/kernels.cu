@@ -174,6 +174,92 @@ __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int 
     }
 }
 
+__device__ __forceinline__ uint32_t word_flags(uint32_t word) { return word >> MATERIAL_FLAG_SHIFT; }
+
+// ---------------------------------------------------------------------------
+// Region: the largest aligned piece of the world the tree describes with ONE node around a
+// voxel -- an empty 4^k cell (mask 0), a uniform solid 4^k cell (mask ~0, base = its material
+// word), or a 4^3 brick (mask = occupancy, base = first voxel word).  While a ray stays inside
+// a region the tree is not touched: emptiness is a bit test in registers.
+// ---------------------------------------------------------------------------
+constexpr uint32_t BR_UNIFORM = 0x40000000u;    // the whole cell is one material, base = its word
+constexpr uint32_t BR_LIQUID = 0x80000000u;     // some voxel of the cell is LIQUID: the word decides
+
+struct Region {
+    unsigned long long mask;  // occupancy of the 4^3 cell, bit z<<4|y<<2|x (0 / ~0 for uniform cells)
+    uint32_t base;            // voxels[base + rank], or the material word (BR_UNIFORM)
+    uint32_t info;            // BR_* (the AO kernel keeps its cache key in the low 30 bits)
+    int shift;                // log2 of the region's edge (2 for a brick)
+};
+
+// Region around wrapped voxel (wx,wy,wz); descends from the deepest cached node that contains it.
+__device__ __forceinline__ void fetch_region(const DeviceWorld& W, Cursor& c, int wx, int wy, int wz, Region& r) {
+    if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
+        uint4 n = __ldg(&W.nodes[0]);
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift = W.root_shift;
+    }
+    c.lx = wx;
+    c.ly = wy;
+    c.lz = wz;
+    for (;;) {
+        if (c.shift == 0) {  // the cached node is itself the brick around the voxel
+            r.mask = c.mask;
+            r.base = c.base;
+            r.info = (c.kind & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
+            r.shift = 2;
+            return;
+        }
+        const int idx = (((wz >> c.shift) & 3) << 4) | (((wy >> c.shift) & 3) << 2) | ((wx >> c.shift) & 3);
+        if (!((c.mask >> idx) & 1ull)) {
+            r.mask = 0ull;
+            r.base = 0u;
+            r.info = 0u;
+            r.shift = c.shift;
+            return;
+        }
+        const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
+        const uint4 n = __ldg(&W.nodes[c.base + rank]);
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+            r.mask = ~0ull;
+            r.base = n.z;
+            r.info = BR_UNIFORM | ((word_flags(n.z) & 0x10u) ? BR_LIQUID : 0u);
+            r.shift = c.shift;
+            return;
+        }
+        if (c.shift == 2) {  // n is the brick node of this 4^3 cell
+            r.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+            r.base = n.z;
+            r.info = (n.w & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
+            r.shift = 2;
+            return;
+        }
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.shift -= 2;
+    }
+}
+
+__device__ __forceinline__ int brick_bit(int x, int y, int z) { return ((z & 3) << 4) | ((y & 3) << 2) | (x & 3); }
+
+// Material word of an occupied voxel (bit idx of r.mask is set).
+__device__ __forceinline__ uint32_t region_word(const DeviceWorld& W, const Region& r, int idx) {
+    return (r.info & BR_UNIFORM) ? r.base : __ldg(&W.voxels[r.base + (uint32_t)__popcll(r.mask & ((1ull << idx) - 1ull))]);
+}
+
+// State of a shadow / AO ray after entering voxel (x,y,z) of region r: 0 empty, 1 LIQUID (the
+// ray goes on, low_res.frag:384), 2 opaque.
+__device__ __forceinline__ uint32_t occlusion_state(const DeviceWorld& W, const Region& r, int x, int y, int z) {
+    if (r.mask == 0ull) return 0u;
+    const int idx = brick_bit(x, y, z);
+    if (!((r.mask >> idx) & 1ull)) return 0u;
+    if (!(r.info & BR_LIQUID)) return 2u;
+    return (word_flags(region_word(W, r, idx)) & 0x10u) ? 1u : 2u;
+}
+
 // ---------------------------------------------------------------------------
 // Ray + position state (the shader's `ray` and `pos` globals)
 // ---------------------------------------------------------------------------
@@ -277,6 +363,62 @@ __device__ __forceinline__ int dda_step(const Ray& r, Pos& p, CellCount& n, bool
     return a;
 }
 
+// nextIntersectDDA without pos.exact and without divergence: the three-way choice becomes
+// predicates.  Same comparisons, same additions as dda_step.
+struct StepAxis {
+    bool x, y;  // neither: z
+};
+__device__ __forceinline__ StepAxis dda_step_bl(const Ray& r, Pos& p) {
+    StepAxis a;
+    a.x = p.tx < p.ty && p.tx < p.tz;
+    a.y = !a.x && p.ty < p.tz;
+    const bool az = !a.x && !a.y;
+    if (a.x) { p.x += r.sx; p.tx = FADD(p.tx, r.adx); }
+    if (a.y) { p.y += r.sy; p.ty = FADD(p.ty, r.ady); }
+    if (az) { p.z += r.sz; p.tz = FADD(p.tz, r.adz); }
+    return a;
+}
+__device__ __forceinline__ int axis_index(StepAxis a) { return a.x ? 0 : (a.y ? 1 : 2); }
+
+// The same step with pos.exact carried along (low_res.frag:447,489: dst is taken BEFORE the
+// update, exact += dst[a] * ratios[a] with ratios[a][a] = 1), still branch-free.
+__device__ __forceinline__ StepAxis dda_step_exact_bl(const Ray& r, Pos& p) {
+    StepAxis a;
+    a.x = p.tx < p.ty && p.tx < p.tz;
+    a.y = !a.x && p.ty < p.tz;
+    const bool az = !a.x && !a.y;
+    const float ea = a.x ? p.ex : (a.y ? p.ey : p.ez);
+    const int ra = a.x ? p.x : (a.y ? p.y : p.z);
+    const int sa = a.x ? r.sx : (a.y ? r.sy : r.sz);
+    const float dst = FSUB((float)sa, FSUB(ea, (float)ra));
+    const float rx = a.x ? 1.0f : (a.y ? r.r1x : r.r2x);
+    const float ry = a.x ? r.r0y : (a.y ? 1.0f : r.r2y);
+    const float rz = a.x ? r.r0z : (a.y ? r.r1z : 1.0f);
+    p.ex = FADD(p.ex, FMUL(dst, rx));
+    p.ey = FADD(p.ey, FMUL(dst, ry));
+    p.ez = FADD(p.ez, FMUL(dst, rz));
+    if (a.x) { p.x += r.sx; p.tx = FADD(p.tx, r.adx); }
+    if (a.y) { p.y += r.sy; p.ty = FADD(p.ty, r.ady); }
+    if (az) { p.z += r.sz; p.tz = FADD(p.tz, r.adz); }
+    return a;
+}
+
+// Region that holds the ray's voxel + where it was fetched (raw coordinates: aligned cells up to
+// the root's children keep their extent under wrap_coord).
+struct RegionAt {
+    Region r;
+    int x, y, z;
+};
+__device__ __forceinline__ bool left_region(const RegionAt& g, const Pos& p) {
+    return ((((p.x ^ g.x) | (p.y ^ g.y) | (p.z ^ g.z)) >> g.r.shift) != 0);
+}
+__device__ __forceinline__ void enter_region(const DeviceWorld& W, Cursor& c, RegionAt& g, const Pos& p) {
+    g.x = p.x;
+    g.y = p.y;
+    g.z = p.z;
+    fetch_region(W, c, wrap_coord(W, p.x), wrap_coord(W, p.y), wrap_coord(W, p.z), g.r);
+}
+
 // After a lookup: refresh the countdown. A solid voxel forces a lookup on the next step.
 __device__ __forceinline__ void after_lookup(CellCount& n, const Ray& r, const Pos& p, uint32_t word, int cellShift) {
     if (word == 0u) {
@@ -285,8 +427,6 @@ __device__ __forceinline__ void after_lookup(CellCount& n, const Ray& r, const P
         n.nx = n.ny = n.nz = 1;
     }
 }
-
-__device__ __forceinline__ uint32_t word_flags(uint32_t word) { return word >> MATERIAL_FLAG_SHIFT; }
 
 // low_res.frag:137-147
 __device__ __forceinline__ F3 decode_color(unsigned long long color) {
@@ -334,7 +474,9 @@ struct PixelResult {
 };
 
 // One pixel of low_res.frag main() (:256-393).
-__device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uint32_t py, PixelResult& out) {
+// Called by ALL 32 lanes of a warp (valid = the lane has a pixel): the primary loop agrees on its
+// batch length with warp votes.
+__device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint32_t px, uint32_t py, PixelResult& out) {
     const rc_frame_params& P = A.p;
     const DeviceWorld& W = A.world;
     out.color = F3{0.0f, 0.0f, 0.0f};
@@ -348,15 +490,16 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uin
     const float fragX = FADD((float)px, 0.5f), fragY = FADD((float)py, 0.5f);
 
     // :259-262
-    if ((P.flags & RC_F_CROSSHAIR) && P.render_pos_data == 0) {
+    bool live = valid;  // this lane still traces a ray
+    if (live && (P.flags & RC_F_CROSSHAIR) && P.render_pos_data == 0) {
         const float mx = FSUB(fragX, P.mouse_pos[0]), my = FSUB(fragY, P.mouse_pos[1]);
         if (FSQRT(FADD(FMUL(mx, mx), FMUL(my, my))) <= 3.0f) {
             out.color = F3{1.0f, 1.0f, 1.0f};
             out.hit.kind = RC_KIND_CROSSHAIR;
-            return;
+            live = false;
         }
     }
-    out.traced = true;
+    out.traced = live;
 
     // :264-265
     const float fcx = FMUL(fragX, FDIV(1.0f, (float)P.width));
@@ -394,8 +537,14 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uin
     float refrIndex = 1.0f;
 
     // :299-307
-    uint32_t word = lookup(W, cur, pos.x, pos.y, pos.z, cellShift);
-    if (word != 0u) {
+    RegionAt rg;
+    enter_region(W, cur, rg, pos);
+    uint32_t word = 0u;
+    {
+        const int idx = brick_bit(pos.x, pos.y, pos.z);
+        if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
+    }
+    if (live && word != 0u) {
         if (word_flags(word) & 0x4u) {
             refrIndex = 1.1f;
         } else {
@@ -405,24 +554,65 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uin
             out.hit.x = pos.x;
             out.hit.y = pos.y;
             out.hit.z = pos.z;
-            return;
+            live = false;
         }
     }
-    after_lookup(cnt, ray, pos, word, cellShift);
 
-    // :309-315  loop A
+    // :309-315  loop A: to the first non-empty voxel.  pos.exact is not needed to FIND it, so this
+    // pass leaves it alone (sky rays, ~300 steps each, never need it); rays that do hit replay their
+    // steps below with pos.exact carried, in registers, without touching the tree.
+    // Inside an empty 4^k cell a step is the DDA arithmetic plus one XOR test against the cell; the
+    // tree is consulted only when the ray leaves the cell.  Inside a brick a step adds a bit test.
     uint32_t i = 0;
     uint32_t steps = 0;
     const uint32_t numSteps = P.max_steps;
-    while (word == 0u && i++ < numSteps) {
-        bool leftCell;
-        face = dda_step<true>(ray, pos, cnt, leftCell);
-        steps++;
-        if (leftCell) {
-            word = lookup(W, cur, pos.x, pos.y, pos.z, cellShift);
-            after_lookup(cnt, ray, pos, word, cellShift);
+    {
+        StepAxis ax;
+        ax.x = ax.y = false;
+        bool act = live && word == 0u && numSteps != 0u;
+        while (act) {
+            if (rg.r.mask == 0ull) {
+                bool inside;
+                do {
+                    ax = dda_step_bl(ray, pos);
+                    steps++;
+                    inside = !left_region(rg, pos);
+                } while (inside && steps < numSteps);
+                if (inside) break;  // out of steps inside the empty cell
+                enter_region(W, cur, rg, pos);
+            } else {
+                ax = dda_step_bl(ray, pos);
+                steps++;
+                if (left_region(rg, pos)) enter_region(W, cur, rg, pos);
+            }
+            if (rg.r.mask != 0ull) {
+                const int idx = brick_bit(pos.x, pos.y, pos.z);
+                if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
+            }
+            act = word == 0u && steps < numSteps;
         }
+        if (!live) return;
+        // the shader's counter: `while (empty && i++ < numSteps)` leaves numSteps + 1 behind when it runs out
+        i = word != 0u ? steps : numSteps + 1u;
+        if (steps) face = axis_index(ax);
     }
+    if (steps != 0u && (word != 0u || P.render_pos_data == 1)) {
+        // replay: same ray, same comparisons, now with pos.exact (low_res.frag:447,489)
+        Pos rp;
+        rp.x = (int)floorf(origin.x);
+        rp.y = (int)floorf(origin.y);
+        rp.z = (int)floorf(origin.z);
+        rp.ex = pos.ex;
+        rp.ey = pos.ey;
+        rp.ez = pos.ez;
+        init_delta_pos(ray, rp);
+        for (uint32_t n = 0; n < steps; n++) dda_step_exact_bl(ray, rp);
+        pos.ex = rp.ex;
+        pos.ey = rp.ey;
+        pos.ez = rp.ez;
+    }
+    cnt.nx = cnt.ny = cnt.nz = 1;
+    cellShift = 0;
     // :317-333  loop B
     while (i++ < numSteps) {
         if (word != 0u) {
@@ -592,19 +782,16 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, uint32_t px, uin
         else if (face == 1) sp.ty = FSUB(sp.ty, sr.ady);
         else sp.tz = FSUB(sp.tz, sr.adz);
         uint32_t k = P.shadow_steps;
-        uint32_t sw = 0u;       // block = (-1,-1): "empty"
+        uint32_t state = 0u;  // block = (-1,-1): "empty"; 1 = LIQUID (the ray goes on), 2 = opaque
         uint32_t ssteps = 0;
-        CellCount sc;
-        sc.nx = sc.ny = sc.nz = 1;
-        while ((sw == 0u || (word_flags(sw) & 0x10u)) && k-- != 0u) {
-            bool leftCell;
-            dda_step<false>(sr, sp, sc, leftCell);
+        enter_region(W, cur, rg, sp);
+        while (state != 2u && k-- != 0u) {
+            dda_step_bl(sr, sp);
             ssteps++;
-            if (leftCell) {
-                sw = lookup(W, cur, sp.x, sp.y, sp.z, cellShift);
-                after_lookup(sc, sr, sp, sw, cellShift);
-            }
+            if (left_region(rg, sp)) enter_region(W, cur, rg, sp);
+            state = occlusion_state(W, rg.r, sp.x, sp.y, sp.z);
         }
+        const uint32_t sw = state;
         out.hit.shadow_steps = (uint16_t)ssteps;
         if (sw != 0u) {
             out.color = dim;
@@ -641,8 +828,8 @@ __global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ Fr
     R.aoSeed = false;
     R.hit.kind = RC_KIND_SKY;
     R.hit.steps = 0;
+    shade_pixel(A, active, px, py, R);
     if (active) {
-        shade_pixel(A, px, py, R);
         const uint32_t idx = local_index(A, px, localRow);
         // AO pixels get their final colour from the AO kernel
         if (!(R.aoSeed)) store_pixel(A, idx, R.color);
@@ -710,61 +897,6 @@ __global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ Fr
 constexpr int AO_THREADS = 128;
 constexpr int AO_SLOTS = 16;
 constexpr uint32_t AO_KEY_MASK = 0x3FFFFFFFu;   // 10 bits of brick coordinate per axis (max_depth <= 7)
-constexpr uint32_t BR_UNIFORM = 0x40000000u;    // the whole 4^3 cell is one material, base = its word
-constexpr uint32_t BR_LIQUID = 0x80000000u;     // some voxel of the cell is LIQUID: the word decides
-
-struct Brick {
-    unsigned long long mask;  // occupancy of the 4^3 cell, bit z<<4|y<<2|x
-    uint32_t base;            // voxels[base + rank], or the material word (BR_UNIFORM)
-    uint32_t info;            // BR_* | key
-};
-
-// The 4^3 cell around wrapped voxel (wx,wy,wz): occupancy + where its words live.
-__device__ __forceinline__ void fetch_brick(const DeviceWorld& W, Cursor& c, int wx, int wy, int wz, Brick& b) {
-    if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
-        uint4 n = __ldg(&W.nodes[0]);
-        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
-        c.base = n.z;
-        c.kind = n.w;
-        c.shift = W.root_shift;
-    }
-    c.lx = wx;
-    c.ly = wy;
-    c.lz = wz;
-    for (;;) {
-        if (c.shift == 0) {  // max_depth 2: the root itself is the only brick
-            b.mask = c.mask;
-            b.base = c.base;
-            b.info = (c.kind & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
-            return;
-        }
-        const int idx = (((wz >> c.shift) & 3) << 4) | (((wy >> c.shift) & 3) << 2) | ((wx >> c.shift) & 3);
-        if (!((c.mask >> idx) & 1ull)) {
-            b.mask = 0ull;
-            b.base = 0u;
-            b.info = 0u;
-            return;
-        }
-        const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
-        const uint4 n = __ldg(&W.nodes[c.base + rank]);
-        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
-            b.mask = ~0ull;
-            b.base = n.z;
-            b.info = BR_UNIFORM | ((word_flags(n.z) & 0x10u) ? BR_LIQUID : 0u);
-            return;
-        }
-        if (c.shift == 2) {  // n is the brick node of this cell
-            b.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
-            b.base = n.z;
-            b.info = (n.w & PK_HAS_LIQUID) ? BR_LIQUID : 0u;
-            return;
-        }
-        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
-        c.base = n.z;
-        c.kind = n.w;
-        c.shift -= 2;
-    }
-}
 
 __global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ FrameArgs A) {
     __shared__ uint32_t sInfo[AO_SLOTS][AO_THREADS];
@@ -790,11 +922,12 @@ __global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ 
 
     Cursor cur;
     cursor_reset(W, cur);
-    Brick br;
+    Region br;
     br.mask = 0ull;
     br.base = 0u;
     br.info = 0u;
-    int cx = s.x ^ 0x40000000, cy = s.y, cz = s.z;  // a voxel of the brick held in br: none yet (far away)
+    br.shift = 2;
+    int cx = s.x ^ 0x40000000, cy = s.y, cz = s.z;  // a voxel of the region held in br: none yet (far away)
 
     const float fx = (float)s.x, fy = (float)s.y, fz = (float)s.z;
     uint32_t occluded = 0;
@@ -834,22 +967,23 @@ __global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ 
             if (by) { y += sy; py = FADD(py, ady); }
             if (bz) { z += sz; pz = FADD(pz, adz); }
 
-            if ((((x ^ cx) | (y ^ cy) | (z ^ cz)) >> 2) != 0) {
+            if ((((x ^ cx) | (y ^ cy) | (z ^ cz)) >> br.shift) != 0) {
                 cx = x;
                 cy = y;
                 cz = z;
                 const int wx = wrap_coord(W, x), wy = wrap_coord(W, y), wz = wrap_coord(W, z);
                 const uint32_t bxk = (uint32_t)wx >> 2, byk = (uint32_t)wy >> 2, bzk = (uint32_t)wz >> 2;
                 const uint32_t key = bxk | (byk << 10) | (bzk << 20);
-                const uint32_t slot = (bxk & 1u) | ((byk & 1u) << 1) | ((bzk & 1u) << 2) | ((((bxk ^ byk ^ bzk) >> 1) & 1u) << 3);
+                const uint32_t slot = (bxk & 1u) | ((byk & 1u) << 1) | (bzk & 3u) << 2;
                 const uint32_t info = sInfo[slot][tid];
                 if (cacheable && (info & AO_KEY_MASK) == key) {
                     const uint2 m = sMask[slot][tid];
                     br.mask = (unsigned long long)m.x | ((unsigned long long)m.y << 32);
                     br.base = sBase[slot][tid];
                     br.info = info;
+                    br.shift = 2;
                 } else {
-                    fetch_brick(W, cur, wx, wy, wz, br);
+                    fetch_region(W, cur, wx, wy, wz, br);
                     br.info |= key;
                     if (cacheable) {
                         sInfo[slot][tid] = br.info;
@@ -858,17 +992,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ 
                     }
                 }
             }
-            const int idx = ((z & 3) << 4) | ((y & 3) << 2) | (x & 3);
-            if (!((br.mask >> idx) & 1ull)) {
-                state = 0u;
-            } else if (!(br.info & BR_LIQUID)) {
-                state = 2u;
-            } else {
-                const uint32_t w = (br.info & BR_UNIFORM)
-                                       ? br.base
-                                       : __ldg(&W.voxels[br.base + (uint32_t)__popcll(br.mask & ((1ull << idx) - 1ull))]);
-                state = (word_flags(w) & 0x10u) ? 1u : 2u;
-            }
+            state = occlusion_state(W, br, x, y, z);
         }
         if (state != 0u) occluded++;
     }

@@ -1,0 +1,23 @@
+"""Developer probe for ncu: renders a few frames of one BASELINE config on cuda:0 and exits.
+python tools/profile_frame.py [width height shadows ao_samples frames]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from raytracing_test_b200 import rc, voxel_host as vh
+
+a = sys.argv[1:]
+w, h = (int(a[0]), int(a[1])) if len(a) >= 2 else (1920, 1080)
+sh = bool(int(a[2])) if len(a) >= 3 else True
+ao = int(a[3]) if len(a) >= 4 else 64
+frames = int(a[4]) if len(a) >= 5 else 4
+host = vh.World.default()
+pos, d, sun = vh.default_camera()
+with rc.RayCaster(0) as c:
+    c.upload_world(host.describe())
+    p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao)
+    for _ in range(frames):
+        c.render_frame(p)
+        c.sync()
+    st = c.stats()
+    print(f"{w}x{h} shadows={sh} ao={ao}: primary {st.primary_ms:.3f} ms ao {st.ao_ms:.3f} ms")
