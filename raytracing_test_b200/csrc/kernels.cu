@@ -572,13 +572,33 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         bool act = live && word == 0u && numSteps != 0u;
         while (act) {
             if (rg.r.mask == 0ull) {
-                bool inside;
+                // Empty cell.  The integer side of a step (position, cell test, step budget) is kept
+                // as float countdowns -- voxels left to the cell's faces per axis, steps left -- so the
+                // loop body is FADD/FMUL on the FMA pipes plus five compares, instead of integer/logic
+                // work on the half-rate ALU pipe.  All values are small integers: exact in fp32.
+                CellCount n;
+                count_cell(n, ray, pos, rg.r.shift);
+                float fnx = (float)n.nx, fny = (float)n.ny, fnz = (float)n.nz;
+                const float rem0 = (float)(numSteps - steps);
+                float rem = rem0;
+                float tx = pos.tx, ty = pos.ty, tz = pos.tz;
                 do {
-                    ax = dda_step_bl(ray, pos);
-                    steps++;
-                    inside = !left_region(rg, pos);
-                } while (inside && steps < numSteps);
-                if (inside) break;  // out of steps inside the empty cell
+                    ax.x = tx < ty && tx < tz;
+                    ax.y = !ax.x && ty < tz;
+                    const bool az = !ax.x && !ax.y;
+                    if (ax.x) { tx = FADD(tx, ray.adx); fnx -= 1.0f; }
+                    if (ax.y) { ty = FADD(ty, ray.ady); fny -= 1.0f; }
+                    if (az) { tz = FADD(tz, ray.adz); fnz -= 1.0f; }
+                    rem -= 1.0f;
+                } while ((fnx * fny) * (fnz * rem) != 0.0f);
+                pos.tx = tx;
+                pos.ty = ty;
+                pos.tz = tz;
+                pos.x += ray.sx * (n.nx - (int)fnx);
+                pos.y += ray.sy * (n.ny - (int)fny);
+                pos.z += ray.sz * (n.nz - (int)fnz);
+                steps += (uint32_t)(rem0 - rem);
+                if ((fnx * fny) * fnz != 0.0f) break;  // out of steps inside the empty cell
                 enter_region(W, cur, rg, pos);
             } else {
                 ax = dda_step_bl(ray, pos);
