@@ -918,7 +918,7 @@ constexpr int AO_THREADS = 128;
 constexpr int AO_SLOTS = 16;
 constexpr uint32_t AO_KEY_MASK = 0x3FFFFFFFu;   // 10 bits of brick coordinate per axis (max_depth <= 7)
 
-__global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ FrameArgs A) {
+__global__ void __launch_bounds__(AO_THREADS) ao_cached_kernel(const __grid_constant__ FrameArgs A) {
     __shared__ uint32_t sInfo[AO_SLOTS][AO_THREADS];
     __shared__ uint32_t sBase[AO_SLOTS][AO_THREADS];
     __shared__ uint2 sMask[AO_SLOTS][AO_THREADS];
@@ -1021,6 +1021,173 @@ __global__ void __launch_bounds__(AO_THREADS) ao_kernel(const __grid_constant__ 
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
 }
 
+// ---------------------------------------------------------------------------
+// AO kernel for ao_steps <= AOW_MAX_STEPS (the reference's 5, light_scattering.frag:231).
+//
+// The first step of every AO ray leaves the hit voxel through the hit face (deltaPos[face] was
+// lowered by absDelta[face]); after that its normal coordinate never comes back.  So all rays of
+// a pixel stay inside a box of 2 bricks along the normal and 3 bricks along each tangent axis:
+// 12 x 12 x 8 voxels.  Each thread first copies the occupancy of those 18 bricks out of the tree
+// into a private dense bit window in shared memory ([word][thread] columns), laid out so that a
+// DDA step is ONE integer add (q += +-1 | +-strideY | +-strideZ) and the emptiness test one
+// shared-memory word + shift.  The 64 rays then run without touching the tree.
+//   face x: strides 1, 8, 96   (8 x 12 x 12 voxels)
+//   face y: strides 1, 16, 128 (12 x 8 x 12, rows padded to 16)
+//   face z: strides 1, 16, 192 (12 x 12 x 8, rows padded to 16)
+// A 4-voxel x-row of a brick lands at a multiple of 4 and never straddles a word.
+// Pixels with LIQUID voxels nearby (rays pass through them, low_res.frag:384) and rays whose first
+// step is not the forced one (possible only through accumulated rounding of pos.exact) take the
+// general loop of ao_ray_general instead.
+// ---------------------------------------------------------------------------
+constexpr uint32_t AOW_MAX_STEPS = 5;
+constexpr int AOW_WORDS = 48;
+
+// One table entry per (orientation = face*2 + negative normal, sample): what buildRay derives
+// from the direction, precomputed on the host with the same IEEE operations.
+struct AoDir {
+    float ix, iy, iz;   // ray.delta = 1 / dir
+    int qx, qy, qz;     // window stride of one step along each axis: sign(dir) * stride(face)
+    float dx, dy;       // unused by the kernel (kept for debugging), pads the entry to 32 bytes
+};
+static_assert(sizeof(AoDir) == 32, "AoDir is two 128-bit loads");
+
+__device__ __forceinline__ int aow_stride_y(int face) { return face == 0 ? 8 : 16; }
+__device__ __forceinline__ int aow_stride_z(int face) { return face == 0 ? 96 : (face == 1 ? 128 : 192); }
+
+// The shader's loop for one AO ray on the tree itself (no window): semantics of castAo.
+__device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, int hy, int hz, float px, float py, float pz,
+                                                float adx, float ady, float adz, int sx, int sy, int sz, uint32_t nSteps) {
+    Cursor cur;
+    cursor_reset(W, cur);
+    RegionAt g;
+    Pos p;
+    p.x = hx; p.y = hy; p.z = hz;
+    p.tx = px; p.ty = py; p.tz = pz;
+    p.ex = p.ey = p.ez = 0.0f;
+    Ray r;
+    r.sx = sx; r.sy = sy; r.sz = sz;
+    r.adx = adx; r.ady = ady; r.adz = adz;
+    enter_region(W, cur, g, p);
+    uint32_t state = 0u, i = nSteps;
+    while (state != 2u && i-- != 0u) {
+        dda_step_bl(r, p);
+        if (left_region(g, p)) enter_region(W, cur, g, p);
+        state = occlusion_state(W, g.r, p.x, p.y, p.z);
+    }
+    return state != 0u ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_constant__ FrameArgs A, const AoDir* __restrict__ table) {
+    __shared__ uint32_t sWin[AOW_WORDS][AO_THREADS];
+
+    const uint32_t nSeeds = A.counters->ao_seed_count;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nSeeds) return;
+    const uint32_t tid = threadIdx.x;
+    const rc_frame_params& P = A.p;
+    const DeviceWorld& W = A.world;
+    const AoSeed s = A.ao_seeds[t];
+    const int face = (int)(s.face_sign & 3u);
+    const bool negNormal = (s.face_sign & 4u) != 0u;
+    const bool f0 = face == 0, f1 = face == 1;
+    const int strideY = aow_stride_y(face), strideZ = aow_stride_z(face);
+
+    // window origin in bricks (raw coordinates): tangent axes cover h-4 .. h+4, the normal axis
+    // h+1 .. h+5 or h-5 .. h-1
+    const int nOff = negNormal ? -5 : 1;
+    const int b0x = (s.x + (f0 ? nOff : -4)) >> 2;
+    const int b0y = (s.y + (f1 ? nOff : -4)) >> 2;
+    const int b0z = (s.z + ((!f0 && !f1) ? nOff : -4)) >> 2;
+    const int nbx = f0 ? 2 : 3, nby = f1 ? 2 : 3, nbz = (!f0 && !f1) ? 2 : 3;
+
+#pragma unroll
+    for (int k = 0; k < AOW_WORDS; k++) sWin[k][tid] = 0u;
+
+    // fill: one region fetch per brick (siblings share the cached parent node)
+    bool liquid = false;
+    {
+        Cursor cur;
+        cursor_reset(W, cur);
+        Region r;
+        for (int bz = 0; bz < nbz; bz++) {
+            const int wz = wrap_coord(W, (b0z + bz) << 2);
+            for (int by = 0; by < nby; by++) {
+                const int wy = wrap_coord(W, (b0y + by) << 2);
+                for (int bx = 0; bx < nbx; bx++) {
+                    const int wx = wrap_coord(W, (b0x + bx) << 2);
+                    fetch_region(W, cur, wx, wy, wz, r);
+                    if (r.mask == 0ull) continue;
+                    if (r.info & BR_LIQUID) liquid = true;
+                    const int pBrick = (bx << 2) + strideY * (by << 2) + strideZ * (bz << 2);
+#pragma unroll
+                    for (int z2 = 0; z2 < 4; z2++) {
+                        const uint32_t slice = (uint32_t)(r.mask >> (16 * z2)) & 0xFFFFu;
+                        if (slice == 0u) continue;
+#pragma unroll
+                        for (int y2 = 0; y2 < 4; y2++) {
+                            const uint32_t nib = (slice >> (4 * y2)) & 15u;
+                            const int p0 = pBrick + strideY * y2 + strideZ * z2;
+                            sWin[p0 >> 5][tid] |= nib << (p0 & 31);
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    const float fx = (float)s.x, fy = (float)s.y, fz = (float)s.z;
+    // (pos.exact - pos.round) for a positive and for a negative step sign (exact is biased by -1)
+    const float a0x = FSUB(s.ex, fx), a1x = FSUB(FSUB(s.ex, 1.0f), fx);
+    const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
+    const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
+    const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
+    const uint32_t nSamples = P.ao_samples, nSteps = P.ao_steps;
+    const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
+    const uint32_t* win = &sWin[0][tid];
+
+    uint32_t occluded = 0;
+    for (uint32_t k = 0; k < nSamples; k++) {
+        const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
+        const int4 v1 = __ldg(reinterpret_cast<const int4*>(dirs + k) + 1);
+        const float ix = v0.x, iy = v0.y, iz = v0.z;
+        const int qx = __float_as_int(v0.w), qy = v1.x, qz = v1.y;
+        const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
+        // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face]
+        float px = FSUB(adx, FMUL(qx < 0 ? a1x : a0x, ix));
+        float py = FSUB(ady, FMUL(qy < 0 ? a1y : a0y, iy));
+        float pz = FSUB(adz, FMUL(qz < 0 ? a1z : a0z, iz));
+        if (f0) px = FSUB(px, adx);
+        else if (f1) py = FSUB(py, ady);
+        else pz = FSUB(pz, adz);
+
+        // the forced first step must be the one the DDA takes, else the window does not cover the ray
+        const bool firstX = px < py && px < pz;
+        const bool firstY = !firstX && py < pz;
+        const bool firstOk = f0 ? firstX : (f1 ? firstY : (!firstX && !firstY));
+        if (liquid || !firstOk) {
+            occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
+                                       qz < 0 ? -1 : 1, nSteps);
+            continue;
+        }
+        int q = q0;
+        uint32_t hit = 0u;
+        for (uint32_t i = nSteps; i != 0u; i--) {
+            const bool bx = px < py && px < pz;
+            const bool by = !bx && py < pz;
+            const bool bz = !bx && !by;
+            if (bx) { q += qx; px = FADD(px, adx); }
+            if (by) { q += qy; py = FADD(py, ady); }
+            if (bz) { q += qz; pz = FADD(pz, adz); }
+            hit = (win[(q >> 5) * AO_THREADS] >> (q & 31)) & 1u;
+            if (hit) break;
+        }
+        occluded += hit;
+    }
+    const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
+    store_pixel(A, s.pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
+    if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
+}
+
 // Frame composition after the NCCL gather: row y of the frame lives in rank (y/16) % world,
 // local row ((y/16) / world) * 16 + y % 16. One thread per 16-byte (or 4-byte) word of the frame:
 // coalesced reads of whole rows, coalesced writes.
@@ -1055,6 +1222,8 @@ __global__ void detmath_kernel(const float* in, uint32_t n, float* outSin, float
     outExp[t] = det_exp(in[t]);
 }
 
+static AoDir* g_aoTable = nullptr;  // [6][RC_MAX_AO_SAMPLES], device
+
 cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream) {
     if (n > RC_MAX_AO_SAMPLES) return cudaErrorInvalidValue;
     float inv[3 * RC_MAX_AO_SAMPLES];
@@ -1063,7 +1232,44 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
     if (e != cudaSuccess) return e;
     e = cudaMemcpyToSymbolAsync(c_hemi_inv, inv, 3 * n * sizeof(float), 0, cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
+
+    // oriented table of the window kernel: d[face] = sg*up, d[(face+1)%3] = x, d[(face+2)%3] = y
+    static AoDir host[6 * RC_MAX_AO_SAMPLES];
+    for (int face = 0; face < 3; face++) {
+        const int strides[3] = {1, face == 0 ? 8 : 16, face == 0 ? 96 : (face == 1 ? 128 : 192)};
+        for (int neg = 0; neg < 2; neg++)
+            for (uint32_t k = 0; k < n; k++) {
+                float d[3], iv[3];
+                const float up = dirs[3 * k + 2], iup = inv[3 * k + 2];
+                d[face] = neg ? -up : up;
+                iv[face] = neg ? -iup : iup;  // 1/(-up) == -(1/up) exactly
+                d[(face + 1) % 3] = dirs[3 * k + 0];
+                iv[(face + 1) % 3] = inv[3 * k + 0];
+                d[(face + 2) % 3] = dirs[3 * k + 1];
+                iv[(face + 2) % 3] = inv[3 * k + 1];
+                AoDir& o = host[(size_t)(face * 2 + neg) * RC_MAX_AO_SAMPLES + k];
+                o.ix = iv[0];
+                o.iy = iv[1];
+                o.iz = iv[2];
+                o.qx = d[0] < 0.0f ? -strides[0] : strides[0];
+                o.qy = d[1] < 0.0f ? -strides[1] : strides[1];
+                o.qz = d[2] < 0.0f ? -strides[2] : strides[2];
+                o.dx = d[0];
+                o.dy = d[1];
+            }
+    }
+    if (!g_aoTable) {
+        e = cudaMalloc((void**)&g_aoTable, sizeof(host));
+        if (e != cudaSuccess) return e;
+    }
+    e = cudaMemcpyAsync(g_aoTable, host, sizeof(host), cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
     return cudaStreamSynchronize(stream);  // inv[] lives on this stack frame
+}
+
+void release_hemisphere() {
+    if (g_aoTable) cudaFree(g_aoTable);
+    g_aoTable = nullptr;
 }
 
 cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
@@ -1075,7 +1281,11 @@ cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
 
 cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
     if (maxSeeds == 0) return cudaSuccess;
-    ao_kernel<<<(maxSeeds + AO_THREADS - 1u) / AO_THREADS, AO_THREADS, 0, stream>>>(args);
+    const unsigned blocks = (maxSeeds + AO_THREADS - 1u) / AO_THREADS;
+    if (args.p.ao_steps <= AOW_MAX_STEPS && g_aoTable)
+        ao_window_kernel<<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
+    else
+        ao_cached_kernel<<<blocks, AO_THREADS, 0, stream>>>(args);
     return cudaGetLastError();
 }
 

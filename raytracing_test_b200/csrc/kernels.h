@@ -59,6 +59,7 @@ struct FrameArgs {
 
 // Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory.
 cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream);
+void release_hemisphere();
 
 // Primary + shading + shadow kernel. Returns the launch error.
 cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream);

@@ -171,6 +171,7 @@ void rc_shutdown(void) {
     cudaStreamSynchronize(g.stream);
     freeWorld();
     freeFrameBuffers();
+    release_hemisphere();
     if (g.dCounters) cudaFree(g.dCounters);
     if (g.hCounters) cudaFreeHost(g.hCounters);
     g.dCounters = nullptr;
