@@ -46,8 +46,8 @@ HBM_FALLBACK_GBS = 6650.0  # B200_PROFILING.md, used only when MEASURED_PEAKS.js
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
@@ -67,9 +67,23 @@ def hbm_peak():
 def golden_counters(case):
     """Algorithmic bytes of the reference algorithm for exactly this frame, counted by the oracle when
     tests/golden was generated (tools/make_golden.py): 16 B per nodes[] read + 4 B per child-index read."""
+    for name in ("frames.json", "frames_big.json"):  # configs 1-3 / configs 4-5 (tools/make_golden_big.py)
+        try:
+            with open(os.path.join(ROOT, "tests", "golden", name)) as f:
+                cases = json.load(f)["cases"]
+            if case in cases:
+                return cases[case]["counters"]
+        except Exception:
+            pass
+    return None
+
+
+def measured_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full`
+    capture of this workload (profiles/traffic.json, written by tools/ncu_traffic.py); None if not captured."""
     try:
-        with open(os.path.join(ROOT, "tests", "golden", "frames.json")) as f:
-            return json.load(f)["cases"][case]["counters"]
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[workload][kernel]["dram_bytes_per_launch"]
     except Exception:
         return None
 
@@ -353,9 +367,12 @@ def run_b200_arm(args, workload):
     peak, peak_src = hbm_peak()
     counters = golden_counters(golden_case)
     roof, roof_all = None, {}
-    if counters and world_size == 1:
-        ab = counters["algorithmic_bytes"]  # [primary, shadow, ao]
-        per_kernel = {"primary_kernel": ((ab[0] + ab[1]), kern_ms["primary"]), "ao_kernel": (ab[2], kern_ms["ao"])}
+    if counters:
+        # one launch per rank renders 1/world_size of the frame's bands (round-robin: the shares are equal
+        # to within a band), timed on rank 0
+        ab = [b / world_size for b in counters["algorithmic_bytes"]]  # [primary, shadow, ao]
+        ao_name = "ao_window_kernel"  # ao_steps = 5 (<= 5: dense-window kernel; above: ao_cached_kernel)
+        per_kernel = {"primary_kernel": ((ab[0] + ab[1]), kern_ms["primary"]), ao_name: (ab[2], kern_ms["ao"])}
         for name, (bytes_, ms) in per_kernel.items():
             if ms > 0:
                 ach = bytes_ / (ms * 1e-3) / 1e9
@@ -363,12 +380,12 @@ def run_b200_arm(args, workload):
         dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
         if dom:
             roof = {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
-                    "frac": roof_all[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "frac": roof_all[dom]["frac"], "traffic": measured_traffic(workload, dom), "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": roof_all[dom]["algorithmic_bytes_per_launch"],
                     "launch_ms": roof_all[dom]["ms"],
                     "note": "algorithmic bytes = what the REFERENCE algorithm fetches for this frame (16 B per nodes[] read + "
                             "4 B per child index, counted by the oracle); the kernel's cell caching avoids most of them, so "
-                            "frac can exceed 1; real DRAM traffic: see profiles/"}
+                            "frac can exceed 1; traffic = DRAM bytes of one launch from the ncu capture in profiles/"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world_size > 1 else "weak",

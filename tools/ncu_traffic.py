@@ -1,0 +1,43 @@
+"""Writes profiles/traffic.json from an `ncu --page raw --csv` export of ONE workload's capture:
+per kernel, dram__bytes_read.sum + dram__bytes_write.sum per launch (mean over the captured launches).
+bench.py puts the dominant kernel's figure into roofline.traffic.
+    python tools/ncu_traffic.py <workload> <raw.csv>"""
+import csv
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def main():
+    workload, path = sys.argv[1], sys.argv[2]
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    acc = {}
+    for r in rows[2:]:
+        name = r[col["Kernel Name"]].split("(")[0]
+        tot = 0.0
+        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            tot += float(r[col[m]].replace(",", "")) * UNIT[units[col[m]]]
+        t_us = float(r[col["gpu__time_duration.sum"]].replace(",", ""))
+        t_us *= {"us": 1.0, "ms": 1e3, "ns": 1e-3, "s": 1e6}.get(units[col["gpu__time_duration.sum"]], 1.0)
+        a = acc.setdefault(name, {"bytes": [], "us": []})
+        a["bytes"].append(tot)
+        a["us"].append(t_us)
+    out_path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        out = json.load(open(out_path))
+    except Exception:
+        out = {}
+    out[workload] = {k: {"dram_bytes_per_launch": sum(v["bytes"]) / len(v["bytes"]), "launches": len(v["bytes"]),
+                         "ncu_duration_us": sum(v["us"]) / len(v["us"]), "source": os.path.basename(path)}
+                     for k, v in acc.items()}
+    json.dump(out, open(out_path, "w"), indent=1)
+    print(json.dumps(out[workload], indent=1))
+
+
+if __name__ == "__main__":
+    main()
