@@ -189,6 +189,31 @@ int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t h
 int rc_upload_world(const rc_world_desc* desc);
 int rc_world_info_get(rc_world_info* out);
 
+/* Incremental form of the same call, mirroring the BlockPtr.modified protocol: updateSsboData()
+ * pushes exactly the 4 MiB blocks whose `modified` flag putBlock / deleteBlock set
+ * (src/voxel_data/voxel_allocator.hpp:50-56,69-75; setters tetrahexa_tree.cpp:205,215,245,
+ * 260-262,275,278) -- pass the indices of those blocks (i of `glBufferSubData(i << 22, ...)`).
+ * The library diffs them against its copy of the pools, re-flattens only the packed subtrees that
+ * depend on nodes / child arrays that really changed, appends them to the device arrays and patches
+ * the subtree roots in place (n_dirty_* = RC_ALL_BLOCKS: diff every block -- for hosts that do not
+ * trust the flags: deleteBlock's final branch, tetrahexa_tree.cpp:348-353, never sets one): a click costs a few memcmp's and a few KB of upload instead of a full
+ * flatten.  Falls back to a full upload by itself (info->full_rebuild = 1) on the first call, when
+ * the root or the depth changed, or when more than half of the device arrays has become garbage. */
+#define RC_ALL_BLOCKS 0xFFFFFFFFu
+typedef struct rc_update_info {
+    uint32_t full_rebuild;        /* 1: did a full flatten + upload instead */
+    uint32_t changed_ref_nodes;   /* 16-byte nodes that differ from the previous upload */
+    uint32_t changed_ref_arrays;  /* 256-byte child arrays that differ */
+    uint32_t reflattened;         /* packed subtrees re-emitted */
+    uint64_t appended_nodes, appended_voxels;
+    uint64_t garbage_nodes, garbage_voxels;  /* abandoned since the last full upload */
+    uint64_t uploaded_bytes;      /* host -> device bytes of this update */
+    double host_ms;               /* diff + re-flatten */
+    double upload_ms;
+} rc_update_info;
+int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                    const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info);
+
 /* ---- render -------------------------------------------------------------------
  * Replaces the glUniform* block + glDrawArrays of render() (src/main.cpp:83-107).
  * Asynchronous: enqueues the kernels and returns. */
@@ -208,6 +233,21 @@ int rc_frame_stats_get(rc_frame_stats* out);
  * GPUs (NCCL gather over NVLink) without a host round trip. NULL if absent. */
 void* rc_device_image(int format);
 void* rc_device_hits(void);
+
+/* ---- picking -------------------------------------------------------------------
+ * RAY_CASTER::castRayFromCam(steps) (src/ray_caster.cpp:54-87) on the device, over the
+ * uploaded world: the ray from the camera that feeds lookingAtBlock (src/main.cpp:81,89)
+ * and the click handlers (src/input.cpp:143,156).  Same arithmetic: start voxel
+ * trunc(cam_pos), DOUBLE deltas of the fp32 quotients 1/dir, one voxel per step, stops at
+ * the first block that is neither empty nor LIQUID.  getBlock there is the host's
+ * (src/voxel_data/tetrahexa_tree.cpp:113-157): coordinates wrap as a plain torus.
+ * Synchronous (one 1-thread kernel + a 28-byte read-back). */
+typedef struct rc_pick_result {
+    int32_t pos[3];       /* RayResult.pos: pos.round when the loop ended */
+    int32_t last_pos[3];  /* RayResult.lastPos: the voxel before the last step (where a block is placed) */
+    int32_t steps;        /* RayResult.steps: steps left, 0 = nothing hit */
+} rc_pick_result;
+int rc_pick(const float cam_pos[3], const float cam_dir[3], int steps, rc_pick_result* out);
 
 /* The hemisphere direction table the AO kernel uses: gen_hemisphare_distrib.py:4-12
  * with num_pts = n, as 3*n floats (x, y, up) in tangent space. */

@@ -36,6 +36,12 @@ int rc_debug_palette(uint32_t word, uint32_t* out_leaf);
 /* Device det_sin / det_exp (DESIGN.md "deterministic transcendentals"). Host pointers. */
 int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp);
 
+/* Host-only halves of rc_upload_world / rc_update_world with tracking (no CUDA needed): flatten into the
+ * debug world (which = 1 of rc_debug_lookup_host) keeping the update maps, then patch it incrementally. */
+int rc_debug_flatten_host_tracked(const rc_world_desc* desc, rc_world_info* info);
+int rc_debug_update_host(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                         const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info);
+
 /* sizeof of the ABI structs as the library was compiled: rc_world_desc, rc_world_info,
  * rc_frame_params, rc_hit, rc_frame_stats (bindings check their layouts against it). */
 int rc_debug_struct_sizes(uint32_t out[5]);

@@ -1205,6 +1205,49 @@ __global__ void __launch_bounds__(256) compose_kernel(const WordT* __restrict__ 
     }
 }
 
+// RAY_CASTER::castRayFromCam (src/ray_caster.cpp:54-87): fp32 quotient 1/dir widened to double,
+// double deltaPos, the host getBlock's plain torus (W.leak is 0 here).
+struct PickArgs {
+    float px, py, pz, dx, dy, dz;
+    int steps;
+};
+__global__ void pick_kernel(DeviceWorld W, PickArgs a, int* out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const float pos[3] = {a.px, a.py, a.pz}, dir[3] = {a.dx, a.dy, a.dz};
+    int step[3], rnd[3], last[3];
+    double ad[3], t[3];
+    for (int k = 0; k < 3; k++) {
+        step[k] = dir[k] < 0.0f ? -1 : 1;
+        const double delta = (double)__fdiv_rn(1.0f, dir[k]);
+        ad[k] = fabs(delta);
+        rnd[k] = (int)truncf(pos[k]);
+        double exact = (double)pos[k];
+        if (step[k] < 0) exact = __dsub_rn(exact, 1.0);
+        t[k] = __dsub_rn(ad[k], __dmul_rn(__dsub_rn(exact, (double)rnd[k]), delta));
+        last[k] = rnd[k];
+    }
+    Cursor cur;
+    cursor_reset(W, cur);
+    int left = 0, steps = a.steps;
+    while (steps-- > 0) {
+        for (int k = 0; k < 3; k++) last[k] = rnd[k];
+        const int ax = (t[0] < t[1] && t[0] < t[2]) ? 0 : (t[1] < t[2] ? 1 : 2);
+        rnd[ax] += step[ax];
+        t[ax] = __dadd_rn(t[ax], ad[ax]);
+        int shift;
+        const uint32_t w = lookup(W, cur, rnd[0], rnd[1], rnd[2], shift);
+        if (w != 0u && (word_flags(w) & 0x10u) == 0u) {
+            left = steps;
+            break;
+        }
+    }
+    for (int k = 0; k < 3; k++) {
+        out[k] = rnd[k];
+        out[3 + k] = last[k];
+    }
+    out[6] = left;
+}
+
 __global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -1303,6 +1346,14 @@ cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint
     else
         compose_kernel<uint32_t><<<(unsigned)blocks, 256, 0, stream>>>((const uint32_t*)gathered, (uint32_t*)dst,
                                                                        (uint32_t)(rowBytes / 4), height, worldSize, paddedRows);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pick(const DeviceWorld& world, const float* p, const float* d, int steps, int* out7, cudaStream_t stream) {
+    DeviceWorld w = world;
+    w.leak = 0u;  // the host's getBlock shifts signed ints: plain torus
+    PickArgs a{p[0], p[1], p[2], d[0], d[1], d[2], steps};
+    pick_kernel<<<1, 32, 0, stream>>>(w, a, out7);
     return cudaGetLastError();
 }
 

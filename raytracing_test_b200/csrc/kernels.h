@@ -71,6 +71,10 @@ cudaError_t launch_ao(const FrameArgs& args, uint32_t max_seeds, cudaStream_t st
 cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t world_size,
                            uint32_t padded_rows, uint32_t bytes_per_element, cudaStream_t stream);
 
+// castRayFromCam (src/ray_caster.cpp:54-87) as a 1-thread kernel; out = device int[7]: pos, lastPos, steps left.
+cudaError_t launch_pick(const DeviceWorld& world, const float* cam_pos3, const float* cam_dir3, int steps, int* out7,
+                        cudaStream_t stream);
+
 // Single-voxel lookups through the same device code path the kernels use (tests).
 cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,
                           cudaStream_t stream);

@@ -73,9 +73,44 @@ struct PackedWorld {
     uint32_t null_children = 0;
 };
 
+// What rc_update_world needs to patch a packed world in place after the host edited its tree
+// (putBlock / deleteBlock mark whole 4 MiB blocks modified: src/voxel_data/voxel_allocator.hpp:50-56,
+// 69-75).  Kept next to the PackedWorld when tracking is on.
+struct FlattenTracking {
+    bool enabled = false;
+    std::vector<uint8_t> node_mirror, array_mirror;  // the pools as of the last upload / update
+    std::vector<uint32_t> node_owner;    // ref node index  -> packed node whose 16 bytes / voxel run depend on it
+    std::vector<uint32_t> array_owner;   // ref array index -> packed node built from it
+    std::vector<uint32_t> packed_ref;    // packed node -> ref node index
+    std::vector<uint8_t> packed_depth;   // packed node -> depth of that ref node
+    std::vector<uint8_t> packed_dead;    // packed node abandoned by an update (garbage until the next full upload)
+    uint32_t root_index = 0;
+    uint64_t garbage_nodes = 0, garbage_voxels = 0;
+};
+constexpr uint32_t NO_OWNER = 0xFFFFFFFFu;
+
+// Device-side consequences of one update: nodes rewritten in place + the appended tails.
+struct WorldPatch {
+    std::vector<uint32_t> node_index;  // packed nodes whose 16 bytes changed in place
+    uint64_t nodes_before = 0, voxels_before = 0, palette_before = 0;  // arrays grew from these sizes
+};
+
+struct UpdateStats {
+    uint32_t changed_ref_nodes = 0, changed_ref_arrays = 0, reflattened = 0;
+};
+
 // Host-side flattener: reference pools -> PackedWorld. Returns RC_OK or a negative
-// rc_status with a message in err.
-int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err);
+// rc_status with a message in err.  With `track`, also fills the maps an update needs.
+int flatten_world(const rc_world_desc& desc, PackedWorld& out, std::string& err, FlattenTracking* track = nullptr);
+
+// Incremental re-flatten after the host modified the listed 4 MiB blocks. Finds the 16-byte nodes /
+// 256-byte child arrays that really changed (diff against the mirror), re-emits the packed subtrees
+// that depend on them at the END of the packed arrays (children runs stay contiguous; the old runs
+// become garbage) and rewrites the subtree roots in place.  Returns RC_OK, a negative rc_status, or
+// 1 = "do a full flatten instead" (no tracking yet, depth / root changed, root edited, too much garbage).
+int update_world(const rc_world_desc& desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                 const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, PackedWorld& pw,
+                 FlattenTracking& tr, WorldPatch& patch, UpdateStats& stats, std::string& err);
 
 // Host-side lookup in the packed form (used by the flattener's self-check and by
 // tests through rc_debug_lookup). Returns the material word, 0 = empty;

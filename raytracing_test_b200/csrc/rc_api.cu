@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <string>
 #include <vector>
@@ -34,8 +35,11 @@ struct Context {
     uint4* dPalette = nullptr;
     DeviceWorld world{};
     rc_world_info info{};
-    PackedWorld packed;       // host copy of the uploaded world (debug lookups)
+    PackedWorld packed;       // host copy of the uploaded world (debug lookups, incremental updates)
+    FlattenTracking tracking; // maps + pool mirror for rc_update_world (built by its first call)
+    size_t capNodes = 0, capVoxels = 0, capPalette = 0;  // device array capacities (elements)
     PackedWorld debugPacked;  // result of rc_debug_flatten_host (CPU-only tests)
+    FlattenTracking debugTracking;
 
     // frame buffers (grown on demand)
     size_t pixelCapacity = 0;
@@ -46,6 +50,8 @@ struct Context {
     size_t f32Capacity = 0, hitCapacity = 0, seedCapacity = 0;
     FrameCounters* dCounters = nullptr;
     FrameCounters* hCounters = nullptr;  // pinned
+    int* dPick = nullptr;
+    int* hPick = nullptr;  // pinned
 
     // last frame
     bool haveFrame = false;
@@ -176,6 +182,10 @@ void rc_shutdown(void) {
     if (g.hCounters) cudaFreeHost(g.hCounters);
     g.dCounters = nullptr;
     g.hCounters = nullptr;
+    if (g.dPick) cudaFree(g.dPick);
+    if (g.hPick) cudaFreeHost(g.hPick);
+    g.dPick = nullptr;
+    g.hPick = nullptr;
     if (g.evStart) cudaEventDestroy(g.evStart);
     if (g.evPrimary) cudaEventDestroy(g.evPrimary);
     if (g.evEnd) cudaEventDestroy(g.evEnd);
@@ -183,6 +193,7 @@ void rc_shutdown(void) {
     if (g.ownStream) cudaStreamDestroy(g.ownStream);
     g.ownStream = g.stream = nullptr;
     g.packed = PackedWorld();
+    g.tracking = FlattenTracking();
     g.initialized = false;
 }
 
@@ -238,26 +249,19 @@ int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t h
     return RC_OK;
 }
 
-int rc_upload_world(const rc_world_desc* desc) {
-    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_upload_world: call rc_init first");
-    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_upload_world: null desc");
-    CUDA_TRY(cudaSetDevice(g.device));
-    auto t0 = std::chrono::steady_clock::now();
-    PackedWorld pw;
-    std::string err;
-    int rcode = flatten_world(*desc, pw, err);
-    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+// Replaces the device world with pw (arrays get slack for later appends) and fills g.info.
+static int installWorld(const rc_world_desc* desc, PackedWorld&& pw, double flattenMs) {
     auto t1 = std::chrono::steady_clock::now();
-
     CUDA_TRY(cudaStreamSynchronize(g.stream));  // no frame may still read the old world
     freeWorld();
-    const size_t nodeBytes = pw.nodes.size() * sizeof(PackedNode);
-    const size_t voxBytes = (pw.voxels.size() ? pw.voxels.size() : 1) * sizeof(uint32_t);
-    const size_t palBytes = (pw.palette.size() ? pw.palette.size() : 1) * sizeof(PaletteEntry);
-    CUDA_TRY(cudaMalloc((void**)&g.dNodes, nodeBytes));
-    CUDA_TRY(cudaMalloc((void**)&g.dVoxels, voxBytes));
-    CUDA_TRY(cudaMalloc((void**)&g.dPalette, palBytes));
-    CUDA_TRY(cudaMemcpyAsync(g.dNodes, pw.nodes.data(), nodeBytes, cudaMemcpyHostToDevice, g.stream));
+    g.capNodes = pw.nodes.size() + pw.nodes.size() / 4 + 4096;
+    g.capVoxels = pw.voxels.size() + pw.voxels.size() / 4 + 65536;
+    g.capPalette = pw.palette.size() * 2 + 256;
+    CUDA_TRY(cudaMalloc((void**)&g.dNodes, g.capNodes * sizeof(PackedNode)));
+    CUDA_TRY(cudaMalloc((void**)&g.dVoxels, g.capVoxels * sizeof(uint32_t)));
+    CUDA_TRY(cudaMalloc((void**)&g.dPalette, g.capPalette * sizeof(PaletteEntry)));
+    CUDA_TRY(cudaMemcpyAsync(g.dNodes, pw.nodes.data(), pw.nodes.size() * sizeof(PackedNode), cudaMemcpyHostToDevice,
+                             g.stream));
     if (!pw.voxels.empty())
         CUDA_TRY(cudaMemcpyAsync(g.dVoxels, pw.voxels.data(), pw.voxels.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
                                  g.stream));
@@ -285,10 +289,129 @@ int rc_upload_world(const rc_world_desc* desc) {
     g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
     g.info.max_depth = pw.max_depth;
     g.info.null_children = pw.null_children;
-    g.info.flatten_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    g.info.flatten_ms = flattenMs;
     g.info.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
     g.packed = std::move(pw);
     g.haveWorld = true;
+    return RC_OK;
+}
+
+int rc_upload_world(const rc_world_desc* desc) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_upload_world: call rc_init first");
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_upload_world: null desc");
+    CUDA_TRY(cudaSetDevice(g.device));
+    auto t0 = std::chrono::steady_clock::now();
+    PackedWorld pw;
+    std::string err;
+    g.tracking = FlattenTracking();  // the maps of the previous world are void; rc_update_world rebuilds them
+    int rcode = flatten_world(*desc, pw, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    auto t1 = std::chrono::steady_clock::now();
+    return installWorld(desc, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
+}
+
+// Contiguous runs of the sorted indices (gaps up to 256 nodes are copied along: fewer, larger copies).
+static int uploadNodeRanges(std::vector<uint32_t> idx, uint64_t limit, uint64_t* bytes) {
+    std::sort(idx.begin(), idx.end());
+    size_t i = 0;
+    while (i < idx.size()) {
+        if (idx[i] >= limit) break;  // appended nodes travel with the tail copy
+        size_t j = i;
+        while (j + 1 < idx.size() && idx[j + 1] < limit && idx[j + 1] - idx[j] <= 256) j++;
+        const size_t first = idx[i], count = idx[j] - idx[i] + 1;
+        CUDA_TRY(cudaMemcpyAsync(g.dNodes + first, g.packed.nodes.data() + first, count * sizeof(PackedNode),
+                                 cudaMemcpyHostToDevice, g.stream));
+        *bytes += count * sizeof(PackedNode);
+        i = j + 1;
+    }
+    return RC_OK;
+}
+
+int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                    const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_update_world: call rc_init first");
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_update_world: null desc");
+    CUDA_TRY(cudaSetDevice(g.device));
+    rc_update_info ui;
+    memset(&ui, 0, sizeof(ui));
+    auto t0 = std::chrono::steady_clock::now();
+    std::string err;
+    WorldPatch patch;
+    UpdateStats st;
+    int rcode = 1;
+    if (g.haveWorld && g.tracking.enabled)
+        rcode = update_world(*desc, dirty_node_blocks, n_dirty_node_blocks, dirty_array_blocks, n_dirty_array_blocks, g.packed,
+                             g.tracking, patch, st, err);
+    if (rcode < 0) {
+        g.tracking = FlattenTracking();  // g.packed may be half patched: force a full flatten next time
+        return fail(rcode, "%s", err.c_str());
+    }
+    if (rcode == 1) {
+        // full flatten with tracking: the baseline later updates diff against
+        PackedWorld pw;
+        FlattenTracking tr;
+        rcode = flatten_world(*desc, pw, err, &tr);
+        if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+        auto t1 = std::chrono::steady_clock::now();
+        ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        rcode = installWorld(desc, std::move(pw), ui.host_ms);
+        if (rcode != RC_OK) return rcode;
+        g.tracking = std::move(tr);
+        ui.full_rebuild = 1;
+        ui.uploaded_bytes = g.info.packed_bytes;
+        ui.upload_ms = g.info.upload_ms;
+        if (info) *info = ui;
+        return RC_OK;
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    const PackedWorld& pw = g.packed;
+    ui.changed_ref_nodes = st.changed_ref_nodes;
+    ui.changed_ref_arrays = st.changed_ref_arrays;
+    ui.reflattened = st.reflattened;
+    ui.appended_nodes = pw.nodes.size() - patch.nodes_before;
+    ui.appended_voxels = pw.voxels.size() - patch.voxels_before;
+    ui.garbage_nodes = g.tracking.garbage_nodes;
+    ui.garbage_voxels = g.tracking.garbage_voxels;
+
+    // device side, ordered after the frames already enqueued on the stream
+    if (pw.nodes.size() > g.capNodes || pw.voxels.size() > g.capVoxels || pw.palette.size() > g.capPalette) {
+        // out of slack: new, larger arrays with everything copied again (still no flatten)
+        PackedWorld copy = pw;
+        rcode = installWorld(desc, std::move(copy), 0.0);
+        if (rcode != RC_OK) return rcode;
+        ui.uploaded_bytes = g.info.packed_bytes;
+    } else {
+        if ((rcode = uploadNodeRanges(patch.node_index, patch.nodes_before, &ui.uploaded_bytes)) != RC_OK) return rcode;
+        if (pw.nodes.size() > patch.nodes_before) {
+            const size_t n = pw.nodes.size() - patch.nodes_before;
+            CUDA_TRY(cudaMemcpyAsync(g.dNodes + patch.nodes_before, pw.nodes.data() + patch.nodes_before, n * sizeof(PackedNode),
+                                     cudaMemcpyHostToDevice, g.stream));
+            ui.uploaded_bytes += n * sizeof(PackedNode);
+        }
+        if (pw.voxels.size() > patch.voxels_before) {
+            const size_t n = pw.voxels.size() - patch.voxels_before;
+            CUDA_TRY(cudaMemcpyAsync(g.dVoxels + patch.voxels_before, pw.voxels.data() + patch.voxels_before, n * 4,
+                                     cudaMemcpyHostToDevice, g.stream));
+            ui.uploaded_bytes += n * 4;
+        }
+        if (pw.palette.size() > patch.palette_before) {
+            const size_t n = pw.palette.size() - patch.palette_before;
+            CUDA_TRY(cudaMemcpyAsync(g.dPalette + patch.palette_before, pw.palette.data() + patch.palette_before,
+                                     n * sizeof(PaletteEntry), cudaMemcpyHostToDevice, g.stream));
+            ui.uploaded_bytes += n * sizeof(PaletteEntry);
+        }
+        CUDA_TRY(cudaStreamSynchronize(g.stream));  // the copies read pageable host vectors
+        g.world.n_nodes = (uint32_t)pw.nodes.size();
+        g.info.packed_nodes = pw.nodes.size();
+        g.info.packed_voxels = pw.voxels.size();
+        g.info.packed_materials = pw.palette.size();
+        g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
+        g.info.ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+    }
+    auto t2 = std::chrono::steady_clock::now();
+    ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    ui.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
+    if (info) *info = ui;
     return RC_OK;
 }
 
@@ -456,6 +579,24 @@ void* rc_device_hits(void) {
     return g.dHits;
 }
 
+int rc_pick(const float cam_pos[3], const float cam_dir[3], int steps, rc_pick_result* out) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_pick: call rc_init first");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_pick: call rc_upload_world first");
+    if (!cam_pos || !cam_dir || !out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_pick: null argument");
+    CUDA_TRY(cudaSetDevice(g.device));
+    if (!g.dPick) CUDA_TRY(cudaMalloc((void**)&g.dPick, 7 * sizeof(int)));
+    if (!g.hPick) CUDA_TRY(cudaMallocHost((void**)&g.hPick, 7 * sizeof(int)));
+    CUDA_TRY(launch_pick(g.world, cam_pos, cam_dir, steps, g.dPick, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.hPick, g.dPick, 7 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    for (int k = 0; k < 3; k++) {
+        out->pos[k] = g.hPick[k];
+        out->last_pos[k] = g.hPick[3 + k];
+    }
+    out->steps = g.hPick[6];
+    return RC_OK;
+}
+
 int rc_hemisphere_table(uint32_t n, float* out) {
     if (n == 0 || n > RC_MAX_AO_SAMPLES || !out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_hemisphere_table: n=%u", n);
     hemisphereTable(n, out);
@@ -545,6 +686,66 @@ int rc_debug_flatten_host(const rc_world_desc* desc, rc_world_info* info) {
         info->null_children = pw.null_children;
     }
     g.debugPacked = std::move(pw);
+    return RC_OK;
+}
+
+static void fillInfo(const rc_world_desc* desc, const PackedWorld& pw, rc_world_info* info) {
+    memset(info, 0, sizeof(*info));
+    info->ref_nodes = pw.ref_nodes;
+    info->ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+    info->packed_nodes = pw.nodes.size();
+    info->packed_voxels = pw.voxels.size();
+    info->packed_materials = pw.palette.size();
+    info->packed_bytes = pw.nodes.size() * 16 + pw.voxels.size() * 4 + pw.palette.size() * 16;
+    info->max_depth = pw.max_depth;
+    info->null_children = pw.null_children;
+}
+
+int rc_debug_flatten_host_tracked(const rc_world_desc* desc, rc_world_info* info) {
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_flatten_host_tracked: null desc");
+    PackedWorld pw;
+    FlattenTracking tr;
+    std::string err;
+    int rcode = flatten_world(*desc, pw, err, &tr);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    if (info) fillInfo(desc, pw, info);
+    g.debugPacked = std::move(pw);
+    g.debugTracking = std::move(tr);
+    return RC_OK;
+}
+
+int rc_debug_update_host(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                         const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info) {
+    if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_update_host: null desc");
+    if (g.debugPacked.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_update_host: no tracked debug world");
+    std::string err;
+    WorldPatch patch;
+    UpdateStats st;
+    auto t0 = std::chrono::steady_clock::now();
+    int rcode = update_world(*desc, dirty_node_blocks, n_dirty_node_blocks, dirty_array_blocks, n_dirty_array_blocks,
+                             g.debugPacked, g.debugTracking, patch, st, err);
+    if (rcode < 0) return fail(rcode, "%s", err.c_str());
+    rc_update_info ui;
+    memset(&ui, 0, sizeof(ui));
+    if (rcode == 1) {
+        PackedWorld pw;
+        FlattenTracking tr;
+        rcode = flatten_world(*desc, pw, err, &tr);
+        if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+        g.debugPacked = std::move(pw);
+        g.debugTracking = std::move(tr);
+        ui.full_rebuild = 1;
+    } else {
+        ui.changed_ref_nodes = st.changed_ref_nodes;
+        ui.changed_ref_arrays = st.changed_ref_arrays;
+        ui.reflattened = st.reflattened;
+        ui.appended_nodes = g.debugPacked.nodes.size() - patch.nodes_before;
+        ui.appended_voxels = g.debugPacked.voxels.size() - patch.voxels_before;
+        ui.garbage_nodes = g.debugTracking.garbage_nodes;
+        ui.garbage_voxels = g.debugTracking.garbage_voxels;
+    }
+    ui.host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (info) *info = ui;
     return RC_OK;
 }
 

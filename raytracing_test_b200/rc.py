@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(PKG_DIR, "librc.so")
 
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F = 1, 2, 4, 8
 RC_RGBA8, RC_RGBA32F = 0, 1
+RC_ALL_BLOCKS = 0xFFFFFFFF
 KIND_SKY, KIND_HIT, KIND_CAMERA_INSIDE, KIND_CROSSHAIR, KIND_HIGHLIGHT, KIND_DEBUG = range(6)
 HF_SHADOWED, HF_REFLECTED, HF_REFRACTED, HF_FACING_SUN = 1, 2, 4, 8
 BAND_ROWS = 16
@@ -52,6 +53,19 @@ class WorldInfo(ctypes.Structure):
         ("packed_materials", ctypes.c_uint64), ("packed_bytes", ctypes.c_uint64),
         ("max_depth", ctypes.c_uint32), ("null_children", ctypes.c_uint32),
         ("flatten_ms", ctypes.c_double), ("upload_ms", ctypes.c_double),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class UpdateInfo(ctypes.Structure):
+    _fields_ = [
+        ("full_rebuild", ctypes.c_uint32), ("changed_ref_nodes", ctypes.c_uint32),
+        ("changed_ref_arrays", ctypes.c_uint32), ("reflattened", ctypes.c_uint32),
+        ("appended_nodes", ctypes.c_uint64), ("appended_voxels", ctypes.c_uint64),
+        ("garbage_nodes", ctypes.c_uint64), ("garbage_voxels", ctypes.c_uint64),
+        ("uploaded_bytes", ctypes.c_uint64), ("host_ms", ctypes.c_double), ("upload_ms", ctypes.c_double),
     ]
 
     def as_dict(self):
@@ -97,6 +111,8 @@ ABI = {
                                          ctypes.c_uint32]),
     "rc_upload_world": (ctypes.c_int, [ctypes.POINTER(WorldDesc)]),
     "rc_world_info_get": (ctypes.c_int, [ctypes.POINTER(WorldInfo)]),
+    "rc_update_world": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32,
+                                   ctypes.POINTER(UpdateInfo)]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
@@ -105,8 +121,12 @@ ABI = {
     "rc_device_image": (ctypes.c_void_p, [ctypes.c_int]),
     "rc_device_hits": (ctypes.c_void_p, []),
     "rc_hemisphere_table": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_pick": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
     # rc_debug.h
     "rc_debug_flatten_host": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.POINTER(WorldInfo)]),
+    "rc_debug_flatten_host_tracked": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.POINTER(WorldInfo)]),
+    "rc_debug_update_host": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32,
+                                   ctypes.POINTER(UpdateInfo)]),
     "rc_debug_lookup_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "rc_debug_lookup_host_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p,
@@ -275,6 +295,22 @@ class RayCaster:
         _check(self.lib, self.lib.rc_hemisphere_table(n, out.ctypes.data))
         return out
 
+    def update_world(self, desc, dirty_node_blocks, dirty_array_blocks):
+        """rc_update_world: the blocks updateSsboData() would push (BlockPtr.modified) -> UpdateInfo."""
+        dn, nn, da, na = _dirty_args(dirty_node_blocks, dirty_array_blocks)
+        info = UpdateInfo()
+        _check(self.lib, self.lib.rc_update_world(ctypes.byref(desc), dn.ctypes.data, nn, da.ctypes.data, na,
+                                                  ctypes.byref(info)))
+        return info
+
+    def pick(self, cam_pos, cam_dir, steps=30):
+        """rc_pick = RAY_CASTER::castRayFromCam(steps) on the device -> (pos, lastPos, steps left)."""
+        p = np.ascontiguousarray(cam_pos, dtype=np.float32)
+        d = np.ascontiguousarray(cam_dir, dtype=np.float32)
+        out = np.zeros(7, dtype=np.int32)
+        _check(self.lib, self.lib.rc_pick(p.ctypes.data, d.ctypes.data, int(steps), out.ctypes.data))
+        return out[0:3].copy(), out[3:6].copy(), int(out[6])
+
     def device_image_ptr(self, fmt=RC_RGBA8):
         return self.lib.rc_device_image(fmt)
 
@@ -322,6 +358,31 @@ def flatten_host(desc):
     lib = load_library()
     info = WorldInfo()
     _check(lib, lib.rc_debug_flatten_host(ctypes.byref(desc), ctypes.byref(info)))
+    return info
+
+
+def _dirty_args(dirty_node_blocks, dirty_array_blocks):
+    """None = RC_ALL_BLOCKS (diff every block)."""
+    dn = np.ascontiguousarray([] if dirty_node_blocks is None else dirty_node_blocks, dtype=np.uint32)
+    da = np.ascontiguousarray([] if dirty_array_blocks is None else dirty_array_blocks, dtype=np.uint32)
+    return (dn, RC_ALL_BLOCKS if dirty_node_blocks is None else dn.size,
+            da, RC_ALL_BLOCKS if dirty_array_blocks is None else da.size)
+
+
+def flatten_host_tracked(desc):
+    """CPU-only: full flatten keeping the maps rc_update_world needs (debug world, which=1)."""
+    lib = load_library()
+    info = WorldInfo()
+    _check(lib, lib.rc_debug_flatten_host_tracked(ctypes.byref(desc), ctypes.byref(info)))
+    return info
+
+
+def update_host(desc, dirty_node_blocks, dirty_array_blocks):
+    """CPU-only: the host half of rc_update_world on the tracked debug world."""
+    lib = load_library()
+    dn, nn, da, na = _dirty_args(dirty_node_blocks, dirty_array_blocks)
+    info = UpdateInfo()
+    _check(lib, lib.rc_debug_update_host(ctypes.byref(desc), dn.ctypes.data, nn, da.ctypes.data, na, ctypes.byref(info)))
     return info
 
 

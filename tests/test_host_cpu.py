@@ -275,3 +275,18 @@ def test_deep_world_extension(rcmod):
     a, b = w.get_blocks(probe), w6.get_blocks(probe)
     same = ~((probe[:, 0] >= 20) & (probe[:, 0] < 36) & (probe[:, 2] >= 200) & (probe[:, 2] < 216))  # start-up block level differs
     assert np.array_equal(a[same], b[same])
+
+
+def test_incremental_update_host_side_edit_scenario():
+    """rc_update_world's host half (diff of the modified blocks, re-emission of the changed runs) over the
+    reference's own putBlock / deleteBlock and updateSsboData(): tests/edit_scenario.py, in a subprocess
+    because it edits the reference's process-global tree."""
+    import subprocess
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    if not os.path.exists(os.path.join(here, "..", "oracle", "_ref", "libref_world.so")):
+        pytest.skip("oracle/_ref/libref_world.so not built")
+    r = subprocess.run([sys.executable, os.path.join(here, "edit_scenario.py"), "cpu"], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0 and "edit scenario ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -142,3 +142,37 @@ def test_device_detmath_matches_oracle(ob, caster):
     eo = np.array([L.oracle_expf(float(v)) for v in x], dtype=np.float32)
     assert np.array_equal(s.view(np.uint32), so.view(np.uint32))
     assert np.array_equal(e.view(np.uint32), eo.view(np.uint32))
+
+
+def test_gpu_pick_matches_reference_castRayFromCam(rcmod, caster, ref_world, defaults):
+    """rc_pick against the reference's own RAY_CASTER::castRayFromCam (src/ray_caster.cpp:54-87,
+    compiled unmodified into oracle/_ref): pos, lastPos and steps left, hit or miss."""
+    pos, d, _ = defaults
+    cases = [(pos, d, 30)]
+    rng = np.random.default_rng(11)
+    for (origin, yaw, pitch) in CAMERAS:
+        cases.append((np.array(origin, dtype=np.float32), camera_dir(yaw, pitch), 30))
+    for _ in range(200):
+        o = np.array([rng.uniform(1, 199), rng.uniform(15, 70), rng.uniform(1, 199)], dtype=np.float32)
+        cases.append((o, camera_dir(rng.uniform(-180, 180), rng.uniform(-80, 80)), int(rng.integers(1, 120))))
+    hits = 0
+    for (o, dd, n) in cases:
+        rp, rl, rs = ref_world.pick(o, dd, n)
+        gp, gl, gs = caster.pick(o, dd, n)
+        assert (tuple(gp), tuple(gl), gs) == (tuple(rp), tuple(rl), rs), f"pick from {o} dir {dd} steps {n}"
+        hits += rs > 0
+    assert hits > 20
+
+
+def test_incremental_world_update_edit_scenario_on_device():
+    """rc_update_world end to end (tests/edit_scenario.py gpu, own process: it edits the reference's global
+    tree): after every round of the reference's putBlock / deleteBlock + updateSsboData(), device lookups
+    equal the shader's getBlock over the SSBO view and a frame equals the oracle's, record for record."""
+    import os
+    import subprocess
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, os.path.join(here, "edit_scenario.py"), "gpu"], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0 and "edit scenario ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
