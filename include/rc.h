@@ -214,6 +214,20 @@ typedef struct rc_update_info {
 int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
                     const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info);
 
+/* ---- flattened world as a file ---------------------------------------------------
+ * The reference has no on-disk format (its world lives only in the two malloc'd pools and is
+ * regenerated by genWorld() at every start, src/main.cpp:188-190).  rc_save_world writes the
+ * flattened (device) form of the uploaded world -- 64-byte header, the three arrays, FNV-1a
+ * checksum; rc_load_world installs such a file directly, without the host pools and without
+ * a flatten (checksum and every child run are validated first).  A loaded world has no update
+ * baseline: the first rc_update_world after it is a full upload. */
+int rc_save_world(const char* path);
+int rc_load_world(const char* path);
+
+/* The last frame (RC_RGBA8) as a binary PPM, top row first: the headless stand-in for looking at
+ * the window. Synchronises like rc_read_image. Sharded frames: this rank's rows, others black. */
+int rc_write_ppm(const char* path);
+
 /* ---- render -------------------------------------------------------------------
  * Replaces the glUniform* block + glDrawArrays of render() (src/main.cpp:83-107).
  * Asynchronous: enqueues the kernels and returns. */

@@ -42,6 +42,10 @@ int rc_debug_flatten_host_tracked(const rc_world_desc* desc, rc_world_info* info
 int rc_debug_update_host(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
                          const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info);
 
+/* Host-only halves of rc_save_world / rc_load_world on the debug world (which = 1). */
+int rc_debug_save_host(const char* path);
+int rc_debug_load_host(const char* path, rc_world_info* info);
+
 /* sizeof of the ABI structs as the library was compiled: rc_world_desc, rc_world_info,
  * rc_frame_params, rc_hit, rc_frame_stats (bindings check their layouts against it). */
 int rc_debug_struct_sizes(uint32_t out[5]);

@@ -112,6 +112,11 @@ int update_world(const rc_world_desc& desc, const uint32_t* dirty_node_blocks, u
                  const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, PackedWorld& pw,
                  FlattenTracking& tr, WorldPatch& patch, UpdateStats& stats, std::string& err);
 
+// world_blob.cpp: the flattened world as a file (header + the three arrays + FNV-1a checksum) and frames as PPM.
+int save_packed(const PackedWorld& w, const char* path, std::string& err);
+int load_packed(PackedWorld& w, const char* path, std::string& err);
+int write_ppm(const char* path, const uint8_t* rgba8_bottom_up, uint32_t width, uint32_t height, std::string& err);
+
 // Host-side lookup in the packed form (used by the flattener's self-check and by
 // tests through rc_debug_lookup). Returns the material word, 0 = empty;
 // *cell_shift = log2 of the edge of the uniform cell that contains the voxel.

@@ -250,7 +250,7 @@ int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t h
 }
 
 // Replaces the device world with pw (arrays get slack for later appends) and fills g.info.
-static int installWorld(const rc_world_desc* desc, PackedWorld&& pw, double flattenMs) {
+static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     auto t1 = std::chrono::steady_clock::now();
     CUDA_TRY(cudaStreamSynchronize(g.stream));  // no frame may still read the old world
     freeWorld();
@@ -282,7 +282,7 @@ static int installWorld(const rc_world_desc* desc, PackedWorld&& pw, double flat
 
     memset(&g.info, 0, sizeof(g.info));
     g.info.ref_nodes = pw.ref_nodes;
-    g.info.ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+    g.info.ref_bytes = refBytes;
     g.info.packed_nodes = pw.nodes.size();
     g.info.packed_voxels = pw.voxels.size();
     g.info.packed_materials = pw.palette.size();
@@ -307,7 +307,7 @@ int rc_upload_world(const rc_world_desc* desc) {
     int rcode = flatten_world(*desc, pw, err);
     if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
     auto t1 = std::chrono::steady_clock::now();
-    return installWorld(desc, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
+    return installWorld(desc->node_bytes_used + desc->array_bytes_used, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
 }
 
 // Contiguous runs of the sorted indices (gaps up to 256 nodes are copied along: fewer, larger copies).
@@ -354,7 +354,7 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
         if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
         auto t1 = std::chrono::steady_clock::now();
         ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
-        rcode = installWorld(desc, std::move(pw), ui.host_ms);
+        rcode = installWorld(desc->node_bytes_used + desc->array_bytes_used, std::move(pw), ui.host_ms);
         if (rcode != RC_OK) return rcode;
         g.tracking = std::move(tr);
         ui.full_rebuild = 1;
@@ -377,7 +377,7 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
     if (pw.nodes.size() > g.capNodes || pw.voxels.size() > g.capVoxels || pw.palette.size() > g.capPalette) {
         // out of slack: new, larger arrays with everything copied again (still no flatten)
         PackedWorld copy = pw;
-        rcode = installWorld(desc, std::move(copy), 0.0);
+        rcode = installWorld(desc->node_bytes_used + desc->array_bytes_used, std::move(copy), 0.0);
         if (rcode != RC_OK) return rcode;
         ui.uploaded_bytes = g.info.packed_bytes;
     } else {
@@ -412,6 +412,40 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
     ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     ui.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
     if (info) *info = ui;
+    return RC_OK;
+}
+
+int rc_save_world(const char* path) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_save_world: call rc_init first");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_save_world: no world uploaded");
+    std::string err;
+    int rcode = save_packed(g.packed, path, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    return RC_OK;
+}
+
+int rc_load_world(const char* path) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_load_world: call rc_init first");
+    CUDA_TRY(cudaSetDevice(g.device));
+    auto t0 = std::chrono::steady_clock::now();
+    PackedWorld pw;
+    std::string err;
+    int rcode = load_packed(pw, path, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    g.tracking = FlattenTracking();
+    auto t1 = std::chrono::steady_clock::now();
+    return installWorld(0, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
+}
+
+int rc_write_ppm(const char* path) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_write_ppm: call rc_init first");
+    if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_write_ppm: no frame rendered");
+    std::vector<uint8_t> img((size_t)g.frame.width * g.frame.height * 4, 0);
+    int rcode = rc_read_image(img.data(), img.size(), RC_RGBA8);
+    if (rcode != RC_OK) return rcode;
+    std::string err;
+    rcode = write_ppm(path, img.data(), g.frame.width, g.frame.height, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
     return RC_OK;
 }
 
@@ -746,6 +780,28 @@ int rc_debug_update_host(const rc_world_desc* desc, const uint32_t* dirty_node_b
     }
     ui.host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (info) *info = ui;
+    return RC_OK;
+}
+
+int rc_debug_save_host(const char* path) {
+    std::string err;
+    int rcode = save_packed(g.debugPacked, path, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    return RC_OK;
+}
+
+int rc_debug_load_host(const char* path, rc_world_info* info) {
+    PackedWorld pw;
+    std::string err;
+    int rcode = load_packed(pw, path, err);
+    if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
+    if (info) {
+        rc_world_desc none;
+        memset(&none, 0, sizeof(none));
+        fillInfo(&none, pw, info);
+    }
+    g.debugPacked = std::move(pw);
+    g.debugTracking = FlattenTracking();
     return RC_OK;
 }
 

@@ -113,6 +113,9 @@ ABI = {
     "rc_world_info_get": (ctypes.c_int, [ctypes.POINTER(WorldInfo)]),
     "rc_update_world": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32,
                                    ctypes.POINTER(UpdateInfo)]),
+    "rc_save_world": (ctypes.c_int, [ctypes.c_char_p]),
+    "rc_load_world": (ctypes.c_int, [ctypes.c_char_p]),
+    "rc_write_ppm": (ctypes.c_int, [ctypes.c_char_p]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
@@ -127,6 +130,8 @@ ABI = {
     "rc_debug_flatten_host_tracked": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.POINTER(WorldInfo)]),
     "rc_debug_update_host": (ctypes.c_int, [ctypes.POINTER(WorldDesc), ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32,
                                    ctypes.POINTER(UpdateInfo)]),
+    "rc_debug_save_host": (ctypes.c_int, [ctypes.c_char_p]),
+    "rc_debug_load_host": (ctypes.c_int, [ctypes.c_char_p, ctypes.POINTER(WorldInfo)]),
     "rc_debug_lookup_host": (ctypes.c_int, [ctypes.c_int, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "rc_debug_lookup_host_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p,
@@ -303,6 +308,18 @@ class RayCaster:
                                                   ctypes.byref(info)))
         return info
 
+    def save_world(self, path):
+        _check(self.lib, self.lib.rc_save_world(os.fsencode(path)))
+
+    def load_world(self, path):
+        _check(self.lib, self.lib.rc_load_world(os.fsencode(path)))
+        info = WorldInfo()
+        _check(self.lib, self.lib.rc_world_info_get(ctypes.byref(info)))
+        return info
+
+    def write_ppm(self, path):
+        _check(self.lib, self.lib.rc_write_ppm(os.fsencode(path)))
+
     def pick(self, cam_pos, cam_dir, steps=30):
         """rc_pick = RAY_CASTER::castRayFromCam(steps) on the device -> (pos, lastPos, steps left)."""
         p = np.ascontiguousarray(cam_pos, dtype=np.float32)
@@ -367,6 +384,20 @@ def _dirty_args(dirty_node_blocks, dirty_array_blocks):
     da = np.ascontiguousarray([] if dirty_array_blocks is None else dirty_array_blocks, dtype=np.uint32)
     return (dn, RC_ALL_BLOCKS if dirty_node_blocks is None else dn.size,
             da, RC_ALL_BLOCKS if dirty_array_blocks is None else da.size)
+
+
+def save_host(path):
+    """CPU-only: rc_save_world's writer on the debug world (which=1)."""
+    lib = load_library()
+    _check(lib, lib.rc_debug_save_host(os.fsencode(path)))
+
+
+def load_host(path):
+    """CPU-only: rc_load_world's reader + validation into the debug world (which=1)."""
+    lib = load_library()
+    info = WorldInfo()
+    _check(lib, lib.rc_debug_load_host(os.fsencode(path), ctypes.byref(info)))
+    return info
 
 
 def flatten_host_tracked(desc):

@@ -290,3 +290,31 @@ def test_incremental_update_host_side_edit_scenario():
     r = subprocess.run([sys.executable, os.path.join(here, "edit_scenario.py"), "cpu"], capture_output=True, text=True,
                        timeout=300)
     assert r.returncode == 0 and "edit scenario ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_world_blob_round_trip_and_validation(rcmod, world_desc, tmp_path):
+    """rc_save_world / rc_load_world host halves: a saved flattened world loads back voxel for voxel;
+    truncated, bit-flipped and foreign files are refused (RC_ERR_MALFORMED_WORLD), never installed."""
+    info = rcmod.flatten_host(world_desc)
+    rng = np.random.default_rng(3)
+    pts = np.concatenate([rng.integers(0, 256, size=(50000, 3)), rng.integers(-50, 1100, size=(5000, 3))]).astype(np.int32)
+    w0, s0, l0 = rcmod.lookup_host(pts, which=1)
+    path = str(tmp_path / "world.rcpw")
+    rcmod.save_host(path)
+    blob = open(path, "rb").read()
+    assert blob[:8] == b"RCPWORLD" and len(blob) == 64 + info.packed_bytes
+    rcmod.flatten_host(rcmod.world_desc_from_flat(np.zeros(2, dtype=np.uint64), np.zeros(64, dtype=np.uint32)))  # forget it
+    back = rcmod.load_host(path)
+    assert (back.packed_nodes, back.packed_voxels, back.packed_materials, back.max_depth) == (
+        info.packed_nodes, info.packed_voxels, info.packed_materials, info.max_depth)
+    w1, s1, l1 = rcmod.lookup_host(pts, which=1)
+    assert np.array_equal(w0, w1) and np.array_equal(s0, s1) and np.array_equal(l0, l1)
+    for name, data in [("short", blob[:-5]), ("long", blob + b"x"), ("magic", b"NOTAWRLD" + blob[8:]),
+                       ("flip", blob[:5000] + bytes([blob[5000] ^ 0x10]) + blob[5001:]), ("empty", b"")]:
+        bad = str(tmp_path / f"bad_{name}.rcpw")
+        open(bad, "wb").write(data)
+        with pytest.raises(rcmod.RcError) as e:
+            rcmod.load_host(bad)
+        assert e.value.code == -4, name
+    with pytest.raises(rcmod.RcError):
+        rcmod.load_host(str(tmp_path / "does_not_exist.rcpw"))

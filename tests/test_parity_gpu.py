@@ -3,6 +3,8 @@
 Bar (BASELINE.json north_star): hit voxel, face, step counts, flags bit-exact;
 RGBA8 within 1/255 per channel (in practice identical: the deterministic sin/exp
 make the shading bit-exact too, which the tests report)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -176,3 +178,28 @@ def test_incremental_world_update_edit_scenario_on_device():
     r = subprocess.run([sys.executable, os.path.join(here, "edit_scenario.py"), "gpu"], capture_output=True, text=True,
                        timeout=600)
     assert r.returncode == 0 and "edit scenario ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_world_blob_and_ppm_on_device(rcmod, caster, world_desc, defaults, tmp_path):
+    """rc_save_world -> rc_load_world renders the same frame byte for byte (no host pools, no flatten);
+    rc_write_ppm holds the RGBA8 frame top row first."""
+    pos, d, sun = defaults
+    p = rcmod.frame_params(640, 360, pos, d, sun, shadows=True, ao_samples=16, hits=True)
+    caster.render_frame(p)
+    img, hits = caster.read_image(), caster.read_hits()
+    path = str(tmp_path / "default.rcpw")
+    caster.save_world(path)
+    try:
+        info = caster.load_world(path)
+        assert info.packed_bytes == os.path.getsize(path) - 64 and info.ref_bytes == 0
+        caster.render_frame(p)
+        assert np.array_equal(caster.read_image(), img) and caster.read_hits().tobytes() == hits.tobytes()
+        ppm = str(tmp_path / "frame.ppm")
+        caster.write_ppm(ppm)
+        raw = open(ppm, "rb").read()
+        header = b"P6\n640 360\n255\n"
+        assert raw.startswith(header) and len(raw) == len(header) + 640 * 360 * 3
+        pix = np.frombuffer(raw[len(header):], dtype=np.uint8).reshape(360, 640, 3)
+        assert np.array_equal(pix, img[::-1, :, :3])
+    finally:
+        caster.upload_world(world_desc)
