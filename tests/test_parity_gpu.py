@@ -203,3 +203,28 @@ def test_world_blob_and_ppm_on_device(rcmod, caster, world_desc, defaults, tmp_p
         assert np.array_equal(pix, img[::-1, :, :3])
     finally:
         caster.upload_world(world_desc)
+
+
+def test_headless_cpp_host_drives_the_c_abi(rcmod, caster, defaults, ref_world, tmp_path):
+    """host/rc_headless (the reference's main loop against include/rc.h, C++, no Python): runs, clicks
+    (rc_update_world), picks on the device, writes PPM frames; its first frame equals the same frame asked
+    for through the ctypes binding."""
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "host", "rc_headless")
+    assert os.path.exists(exe), "host/rc_headless not built (make -C raytracing_test_b200/csrc)"
+    r = subprocess.run([exe, "--frames", "14", "--size", "640x360", "--ao", "16", "--out", str(tmp_path) + "/f", "--edit",
+                        "--gpu-pick"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "click at frame 4" in r.stdout and "render time:" in r.stdout
+    pos, d, sun = defaults
+    look, _, _ = ref_world.pick(pos, d, 30)
+    caster.render_frame(rcmod.frame_params(640, 360, pos, d, sun, shadows=True, ao_samples=16, mouse_pos=(320.0, 180.0),
+                                           looking_at=tuple(int(v) for v in look)))
+    img = caster.read_image()
+    raw = open(str(tmp_path) + "/f0000.ppm", "rb").read()
+    header = b"P6\n640 360\n255\n"
+    pix = np.frombuffer(raw[len(header):], dtype=np.uint8).reshape(360, 640, 3)
+    assert np.array_equal(pix, img[::-1, :, :3])
+    assert len([f for f in os.listdir(tmp_path) if f.endswith(".ppm")]) == 14
