@@ -1055,6 +1055,7 @@ __device__ __forceinline__ int aow_stride_y(int face) { return face == 0 ? 8 : 1
 __device__ __forceinline__ int aow_stride_z(int face) { return face == 0 ? 96 : (face == 1 ? 128 : 192); }
 
 // The shader's loop for one AO ray on the tree itself (no window): semantics of castAo.
+// (x,y,z) / (px,py,pz) = the ray's state before its first step.
 __device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, int hy, int hz, float px, float py, float pz,
                                                 float adx, float ady, float adz, int sx, int sy, int sz, uint32_t nSteps) {
     Cursor cur;
@@ -1077,6 +1078,8 @@ __device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, in
     return state != 0u ? 1u : 0u;
 }
 
+// NSTEPS: ao_steps known at compile time (the loop unrolls), 0 = read it from the frame parameters.
+template <uint32_t NSTEPS>
 __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_constant__ FrameArgs A, const AoDir* __restrict__ table) {
     __shared__ uint32_t sWin[AOW_WORDS][AO_THREADS];
 
@@ -1141,7 +1144,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
     const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
     const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
-    const uint32_t nSamples = P.ao_samples, nSteps = P.ao_steps;
+    const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
     const uint32_t* win = &sWin[0][tid];
 
@@ -1160,27 +1163,35 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
         else if (f1) py = FSUB(py, ady);
         else pz = FSUB(pz, adz);
 
-        // the forced first step must be the one the DDA takes, else the window does not cover the ray
-        const bool firstX = px < py && px < pz;
-        const bool firstY = !firstX && py < pz;
-        const bool firstOk = f0 ? firstX : (f1 ? firstY : (!firstX && !firstY));
-        if (liquid || !firstOk) {
+        if (liquid) {
             occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
                                        qz < 0 ? -1 : 1, nSteps);
             continue;
         }
         int q = q0;
         uint32_t hit = 0u;
-        for (uint32_t i = nSteps; i != 0u; i--) {
+        const float px0 = px, py0 = py, pz0 = pz;
+        bool covered = true;
+#pragma unroll
+        for (uint32_t i = 0; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
+            if (NSTEPS == 0 && i >= nSteps) break;
             const bool bx = px < py && px < pz;
             const bool by = !bx && py < pz;
             const bool bz = !bx && !by;
+            // the first step must be the forced one through the hit face, else the window does not cover the ray
+            if (i == 0) {
+                covered = f0 ? bx : (f1 ? by : bz);
+                if (!covered) break;  // q would walk out of the window
+            }
             if (bx) { q += qx; px = FADD(px, adx); }
             if (by) { q += qy; py = FADD(py, ady); }
             if (bz) { q += qz; pz = FADD(pz, adz); }
             hit = (win[(q >> 5) * AO_THREADS] >> (q & 31)) & 1u;
             if (hit) break;
         }
+        if (!covered)
+            hit = ao_ray_general(W, s.x, s.y, s.z, px0, py0, pz0, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
+                                 qz < 0 ? -1 : 1, nSteps);
         occluded += hit;
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
@@ -1325,8 +1336,10 @@ cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
 cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
     if (maxSeeds == 0) return cudaSuccess;
     const unsigned blocks = (maxSeeds + AO_THREADS - 1u) / AO_THREADS;
-    if (args.p.ao_steps <= AOW_MAX_STEPS && g_aoTable)
-        ao_window_kernel<<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
+    if (args.p.ao_steps == AOW_MAX_STEPS && g_aoTable)
+        ao_window_kernel<AOW_MAX_STEPS><<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
+    else if (args.p.ao_steps < AOW_MAX_STEPS && g_aoTable)
+        ao_window_kernel<0><<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
     else
         ao_cached_kernel<<<blocks, AO_THREADS, 0, stream>>>(args);
     return cudaGetLastError();
