@@ -1046,7 +1046,7 @@ constexpr int AOW_WORDS = 48;
 // from the direction, precomputed on the host with the same IEEE operations.
 struct AoDir {
     float ix, iy, iz;   // ray.delta = 1 / dir
-    int qx, qy, qz;     // window stride of one step along each axis: sign(dir) * stride(face)
+    float qx, qy, qz;   // window stride of one step along each axis: sign(dir) * stride(face), as floats
     float dx, dy;       // unused by the kernel (kept for debugging), pads the entry to 32 bytes
 };
 static_assert(sizeof(AoDir) == 32, "AoDir is two 128-bit loads");
@@ -1144,6 +1144,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
     const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
     const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
+    const float q0f = 8388608.0f + (float)q0;
     const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
     const uint32_t* win = &sWin[0][tid];
@@ -1151,9 +1152,9 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     uint32_t occluded = 0;
     for (uint32_t k = 0; k < nSamples; k++) {
         const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
-        const int4 v1 = __ldg(reinterpret_cast<const int4*>(dirs + k) + 1);
+        const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
         const float ix = v0.x, iy = v0.y, iz = v0.z;
-        const int qx = __float_as_int(v0.w), qy = v1.x, qz = v1.y;
+        const float qx = v0.w, qy = v1.x, qz = v1.y;  // never 0: the sign says which way the ray steps
         const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
         // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face]
         float px = FSUB(adx, FMUL(qx < 0 ? a1x : a0x, ix));
@@ -1168,7 +1169,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                                        qz < 0 ? -1 : 1, nSteps);
             continue;
         }
-        int q = q0;
+        // The window index lives in the mantissa of a float (2^23 + q, exact): a step is a predicated
+        // FADD on the FMA pipe instead of select + integer add on the half-rate ALU pipe, and the word /
+        // bit indices are read straight from the bit pattern.
+        float qf = q0f;
+        const float qxf = qx, qyf = qy, qzf = qz;
         uint32_t hit = 0u;
         const float px0 = px, py0 = py, pz0 = pz;
         bool covered = true;
@@ -1183,10 +1188,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                 covered = f0 ? bx : (f1 ? by : bz);
                 if (!covered) break;  // q would walk out of the window
             }
-            if (bx) { q += qx; px = FADD(px, adx); }
-            if (by) { q += qy; py = FADD(py, ady); }
-            if (bz) { q += qz; pz = FADD(pz, adz); }
-            hit = (win[(q >> 5) * AO_THREADS] >> (q & 31)) & 1u;
+            if (bx) { qf += qxf; px = FADD(px, adx); }
+            if (by) { qf += qyf; py = FADD(py, ady); }
+            if (bz) { qf += qzf; pz = FADD(pz, adz); }
+            const uint32_t q = __float_as_uint(qf);  // 0x4B000000 | index
+            hit = (win[((q >> 5) & 63u) * AO_THREADS] >> (q & 31u)) & 1u;
             if (hit) break;
         }
         if (!covered)
@@ -1305,9 +1311,9 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 o.ix = iv[0];
                 o.iy = iv[1];
                 o.iz = iv[2];
-                o.qx = d[0] < 0.0f ? -strides[0] : strides[0];
-                o.qy = d[1] < 0.0f ? -strides[1] : strides[1];
-                o.qz = d[2] < 0.0f ? -strides[2] : strides[2];
+                o.qx = (float)(d[0] < 0.0f ? -strides[0] : strides[0]);
+                o.qy = (float)(d[1] < 0.0f ? -strides[1] : strides[1]);
+                o.qz = (float)(d[2] < 0.0f ? -strides[2] : strides[2]);
                 o.dx = d[0];
                 o.dy = d[1];
             }
