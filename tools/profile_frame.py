@@ -1,5 +1,5 @@
 """Developer probe for ncu: renders a few frames of one BASELINE config on cuda:0 and exits.
-python tools/profile_frame.py [width height shadows ao_samples frames]"""
+python tools/profile_frame.py [width height shadows ao_samples frames max_steps]"""
 import os
 import sys
 
@@ -11,11 +11,12 @@ w, h = (int(a[0]), int(a[1])) if len(a) >= 2 else (1920, 1080)
 sh = bool(int(a[2])) if len(a) >= 3 else True
 ao = int(a[3]) if len(a) >= 4 else 64
 frames = int(a[4]) if len(a) >= 5 else 4
+max_steps = int(a[5]) if len(a) >= 6 else 300
 host = vh.World.default()
 pos, d, sun = vh.default_camera()
 with rc.RayCaster(0) as c:
     c.upload_world(host.describe())
-    p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao)
+    p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao, max_steps=max_steps)
     for _ in range(frames):
         c.render_frame(p)
         c.sync()
