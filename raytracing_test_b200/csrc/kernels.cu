@@ -502,8 +502,8 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     out.traced = live;
 
     // :264-265
-    const float fcx = FMUL(fragX, FDIV(1.0f, (float)P.width));
-    const float fcy = FMUL(fragY, FDIV(1.0f, (float)P.height));
+    const float fcx = FMUL(fragX, A.inv_width);   // 1.0 / resolution, divided once on the host (IEEE fp32)
+    const float fcy = FMUL(fragY, A.inv_height);
 
     const F3 origin = F3{P.origin[0], P.origin[1], P.origin[2]};
     const F3 camDir = F3{P.camera_dir[0], P.camera_dir[1], P.camera_dir[2]};
@@ -517,7 +517,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
 
     // :275,288-296
     Ray ray;
-    build_ray(ray, dir.x, dir.y, dir.z, true);
+    build_ray(ray, dir.x, dir.y, dir.z, false);  // the six ratios only serve pos.exact: rays that hit divide for them below
     Pos pos;
     pos.x = (int)floorf(origin.x);
     pos.y = (int)floorf(origin.y);
@@ -615,6 +615,15 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         // the shader's counter: `while (empty && i++ < numSteps)` leaves numSteps + 1 behind when it runs out
         i = word != 0u ? steps : numSteps + 1u;
         if (steps) face = axis_index(ax);
+    }
+    if (word != 0u || P.render_pos_data == 1) {
+        // ratios columns (low_res.frag:75-91) for pos.exact, now that the ray is known to need it
+        ray.r0y = FDIV(ray.dy, ray.dx);
+        ray.r0z = FDIV(ray.dz, ray.dx);
+        ray.r1x = FDIV(ray.dx, ray.dy);
+        ray.r1z = FDIV(ray.dz, ray.dy);
+        ray.r2x = FDIV(ray.dx, ray.dz);
+        ray.r2y = FDIV(ray.dy, ray.dz);
     }
     if (steps != 0u && (word != 0u || P.render_pos_data == 1)) {
         // replay: same ray, same comparisons, now with pos.exact (low_res.frag:447,489)

@@ -48,6 +48,7 @@ struct FrameArgs {
     rc_frame_params p;
     DeviceWorld world;
     uint32_t rank, world_size;
+    float inv_width, inv_height;  // 1.0f / width, 1.0f / height (low_res.frag:264: 1.0 / resolution)
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
     uchar4* rgba8;           // [local_rows][width]

@@ -498,6 +498,8 @@ int rc_render_frame(const rc_frame_params* params) {
     a.p = p;
     a.world = g.world;
     a.rank = g.rank;
+    a.inv_width = 1.0f / (float)p.width;
+    a.inv_height = 1.0f / (float)p.height;
     a.world_size = g.worldSize;
     a.local_rows = localRows;
     a.n_local_bands = localBands;
