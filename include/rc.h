@@ -224,6 +224,31 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
 int rc_save_world(const char* path);
 int rc_load_world(const char* path);
 
+/* ---- world generation on the device ----------------------------------------------
+ * Replaces initTetraHexaTree() + genWorld() + the SSBO upload (src/main.cpp:181-212,
+ * src/voxel_data/tetrahexa_tree.cpp:14-27, src/world_gen.cpp:13-42): the same world -- three
+ * octaves of 2-D OpenSimplex noise (the reference's seeds 42, 64, 100 by default), water below
+ * y = 20, grass / 3 x dirt / stone down each column, over the start-up test blocks -- is built
+ * straight into the flattened device form, without the host tree (the reference spends one
+ * putBlock per voxel on one core).  Voxel for voxel equal to the host-built world, and node for
+ * node equal to rc_upload_world's flattening of it.  Like a loaded world it has no update
+ * baseline.  Columns whose height falls below y = 0 (the reference wraps them around the torus;
+ * the noise amplitudes make that practically unreachable) are refused with RC_ERR_UNSUPPORTED. */
+typedef struct rc_gen_params {
+    uint32_t width, length;  /* columns along x and z; reference WIDTH = LENGTH = 200 (world_gen.cpp:8-9) */
+    uint32_t max_depth;      /* reference maxDepth = 6 (1024^3 torus); [3,8] */
+    uint32_t startup_blocks; /* 1 = also place initTetraHexaTree's test blocks */
+    int64_t seeds[3];        /* reference: 42, 64, 100 (world_gen.cpp:15-17) */
+} rc_gen_params;
+typedef struct rc_gen_info {
+    uint64_t columns, candidate_bricks, bricks, nodes, voxels;
+    int32_t min_height, max_height;
+    float heights_ms; /* noise + height map */
+    float build_ms;   /* brick masks, sort, tree levels, voxel fill */
+    float total_ms;   /* wall clock of the call, allocations included */
+} rc_gen_info;
+int rc_generate_world(const rc_gen_params* params, rc_gen_info* info);
+
 /* The last frame (RC_RGBA8) as a binary PPM, top row first: the headless stand-in for looking at
  * the window. Synchronises like rc_read_image. Sharded frames: this rank's rows, others black. */
 int rc_write_ppm(const char* path);

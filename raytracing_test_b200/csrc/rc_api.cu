@@ -16,6 +16,7 @@
 #include "../../include/rc_debug.h"
 #include "kernels.h"
 #include "packed_world.h"
+#include "worldgen.h"
 
 namespace {
 
@@ -38,6 +39,7 @@ struct Context {
     PackedWorld packed;       // host copy of the uploaded world (debug lookups, incremental updates)
     FlattenTracking tracking; // maps + pool mirror for rc_update_world (built by its first call)
     size_t capNodes = 0, capVoxels = 0, capPalette = 0;  // device array capacities (elements)
+    bool hostCopyStale = false;  // rc_generate_world: g.packed.nodes / .voxels are fetched from the device on first use
     PackedWorld debugPacked;  // result of rc_debug_flatten_host (CPU-only tests)
     FlattenTracking debugTracking;
 
@@ -90,6 +92,7 @@ void freeWorld() {
     g.dNodes = nullptr;
     g.dVoxels = nullptr;
     g.dPalette = nullptr;
+    g.hostCopyStale = false;
     g.haveWorld = false;
 }
 
@@ -249,6 +252,40 @@ int rc_compose_frame(const void* gathered, void* dst, uint32_t width, uint32_t h
     return RC_OK;
 }
 
+// Points the kernels' view at the device arrays and fills the size fields of g.info.
+static void publishWorld(uint32_t maxDepth, uint64_t nNodes, uint64_t nVoxels, uint64_t nPalette) {
+    g.world.nodes = g.dNodes;
+    g.world.voxels = g.dVoxels;
+    g.world.palette = g.dPalette;
+    g.world.n_nodes = (uint32_t)nNodes;
+    g.world.n_top = 0;
+    g.world.root_shift = 2 * ((int)maxDepth - 2);
+    g.world.wrap = (1u << (2 * (maxDepth - 1))) - 1u;
+    g.world.leak = maxDepth == 6 ? 0x300u : 0u;
+    memset(&g.info, 0, sizeof(g.info));
+    g.info.packed_nodes = nNodes;
+    g.info.packed_voxels = nVoxels;
+    g.info.packed_materials = nPalette;
+    g.info.packed_bytes = nNodes * sizeof(PackedNode) + nVoxels * 4 + nPalette * sizeof(PaletteEntry);
+    g.info.max_depth = maxDepth;
+}
+
+// rc_generate_world leaves the world on the device only; the host copy (save, debug lookups) is made on demand.
+static int ensureHostCopy() {
+    if (!g.hostCopyStale) return RC_OK;
+    CUDA_TRY(cudaSetDevice(g.device));
+    g.packed.nodes.resize(g.info.packed_nodes);
+    g.packed.voxels.resize(g.info.packed_voxels);
+    CUDA_TRY(cudaMemcpyAsync(g.packed.nodes.data(), g.dNodes, g.packed.nodes.size() * sizeof(PackedNode), cudaMemcpyDeviceToHost,
+                             g.stream));
+    if (!g.packed.voxels.empty())
+        CUDA_TRY(cudaMemcpyAsync(g.packed.voxels.data(), g.dVoxels, g.packed.voxels.size() * sizeof(uint32_t),
+                                 cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    g.hostCopyStale = false;
+    return RC_OK;
+}
+
 // Replaces the device world with pw (arrays get slack for later appends) and fills g.info.
 static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     auto t1 = std::chrono::steady_clock::now();
@@ -271,27 +308,14 @@ static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     auto t2 = std::chrono::steady_clock::now();
 
-    g.world.nodes = g.dNodes;
-    g.world.voxels = g.dVoxels;
-    g.world.palette = g.dPalette;
-    g.world.n_nodes = (uint32_t)pw.nodes.size();
-    g.world.n_top = 0;
-    g.world.root_shift = 2 * ((int)pw.max_depth - 2);
-    g.world.wrap = (1u << (2 * (pw.max_depth - 1))) - 1u;
-    g.world.leak = pw.max_depth == 6 ? 0x300u : 0u;
-
-    memset(&g.info, 0, sizeof(g.info));
+    publishWorld(pw.max_depth, pw.nodes.size(), pw.voxels.size(), pw.palette.size());
     g.info.ref_nodes = pw.ref_nodes;
     g.info.ref_bytes = refBytes;
-    g.info.packed_nodes = pw.nodes.size();
-    g.info.packed_voxels = pw.voxels.size();
-    g.info.packed_materials = pw.palette.size();
-    g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
-    g.info.max_depth = pw.max_depth;
     g.info.null_children = pw.null_children;
     g.info.flatten_ms = flattenMs;
     g.info.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
     g.packed = std::move(pw);
+    g.hostCopyStale = false;
     g.haveWorld = true;
     return RC_OK;
 }
@@ -419,7 +443,9 @@ int rc_save_world(const char* path) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_save_world: call rc_init first");
     if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_save_world: no world uploaded");
     std::string err;
-    int rcode = save_packed(g.packed, path, err);
+    int rcode = ensureHostCopy();
+    if (rcode != RC_OK) return rcode;
+    rcode = save_packed(g.packed, path, err);
     if (rcode != RC_OK) return fail(rcode, "%s", err.c_str());
     return RC_OK;
 }
@@ -435,6 +461,49 @@ int rc_load_world(const char* path) {
     g.tracking = FlattenTracking();
     auto t1 = std::chrono::steady_clock::now();
     return installWorld(0, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
+}
+
+int rc_generate_world(const rc_gen_params* params, rc_gen_info* info) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_generate_world: call rc_init first");
+    if (!params) return fail(RC_ERR_INVALID_ARGUMENT, "rc_generate_world: null params");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));  // no frame may still read the old world
+    GeneratedWorld gw;
+    std::string err;
+    int rcode = generate_world(*params, g.stream, gw, err);
+    if (rcode != RC_OK) {
+        if (gw.d_nodes) cudaFree(gw.d_nodes);
+        if (gw.d_voxels) cudaFree(gw.d_voxels);
+        if (info) *info = gw.info;  // heights are known when a column is out of range
+        return fail(rcode, "%s", err.c_str());
+    }
+    freeWorld();
+    g.tracking = FlattenTracking();
+    g.dNodes = (uint4*)gw.d_nodes;
+    g.dVoxels = gw.d_voxels;
+    g.capNodes = gw.cap_nodes;
+    g.capVoxels = gw.cap_voxels;
+    g.capPalette = gw.palette.size() * 2 + 256;
+    CUDA_TRY(cudaMalloc((void**)&g.dPalette, g.capPalette * sizeof(PaletteEntry)));
+    CUDA_TRY(cudaMemcpyAsync(g.dPalette, gw.palette.data(), gw.palette.size() * sizeof(PaletteEntry), cudaMemcpyHostToDevice,
+                             g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    publishWorld(params->max_depth, gw.n_nodes, gw.n_voxels, gw.palette.size());
+    // what the reference's pools would hold for this world: a 16-byte node per packed node and per voxel,
+    // a 256-byte child array per branch (src/voxel_data/types.hpp:29-47)
+    g.info.ref_nodes = gw.n_nodes + gw.n_voxels;
+    g.info.ref_bytes = g.info.ref_nodes * 16 + gw.n_nodes * 256;
+    g.info.flatten_ms = gw.info.total_ms;
+    g.packed = PackedWorld();
+    g.packed.max_depth = params->max_depth;
+    g.packed.palette = std::move(gw.palette);
+    g.packed.level_begin = std::move(gw.level_begin);
+    g.packed.ref_nodes = g.info.ref_nodes;
+    g.hostCopyStale = true;
+    g.haveWorld = true;
+    g.haveFrame = false;
+    if (info) *info = gw.info;
+    return RC_OK;
 }
 
 int rc_write_ppm(const char* path) {
@@ -646,6 +715,7 @@ int rc_hemisphere_table(uint32_t n, float* out) {
 // cell shift, out_leaf[4] = palette entry (the reference Leaf verbatim) when solid.
 int rc_debug_lookup_host(int which, int32_t x, int32_t y, int32_t z, uint32_t* out_word, int32_t* out_shift,
                          uint32_t* out_leaf) {
+    if (!which && ensureHostCopy() != RC_OK) return RC_ERR_CUDA;
     const PackedWorld& pw = which ? g.debugPacked : g.packed;
     if (pw.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_lookup_host: no world (which=%d)", which);
     int shift = 0;
@@ -659,6 +729,7 @@ int rc_debug_lookup_host(int which, int32_t x, int32_t y, int32_t z, uint32_t* o
 // Batch form: xyz = 3*n ints; out_words[n]; out_leaves[4*n] (zeros when empty).
 int rc_debug_lookup_host_batch(int which, const int32_t* xyz, uint64_t n, uint32_t* out_words, int32_t* out_shifts,
                                uint32_t* out_leaves) {
+    if (!which && ensureHostCopy() != RC_OK) return RC_ERR_CUDA;
     const PackedWorld& pw = which ? g.debugPacked : g.packed;
     if (pw.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_lookup_host_batch: no world (which=%d)", which);
     for (uint64_t i = 0; i < n; i++) {
@@ -696,7 +767,7 @@ int rc_debug_lookup_device(const int32_t* xyz, uint32_t n, uint32_t* out_words, 
 
 // Palette entry (Leaf verbatim) of a material word of the uploaded world.
 int rc_debug_palette(uint32_t word, uint32_t* out_leaf) {
-    if (g.packed.nodes.empty()) return fail(RC_ERR_NO_WORLD, "rc_debug_palette: no world");
+    if (g.packed.nodes.empty() && !g.hostCopyStale) return fail(RC_ERR_NO_WORLD, "rc_debug_palette: no world");
     const uint32_t idx = word & MATERIAL_INDEX_MASK;
     if (idx >= g.packed.palette.size()) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_palette: index %u", idx);
     memcpy(out_leaf, &g.packed.palette[idx], 16);

@@ -6,6 +6,7 @@
 // Built with -ffp-contract=off: the terrain heights are functions of double-precision
 // noise values and must round exactly like the reference's.
 #include "../../include/voxel_host.h"
+#include "simplex2.h"
 
 #include <math.h>
 #include <stdlib.h>
@@ -55,112 +56,7 @@ struct NodeRef {
 uint32_t floatBits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 float bitsFloat(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
-// ---------------------------------------------------------------------------
-// 2-D OpenSimplex noise (KdotJPG's algorithm as vendored by the reference:
-// include/OpenSimplexNoise.cpp:52-75 permutation, :77-208 eval, :2518-2523 gradient).
-// The expression order below is the reference's, so doubles agree bit for bit.
-// ---------------------------------------------------------------------------
-struct Simplex2 {
-    static constexpr double kStretch = -0.211324865405187;
-    static constexpr double kSquish = 0.366025403784439;
-    short perm[256];
-
-    explicit Simplex2(int64_t seedIn) {
-        short source[256];
-        for (int i = 0; i < 256; i++) source[i] = (short)i;
-        uint64_t s = (uint64_t)seedIn;
-        auto lcg = [&s]() { s = s * 6364136223846793005ull + 1442695040888963407ull; };
-        lcg();
-        lcg();
-        lcg();
-        for (int i = 255; i >= 0; i--) {
-            lcg();
-            int r = (int)((int64_t)(s + 31) % (i + 1));
-            if (r < 0) r += i + 1;
-            perm[i] = source[r];
-            source[r] = source[i];
-        }
-    }
-
-    double gradient(int xsb, int ysb, double dx, double dy) const {
-        static const signed char g[16] = {5, 2, 2, 5, -5, 2, -2, 5, 5, -2, 2, -5, -5, -2, -2, -5};
-        const int idx = perm[(perm[xsb & 0xFF] + ysb) & 0xFF] & 0x0E;
-        return g[idx] * dx + g[idx + 1] * dy;
-    }
-
-    // One lattice vertex: (2 - dx^2 - dy^2)^4 * gradient, or 0 outside its kernel.
-    double vertex(int xsb, int ysb, double dx, double dy) const {
-        double attn = 2 - dx * dx - dy * dy;
-        if (!(attn > 0)) return 0.0;
-        attn *= attn;
-        return attn * attn * gradient(xsb, ysb, dx, dy);
-    }
-
-    double eval(double x, double y) const {
-        const double stretch = (x + y) * kStretch;
-        const double xs = x + stretch, ys = y + stretch;
-        int xsb = (int)floor(xs), ysb = (int)floor(ys);
-        const double squish = (xsb + ysb) * kSquish;
-        const double xins = xs - xsb, yins = ys - ysb;
-        const double inSum = xins + yins;
-        double dx0 = x - (xsb + squish), dy0 = y - (ysb + squish);
-
-        double value = 0;
-        // vertices (1,0) and (0,1) always contribute
-        {
-            const double dx1 = dx0 - 1 - kSquish, dy1 = dy0 - 0 - kSquish;
-            double a = 2 - dx1 * dx1 - dy1 * dy1;
-            if (a > 0) {
-                a *= a;
-                value += a * a * gradient(xsb + 1, ysb + 0, dx1, dy1);
-            }
-            const double dx2 = dx0 - 0 - kSquish, dy2 = dy0 - 1 - kSquish;
-            double b = 2 - dx2 * dx2 - dy2 * dy2;
-            if (b > 0) {
-                b *= b;
-                value += b * b * gradient(xsb + 0, ysb + 1, dx2, dy2);
-            }
-        }
-        // the fourth ("extra") vertex depends on which half of the rhombus we are in
-        int xe, ye;
-        double dxe, dye;
-        if (inSum <= 1) {
-            const double zins = 1 - inSum;
-            if (zins > xins || zins > yins) {
-                if (xins > yins) { xe = xsb + 1; ye = ysb - 1; dxe = dx0 - 1; dye = dy0 + 1; }
-                else             { xe = xsb - 1; ye = ysb + 1; dxe = dx0 + 1; dye = dy0 - 1; }
-            } else {
-                xe = xsb + 1; ye = ysb + 1;
-                dxe = dx0 - 1 - 2 * kSquish; dye = dy0 - 1 - 2 * kSquish;
-            }
-        } else {
-            const double zins = 2 - inSum;
-            if (zins < xins || zins < yins) {
-                if (xins > yins) { xe = xsb + 2; ye = ysb + 0; dxe = dx0 - 2 - 2 * kSquish; dye = dy0 + 0 - 2 * kSquish; }
-                else             { xe = xsb + 0; ye = ysb + 2; dxe = dx0 + 0 - 2 * kSquish; dye = dy0 - 2 - 2 * kSquish; }
-            } else {
-                xe = xsb; ye = ysb; dxe = dx0; dye = dy0;
-            }
-            xsb += 1;
-            ysb += 1;
-            dx0 = dx0 - 1 - 2 * kSquish;
-            dy0 = dy0 - 1 - 2 * kSquish;
-        }
-        {
-            double a = 2 - dx0 * dx0 - dy0 * dy0;
-            if (a > 0) {
-                a *= a;
-                value += a * a * gradient(xsb, ysb, dx0, dy0);
-            }
-            double e = 2 - dxe * dxe - dye * dye;
-            if (e > 0) {
-                e *= e;
-                value += e * e * gradient(xe, ye, dxe, dye);
-            }
-        }
-        return value / 47;
-    }
-};
+using rc_noise::Simplex2;
 
 }  // namespace
 

@@ -72,6 +72,22 @@ class UpdateInfo(ctypes.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class GenParams(ctypes.Structure):
+    """rc_gen_params (include/rc.h): what initTetraHexaTree() + genWorld() hard-code."""
+    _fields_ = [("width", ctypes.c_uint32), ("length", ctypes.c_uint32), ("max_depth", ctypes.c_uint32),
+                ("startup_blocks", ctypes.c_uint32), ("seeds", ctypes.c_int64 * 3)]
+
+
+class GenInfo(ctypes.Structure):
+    _fields_ = [("columns", ctypes.c_uint64), ("candidate_bricks", ctypes.c_uint64), ("bricks", ctypes.c_uint64),
+                ("nodes", ctypes.c_uint64), ("voxels", ctypes.c_uint64), ("min_height", ctypes.c_int32),
+                ("max_height", ctypes.c_int32), ("heights_ms", ctypes.c_float), ("build_ms", ctypes.c_float),
+                ("total_ms", ctypes.c_float)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
 class FrameParams(ctypes.Structure):
     _fields_ = [
         ("origin", ctypes.c_float * 3), ("camera_dir", ctypes.c_float * 3), ("sun_dir", ctypes.c_float * 3),
@@ -116,6 +132,7 @@ ABI = {
     "rc_save_world": (ctypes.c_int, [ctypes.c_char_p]),
     "rc_load_world": (ctypes.c_int, [ctypes.c_char_p]),
     "rc_write_ppm": (ctypes.c_int, [ctypes.c_char_p]),
+    "rc_generate_world": (ctypes.c_int, [ctypes.POINTER(GenParams), ctypes.POINTER(GenInfo)]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
@@ -315,6 +332,13 @@ class RayCaster:
         _check(self.lib, self.lib.rc_load_world(os.fsencode(path)))
         info = WorldInfo()
         _check(self.lib, self.lib.rc_world_info_get(ctypes.byref(info)))
+        return info
+
+    def generate_world(self, width=200, length=200, max_depth=6, seeds=(42, 64, 100), startup_blocks=True):
+        """rc_generate_world: initTetraHexaTree() + genWorld() (src/main.cpp:181-190) on the device -> GenInfo."""
+        p = GenParams(int(width), int(length), int(max_depth), 1 if startup_blocks else 0, (ctypes.c_int64 * 3)(*seeds))
+        info = GenInfo()
+        _check(self.lib, self.lib.rc_generate_world(ctypes.byref(p), ctypes.byref(info)))
         return info
 
     def write_ppm(self, path):
