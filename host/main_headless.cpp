@@ -6,7 +6,7 @@
 // (include/voxel_host.h), a from-scratch stand-in that the tests hold to the reference's own code voxel for
 // voxel.  INTEGRATION.md shows the same loop as a patch to the real src/main.cpp.
 //
-//   rc_headless [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--device D]
+//   rc_headless [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D]
 //
 // Per frame: camera yaw advances as rotateCamera() would (src/input.cpp:19-30), the picking ray feeds
 // lookingAtBlock (src/main.cpp:81,89), --edit clicks once per 8 frames (src/input.cpp:141-160: delete the picked
@@ -46,7 +46,7 @@ static void cameraDirFor(double rotationX, double rotationY, float out[3]) {
 
 int main(int argc, char** argv) {
     int frames = 16, width = 1920, height = 1080, ao = 64, device = 0;
-    bool edit = false, gpuPick = false;
+    bool edit = false, gpuPick = false, genDevice = false;
     std::string out;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
@@ -58,31 +58,47 @@ int main(int argc, char** argv) {
         else if (a == "--device") device = atoi(next());
         else if (a == "--edit") edit = true;
         else if (a == "--gpu-pick") gpuPick = true;
+        else if (a == "--gen-device") genDevice = gpuPick = true;  // no host tree: the picking ray runs on the device too
         else {
-            fprintf(stderr, "usage: %s [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--device D]\n", argv[0]);
+            fprintf(stderr, "usage: %s [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D]\n", argv[0]);
             return 2;
         }
     }
 
     check(rc_init(device), "rc_init");  // createWindow(); setupOpenGl();            src/main.cpp:176-179
     vh_world* world = vh_create(6);     // initTetraHexaTree();                      :181
-    vh_add_startup_blocks(world);
     const int64_t seeds[3] = {42, 64, 100};
-    auto t0 = std::chrono::steady_clock::now();
-    vh_generate_terrain(world, 200, 200, seeds);  // genWorld();                     :188-190
-    printf("generated chunk! time: %lf\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    bool hostTree = !genDevice;
+    auto buildHostTree = [&]() {
+        vh_add_startup_blocks(world);
+        auto t0 = std::chrono::steady_clock::now();
+        vh_generate_terrain(world, 200, 200, seeds);  // genWorld();                 :188-190
+        printf("generated chunk! time: %lf\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+        hostTree = true;
+    };
+    if (genDevice) {  // the same world built on the device, no host tree and no upload
+        rc_gen_params gp = {200, 200, 6, 1, {seeds[0], seeds[1], seeds[2]}};
+        rc_gen_info gi;
+        check(rc_generate_world(&gp, &gi), "rc_generate_world");
+        printf("generated chunk on the device! time: %lf (noise %.3f ms + tree %.3f ms on the device; %llu bricks, %llu voxels)\n",
+               gi.total_ms / 1e3, gi.heights_ms, gi.build_ms, (unsigned long long)gi.bricks, (unsigned long long)gi.voxels);
+    } else {
+        buildHostTree();
+    }
 
     float cameraPos[3], cameraDir[3], sun[3];
     vh_default_camera(cameraPos, cameraDir, sun);  // src/globals.cpp:20-23 + normalize :195
 
     rc_world_desc desc;
-    vh_describe(world, &desc);
     rc_update_info ui;
-    check(rc_update_world(&desc, nullptr, 0, nullptr, 0, &ui), "rc_update_world");  // first updateSsboData(): full upload
+    if (hostTree) {
+        vh_describe(world, &desc);
+        check(rc_update_world(&desc, nullptr, 0, nullptr, 0, &ui), "rc_update_world");  // first updateSsboData(): full upload
+    }
     rc_world_info wi;
     check(rc_world_info_get(&wi), "rc_world_info_get");
-    printf("world: %llu reference nodes (%.1f MB) -> %.2f MB packed, flatten %.1f ms, upload %.2f ms\n",
-           (unsigned long long)wi.ref_nodes, wi.ref_bytes / 1e6, wi.packed_bytes / 1e6, wi.flatten_ms, wi.upload_ms);
+    printf("world: %llu reference nodes (%.1f MB) -> %.2f MB packed, %s %.1f ms, upload %.2f ms\n", (unsigned long long)wi.ref_nodes,
+           wi.ref_bytes / 1e6, wi.packed_bytes / 1e6, hostTree ? "flatten" : "generate", wi.flatten_ms, wi.upload_ms);
 
     std::vector<uint8_t> frame((size_t)width * height * 4);
     double rotationX = 45.0, rotationY = 0.0, sumMs = 0.0;  // cameraDir (1,0,1) = 45 degrees of yaw
@@ -99,6 +115,7 @@ int main(int argc, char** argv) {
             memcpy(pick.pos, r, 12), memcpy(pick.last_pos, r + 3, 12), pick.steps = r[6];
         }
         if (edit && f % 8 == 4 && pick.steps) {  // one click                        src/input.cpp:141-160
+            if (!hostTree) buildHostTree();  // the first edit needs the host's tree: built late, diffed against nothing
             if ((f / 8) % 2 == 0) vh_put_block(world, pick.last_pos[0], pick.last_pos[1], pick.last_pos[2], &placed, 6);
             else vh_put_block(world, pick.pos[0], pick.pos[1], pick.pos[2], &placed, 6);
             vh_describe(world, &desc);

@@ -228,3 +228,23 @@ def test_headless_cpp_host_drives_the_c_abi(rcmod, caster, defaults, ref_world, 
     pix = np.frombuffer(raw[len(header):], dtype=np.uint8).reshape(360, 640, 3)
     assert np.array_equal(pix, img[::-1, :, :3])
     assert len([f for f in os.listdir(tmp_path) if f.endswith(".ppm")]) == 14
+
+
+def test_headless_host_with_device_generated_world(tmp_path):
+    """--gen-device: rc_generate_world instead of the host's genWorld + upload; every frame of the run
+    (edits included: the host tree is built at the first click) is byte-identical to the host-built run."""
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "host", "rc_headless")
+    assert os.path.exists(exe), "host/rc_headless not built (make -C raytracing_test_b200/csrc)"
+    common = ["--frames", "14", "--size", "480x270", "--ao", "16", "--edit", "--gpu-pick"]
+    for tag, extra in (("h", []), ("d", ["--gen-device"])):
+        r = subprocess.run([exe] + common + ["--out", f"{tmp_path}/{tag}"] + extra, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "click at frame 4" in r.stdout
+        assert ("generated chunk on the device!" in r.stdout) == bool(extra)
+    for f in range(14):
+        a = open(f"{tmp_path}/h{f:04d}.ppm", "rb").read()
+        b = open(f"{tmp_path}/d{f:04d}.ppm", "rb").read()
+        assert a == b, f"frame {f} differs between the host-built and the device-generated world"
