@@ -262,6 +262,16 @@ int rc_render_frame(const rc_frame_params* params);
  * frame and copies it to host memory.  dst_bytes >= width*height*(4|16). */
 int rc_read_image(void* dst, size_t dst_bytes, int format);
 
+/* The same swap, double-buffered like the window's front / back buffers (glfwSwapBuffers returns
+ * while the front buffer is still being scanned out): queues the copy of the last rendered RC_RGBA8
+ * frame into dst on a separate copy stream and returns at once (dst should be pinned host memory,
+ * cudaHostAlloc / cudaHostRegister, for the copy to be asynchronous).  The next rc_render_frame
+ * renders into the other of two device frame buffers, so frame N+1 is traced while frame N travels
+ * to the host; a third frame waits for the first one's copy.  rc_wait_image(ticket) blocks until
+ * that frame is complete in dst.  One queued read-back per rendered frame. */
+int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket);
+int rc_wait_image(int ticket);
+
 /* Parity records of the last frame rendered with RC_F_HITS; n >= width*height. */
 int rc_read_hits(rc_hit* dst, size_t n);
 

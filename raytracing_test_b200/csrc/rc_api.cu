@@ -45,7 +45,17 @@ struct Context {
 
     // frame buffers (grown on demand)
     size_t pixelCapacity = 0;
-    uchar4* dRgba8 = nullptr;
+    uchar4* dRgba8 = nullptr;  // the frame buffer being rendered into (= slot[cur])
+    // rc_read_image_async: two RGBA8 frame buffers, so that frame N+1 renders while frame N travels to the host
+    struct FrameSlot {
+        uchar4* buf = nullptr;
+        size_t capacity = 0;
+        bool copyPending = false;
+        cudaEvent_t evCopied = nullptr;
+    } slot[2];
+    int cur = 0;
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t evRendered = nullptr;
     float4* dRgba32f = nullptr;
     rc_hit* dHits = nullptr;
     AoSeed* dSeeds = nullptr;
@@ -97,7 +107,14 @@ void freeWorld() {
 }
 
 void freeFrameBuffers() {
-    if (g.dRgba8) cudaFree(g.dRgba8);
+    if (g.copyStream) cudaStreamSynchronize(g.copyStream);
+    g.slot[g.cur].buf = g.dRgba8;
+    for (int i = 0; i < 2; i++) {
+        if (g.slot[i].buf) cudaFree(g.slot[i].buf);
+        g.slot[i].buf = nullptr;
+        g.slot[i].capacity = 0;
+        g.slot[i].copyPending = false;
+    }
     if (g.dRgba32f) cudaFree(g.dRgba32f);
     if (g.dHits) cudaFree(g.dHits);
     if (g.dSeeds) cudaFree(g.dSeeds);
@@ -193,6 +210,15 @@ void rc_shutdown(void) {
     if (g.evPrimary) cudaEventDestroy(g.evPrimary);
     if (g.evEnd) cudaEventDestroy(g.evEnd);
     g.evStart = g.evPrimary = g.evEnd = nullptr;
+    if (g.copyStream) cudaStreamDestroy(g.copyStream);
+    if (g.evRendered) cudaEventDestroy(g.evRendered);
+    for (int i = 0; i < 2; i++) {
+        if (g.slot[i].evCopied) cudaEventDestroy(g.slot[i].evCopied);
+        g.slot[i].evCopied = nullptr;
+    }
+    g.copyStream = nullptr;
+    g.evRendered = nullptr;
+    g.cur = 0;
     if (g.ownStream) cudaStreamDestroy(g.ownStream);
     g.ownStream = g.stream = nullptr;
     g.packed = PackedWorld();
@@ -547,6 +573,18 @@ int rc_render_frame(const rc_frame_params* params) {
     const size_t pixels = (size_t)paddedBands * BAND_ROWS * p.width;
 
     int rcode;
+    // a frame whose asynchronous read-back was queued stays untouched: render into the other buffer, after the
+    // copy that last left it (two frames back) has landed
+    g.slot[g.cur].buf = g.dRgba8;
+    g.slot[g.cur].capacity = g.pixelCapacity;
+    if (g.slot[g.cur].copyPending) g.cur ^= 1;
+    if (g.slot[g.cur].copyPending) {
+        CUDA_TRY(cudaStreamWaitEvent(g.stream, g.slot[g.cur].evCopied, 0));
+        g.slot[g.cur].copyPending = false;
+    }
+    g.dRgba8 = g.slot[g.cur].buf;
+    g.pixelCapacity = g.slot[g.cur].capacity;
+    if (pixels > g.pixelCapacity && g.copyStream) CUDA_TRY(cudaStreamSynchronize(g.copyStream));
     if ((rcode = growBuffer(g.dRgba8, g.pixelCapacity, pixels)) != RC_OK) return rcode;
     if (p.flags & RC_F_RGBA32F)
         if ((rcode = growBuffer(g.dRgba32f, g.f32Capacity, pixels)) != RC_OK) return rcode;
@@ -608,11 +646,12 @@ int rc_sync(void) {
 
 // Copies this rank's rows into their place in a full bottom-up frame at dst.
 // (world_size 1: one contiguous copy.)
-static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel) {
+static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel, cudaStream_t stream = nullptr, bool wait = true) {
     const rc_frame_params& p = g.frame;
     const size_t rowBytes = (size_t)p.width * bytesPerPixel;
+    if (!stream) stream = g.stream;
     if (g.worldSize == 1) {
-        CUDA_TRY(cudaMemcpyAsync(dst, src, rowBytes * p.height, cudaMemcpyDeviceToHost, g.stream));
+        CUDA_TRY(cudaMemcpyAsync(dst, src, rowBytes * p.height, cudaMemcpyDeviceToHost, stream));
     } else {
         for (uint32_t lb = 0; lb < g.localBands; lb++) {
             const uint32_t band = lb * g.worldSize + g.rank;
@@ -621,10 +660,41 @@ static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel) {
             const uint32_t rows = (row0 + BAND_ROWS <= p.height) ? BAND_ROWS : (p.height - row0);
             CUDA_TRY(cudaMemcpyAsync((uint8_t*)dst + (size_t)row0 * rowBytes,
                                      (const uint8_t*)src + (size_t)lb * BAND_ROWS * rowBytes, rows * rowBytes,
-                                     cudaMemcpyDeviceToHost, g.stream));
+                                     cudaMemcpyDeviceToHost, stream));
         }
     }
-    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    if (wait) CUDA_TRY(cudaStreamSynchronize(stream));
+    return RC_OK;
+}
+
+int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_image_async: call rc_init first");
+    if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_read_image_async: no frame rendered");
+    if (!dst || !ticket) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image_async: null dst / ticket");
+    const size_t pixels = (size_t)g.frame.width * g.frame.height;
+    if (dst_bytes < pixels * 4) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_image_async: need %zu bytes", pixels * 4);
+    if (g.slot[g.cur].copyPending) return fail(RC_ERR_NO_FRAME, "rc_read_image_async: this frame's read-back is already queued");
+    CUDA_TRY(cudaSetDevice(g.device));
+    if (!g.copyStream) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&g.copyStream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&g.evRendered, cudaEventDisableTiming));
+        for (int i = 0; i < 2; i++) CUDA_TRY(cudaEventCreateWithFlags(&g.slot[i].evCopied, cudaEventDisableTiming));
+    }
+    CUDA_TRY(cudaEventRecord(g.evRendered, g.stream));
+    CUDA_TRY(cudaStreamWaitEvent(g.copyStream, g.evRendered, 0));
+    int rcode = copyRowsToHost(dst, g.dRgba8, 4, g.copyStream, false);
+    if (rcode != RC_OK) return rcode;
+    CUDA_TRY(cudaEventRecord(g.slot[g.cur].evCopied, g.copyStream));
+    g.slot[g.cur].copyPending = true;
+    *ticket = g.cur;
+    return RC_OK;
+}
+
+int rc_wait_image(int ticket) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_wait_image: call rc_init first");
+    if (ticket < 0 || ticket > 1 || !g.slot[ticket].evCopied)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_wait_image: ticket %d was not issued by rc_read_image_async", ticket);
+    CUDA_TRY(cudaEventSynchronize(g.slot[ticket].evCopied));
     return RC_OK;
 }
 

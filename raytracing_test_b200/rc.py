@@ -135,6 +135,8 @@ ABI = {
     "rc_generate_world": (ctypes.c_int, [ctypes.POINTER(GenParams), ctypes.POINTER(GenInfo)]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
+    "rc_read_image_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int)]),
+    "rc_wait_image": (ctypes.c_int, [ctypes.c_int]),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
     "rc_sync": (ctypes.c_int, []),
     "rc_frame_stats_get": (ctypes.c_int, [ctypes.POINTER(FrameStats)]),
@@ -299,6 +301,15 @@ class RayCaster:
             out = np.zeros((h, w, 4), dtype=np.uint8 if fmt == RC_RGBA8 else np.float32)
         _check(self.lib, self.lib.rc_read_image(out.ctypes.data, out.nbytes, fmt))
         return out
+
+    def read_image_async(self, out):
+        """rc_read_image_async into `out` (a uint8 array over PINNED memory, h x w x 4) -> ticket for wait_image."""
+        t = ctypes.c_int(-1)
+        _check(self.lib, self.lib.rc_read_image_async(out.ctypes.data, out.nbytes, ctypes.byref(t)))
+        return t.value
+
+    def wait_image(self, ticket):
+        _check(self.lib, self.lib.rc_wait_image(ticket))
 
     def read_hits(self, out=None):
         w, h = self._last
