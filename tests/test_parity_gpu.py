@@ -285,3 +285,77 @@ def test_pipelined_readback_delivers_every_frame_intact(rcmod, caster, defaults)
     assert np.array_equal(caster.read_image(), want[0])
     with pytest.raises(rcmod.RcError):
         caster.wait_image(7)
+
+
+def build_zoo_world(vh, depth, rng):
+    """A world the terrain never produces: every material flag combination (src/globals.hpp:68-74) as single
+    voxels, as 4^3 / 16^3 / 64^3 uniform cells, uniform cells split by later single-voxel puts, liquid next to
+    opaque, mirrors facing mirrors, non-zero metadata.  Built with the host stand-in's putBlock."""
+    host = vh.World(depth)
+    voxel = depth
+    flag_sets = [0x0, 0x2, 0x4, 0x10, 0x14, 0x6, 0x12, 0x16]
+    col = lambda: int(vh.load_library().vh_rgb(int(rng.integers(0, 256)), int(rng.integers(0, 256)), int(rng.integers(0, 256))))
+    for _ in range(2):  # 64^3
+        x, y, z = (int(v) for v in rng.integers(0, 3, 3) * 64)
+        host.put_block(x, y + 64, z, col(), int(rng.choice([0x0, 0x4, 0x14])), 0.0, voxel - 3)
+    for _ in range(14):  # 16^3
+        x, y, z = (int(v) for v in rng.integers(0, 12, 3) * 16)
+        host.put_block(x, y, z, col(), int(rng.choice(flag_sets)), float(rng.choice([0.0, 0.5])), voxel - 2)
+    for _ in range(150):  # 4^3
+        x, y, z = (int(v) for v in rng.integers(0, 48, 3) * 4)
+        host.put_block(x, y, z, col(), int(rng.choice(flag_sets)), 0.0, voxel - 1)
+    for _ in range(9000):  # single voxels, many of them inside the uniform cells above (splits them)
+        x, y, z = (int(v) for v in rng.integers(0, 192, 3))
+        host.put_block(x, y, z, col(), int(rng.choice(flag_sets, p=[0.6, 0.08, 0.08, 0.04, 0.1, 0.04, 0.03, 0.03])), 0.0, voxel)
+    # a floor so that most rays end on something and cast shadow + AO rays
+    for x in range(0, 192, 4):
+        for z in range(0, 192, 4):
+            host.put_block(x, 0, z, col(), 0x0, 0.0, voxel - 1)
+    return host
+
+
+@pytest.mark.parametrize("depth", [6, 7])
+def test_material_zoo_world(ob, rcmod, caster, world_desc, defaults, depth):
+    from raytracing_test_b200 import voxel_host as vh
+
+    rng = np.random.default_rng(900 + depth)
+    _, _, sun = defaults
+    host = build_zoo_world(vh, depth, rng)
+    try:
+        nodes, arrays = host.pools()
+        oworld = ob.make_world(nodes, arrays, depth)
+        caster.upload_world(host.describe())
+        pts = rng.integers(0, 200, size=(50000, 3)).astype(np.int32)
+        words, _ = caster.lookup_device(pts)
+        refb = ob.get_blocks(oworld, pts)
+        assert np.array_equal(words != 0, refb[:, 0] != np.uint64(0xFFFFFFFFFFFFFFFF))
+        seen = {"refl": 0, "refr": 0, "shadow": 0, "inside": 0, "ao": 0}
+        views = [((96.5, 40.5, 96.5), 30.0, 25.0), ((20.5, 100.5, 30.5), 60.0, 40.0), ((180.5, 8.5, 10.5), -45.0, 5.0),
+                 ((-10.5, 60.5, 96.5), 90.0, 15.0), ((96.5, 190.5, 96.5), 10.0, 80.0), ((100.2, 70.7, 33.3), 200.0, -20.0),
+                 ((64.5, 5.5, 64.5), 135.0, -35.0), ((8.5, 72.5, 8.5), 45.0, 0.0)]
+        # plus cameras placed inside solid / liquid voxels picked from the world itself
+        solid = pts[words != 0]
+        for k in range(4):
+            p = solid[k * 7]
+            views.append(((float(p[0]) + 0.5, float(p[1]) + 0.5, float(p[2]) + 0.5), 33.0 * k, 10.0))
+        for i, (origin, yaw, pitch) in enumerate(views):
+            ref, got = render_both(ob, rcmod, caster, oworld, 480, 270, origin, camera_dir(yaw, pitch), sun, shadows=True,
+                                   ao_samples=24, delta_time=0.75)
+            assert_parity(ref, got, f"zoo depth {depth} view {i}")
+            assert np.array_equal(ref["rgba8"], got["rgba8"]), f"zoo depth {depth} view {i}: shading not bit-exact"
+            fl = got["hits"]["flags"]
+            seen["refl"] += int(((fl & 0x02) != 0).sum())
+            seen["refr"] += int(((fl & 0x04) != 0).sum())
+            seen["shadow"] += int(((fl & 0x01) != 0).sum())
+            seen["inside"] += int((got["hits"]["kind"] == ob.KIND_CAMERA_INSIDE).sum())
+            seen["ao"] += int(got["hits"]["ao_occluded"].astype(np.int64).sum())
+        # the views really exercise what the world was built for
+        assert seen["refl"] > 1000 and seen["refr"] > 1000 and seen["shadow"] > 1000 and seen["ao"] > 10000, seen
+        # more AO steps than the window kernel is specialised for, and ragged step limits, on this world too
+        for (ms, ss, aos) in [(300, 75, 9), (40, 10, 3)]:
+            ref, got = render_both(ob, rcmod, caster, oworld, 320, 180, views[0][0], camera_dir(30.0, 25.0), sun, shadows=True,
+                                   ao_samples=16, ao_steps=aos, max_steps=ms, shadow_steps=ss)
+            assert_parity(ref, got, f"zoo depth {depth} limits {ms}/{ss}/{aos}")
+    finally:
+        caster.upload_world(world_desc)
+        host.close()
