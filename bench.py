@@ -8,7 +8,8 @@ default generated world (initTetraHexaTree + genWorld: seeds 42/64/100, 200 x 20
   N = 1 : BASELINE.json configs[2] -- 1920x1080, primary + sun shadow + 64-sample hemisphere AO
           (the configuration `metric` is quoted on).
   N > 1 : BASELINE.json configs[4] -- 7680x4320, same passes, 16-row bands dealt round-robin to the
-          ranks, NCCL gather of the finished RGBA8 bands to rank 0 + one compose kernel; strong scaling.
+          ranks; every rank's kernels store their pixels straight into rank 0's frame over NVLink peer memory
+          (--frame-path gather: NCCL gather of the band buffers + one compose kernel instead); strong scaling.
 One JSON line on stdout (rank 0). `value` = rays cast by all ranks / device time (max over ranks) with
 everything resident in HBM; `e2e` = the same through the C-ABI with the frame read back into pinned
 host memory every step (rc_render_frame + rc_read_image).
@@ -52,6 +53,9 @@ def parse_args():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
+    ap.add_argument("--frame-path", choices=["direct", "gather"], default="direct",
+                    help="N>1: how the bands become one frame on rank 0 (direct = peer stores from the kernels over NVLink; "
+                         "gather = NCCL gather + compose kernel, the comparison baseline)")
     return ap.parse_args()
 
 
@@ -256,7 +260,7 @@ def run_b200_arm(args, workload):
     pos, d, sun = vh.default_camera()
     look, _, _ = host.pick(pos, d, 30)  # src/main.cpp:81: the host's picking ray feeds lookingAtBlock
 
-    sc = fg.ShardedRayCaster(local_rank, rank, world_size)
+    sc = fg.ShardedRayCaster(local_rank, rank, world_size, mode=args.frame_path)
     info = sc.upload_world(host.describe())
     params = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -279,7 +283,7 @@ def run_b200_arm(args, workload):
     barrier()
     st = sc.stats()
     local_rays = int(st.primary_rays + st.shadow_rays + st.ao_rays)
-    launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0) else 0)
+    launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0 and args.frame_path == "gather") else 0)
 
     # ---- timed: K steps, device time by CUDA events on the launching stream, L2 flushed between steps ----
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -366,6 +370,20 @@ def run_b200_arm(args, workload):
                 prev = t
             sc.caster.wait_image(prev)
 
+        def run_pipelined_sharded():
+            # N>1, direct frame: rank 0 copies frame i out of one frame slot while every rank traces frame i+1
+            # into the other; the peers are held back by the per-frame all-reduce
+            prev = None
+            for i in range(args.steps):
+                sc.render(params)
+                evt = sc.read_frame_async(pinned[i & 1]) if rank == 0 else None
+                if prev is not None:
+                    prev.synchronize()
+                prev = evt
+            if prev is not None:
+                prev.synchronize()
+            torch.cuda.synchronize(dev)
+
         for _ in range(3):
             sync_step()
         sync_s = timed(run_sync)
@@ -377,12 +395,21 @@ def run_b200_arm(args, workload):
             how = ("rc_render_frame(host params) + rc_read_image_async into one of two pinned host frames + rc_wait_image, "
                    "every step; frame N+1 is traced while frame N is copied (double-buffered like the reference's swap chain)")
             assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
+        elif args.frame_path == "direct":
+            run_pipelined_sharded()
+            e2e_s = timed(run_pipelined_sharded)
+            how = ("every rank: rc_render_frame(host params), kernels store into rank 0's frame over NVLink; rank 0: "
+                   "asynchronous copy of the whole frame into one of two pinned host frames, every step, while all ranks "
+                   "trace the next frame into the other frame slot")
+            if rank == 0:
+                assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
         e2e = {"value": frame_rays * args.steps / e2e_s / 1e6, "unit": UNIT,
                "h2d_bytes_per_step": 104, "d2h_bytes_per_step": w * h * 4,
                "ms_per_step": e2e_s / args.steps * 1e3,
                "sync_ms_per_step": sync_s / args.steps * 1e3,
                "sync_value": frame_rays * args.steps / sync_s / 1e6,
-               "what": how + ("; includes the NCCL band gather + compose on rank 0" if world_size > 1 else "")}
+               "what": how + ("; includes the NCCL band gather + compose on rank 0"
+                              if world_size > 1 and args.frame_path == "gather" else "")}
         if rank == 0:
             assert host_img.any(), "e2e frame is empty"
 
@@ -427,7 +454,9 @@ def run_b200_arm(args, workload):
                    "world_bytes": {"reference_format": int(info.ref_bytes), "packed": int(info.packed_bytes)},
                    "camera": "default (35,50,35) dir normalize(1,0,1)", "rays_per_step": frame_rays,
                    "l2": "flushed between steps (256 MB memset, outside the timed events)",
-                   "sharding": f"16-row bands round-robin over {world_size} GPUs, NCCL gather to rank 0 + compose kernel"
+                   "sharding": f"16-row bands round-robin over {world_size} GPUs, " + (
+                       "kernels store into rank 0's frame over NVLink peer memory (CUDA IPC), one-element all-reduce as the "
+                       "completion signal" if args.frame_path == "direct" else "NCCL gather to rank 0 + compose kernel")
                                if world_size > 1 else "none"},
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "kernel_ms": kern_ms,
         "roofline": roof, "roofline_kernels": roof_all, "clocks": clocks,

@@ -249,6 +249,25 @@ typedef struct rc_gen_info {
 } rc_gen_info;
 int rc_generate_world(const rc_gen_params* params, rc_gen_info* info);
 
+/* ---- multi-GPU: one frame written by every GPU ----------------------------------
+ * With rc_set_shard each process renders only its bands.  Instead of gathering the band buffers
+ * afterwards, the composing process (the "owner", usually rank 0) allocates the whole RC_RGBA8 frame
+ * with rc_frame_target_create and hands the returned CUDA IPC handles (RC_IPC_HANDLE_BYTES each, one
+ * per slot) to the other processes of the box, which map them with rc_frame_target_open.  From then
+ * on every rc_render_frame of that resolution ALSO stores each finished pixel at its place in the
+ * owner's frame, straight from the kernels over NVLink peer memory: the transfer rides along with the
+ * tracing, pixel by pixel; there is no gather and no compose pass.  The frame is complete on the owner
+ * once every process's frame has finished (order the streams with any cross-process signal, e.g. a
+ * one-element all-reduce enqueued after rc_render_frame).  slots = 2 alternates between two frames
+ * (frame N can be read while frame N+1 is written); all processes must render the same sequence of
+ * frames.  The reference has no counterpart (single GPU). */
+#define RC_IPC_HANDLE_BYTES 64
+int rc_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void* handles_out);
+int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const void* handles);
+int rc_frame_target_close(void);
+void* rc_frame_target_device(uint32_t slot); /* owner only: the frame, bottom row first */
+int rc_frame_target_last_slot(void);         /* slot the last rc_render_frame wrote, -1 = none */
+
 /* The last frame (RC_RGBA8) as a binary PPM, top row first: the headless stand-in for looking at
  * the window. Synchronises like rc_read_image. Sharded frames: this rank's rows, others black. */
 int rc_write_ppm(const char* path);

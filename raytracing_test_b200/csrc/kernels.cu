@@ -835,8 +835,16 @@ __device__ __forceinline__ uint32_t local_index(const FrameArgs& A, uint32_t px,
     return localRow * A.p.width + px;
 }
 
-__device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, F3 c) {
-    A.rgba8[idx] = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+// idx: this rank's compact buffers; framePixel: the pixel's place in the whole frame, for the direct
+// multi-GPU frame (rc_frame_target_*: a peer-mapped buffer on the composing GPU, written over NVLink)
+__device__ __forceinline__ uint32_t frame_pixel_of(const FrameArgs& A, uint32_t px, uint32_t localRow) {
+    const uint32_t row = ((localRow / BAND_ROWS) * A.world_size + A.rank) * BAND_ROWS + (localRow % BAND_ROWS);
+    return row * A.p.width + px;
+}
+__device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, uint32_t framePixel, F3 c) {
+    const uchar4 v = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+    A.rgba8[idx] = v;
+    if (A.frame_target) A.frame_target[framePixel] = v;
     if (A.rgba32f) A.rgba32f[idx] = make_float4(c.x, c.y, c.z, 0.0f);
 }
 
@@ -861,7 +869,7 @@ __global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ Fr
     if (active) {
         const uint32_t idx = local_index(A, px, localRow);
         // AO pixels get their final colour from the AO kernel
-        if (!(R.aoSeed)) store_pixel(A, idx, R.color);
+        if (!(R.aoSeed)) store_pixel(A, idx, frame_pixel_of(A, px, localRow), R.color);
         if (A.hits) A.hits[idx] = R.hit;
     }
 
@@ -889,7 +897,7 @@ __global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ Fr
                                                   : (R.hit.face == 1 ? (R.hit.flags & RC_HF_STEPY_NEG) : (R.hit.flags & RC_HF_STEPZ_NEG));
             // normal sign = -step[face]: negative normal iff the step was positive
             s.face_sign = (uint32_t)R.hit.face | (sneg ? 0u : 4u);
-            s.pad = 0;
+            s.frame_pixel = frame_pixel_of(A, px, localRow);
             A.ao_seeds[base + __popc(seedMask & ((1u << lane) - 1u))] = s;
         }
     }
@@ -1026,7 +1034,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_cached_kernel(const __grid_cons
         if (state != 0u) occluded++;
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
-    store_pixel(A, s.pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
+    store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
 }
 
@@ -1210,7 +1218,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
         occluded += hit;
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
-    store_pixel(A, s.pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
+    store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
 }
 

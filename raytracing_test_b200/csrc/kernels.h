@@ -31,7 +31,7 @@ struct AoSeed {
     float r, g, b;      // shaded colour before AO
     uint32_t pixel;     // index into the (compact) frame buffers
     uint32_t face_sign; // bits 0-1 face, bit 2: normal sign negative
-    uint32_t pad;
+    uint32_t frame_pixel; // index into the whole frame (py * width + px)
 };
 
 struct FrameCounters {
@@ -52,6 +52,7 @@ struct FrameArgs {
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
     uchar4* rgba8;           // [local_rows][width]
+    uchar4* frame_target;    // optional: the whole frame [height][width] on the composing GPU (peer memory)
     float4* rgba32f;         // optional
     rc_hit* hits;            // optional
     AoSeed* ao_seeds;        // optional (ao_samples > 0)

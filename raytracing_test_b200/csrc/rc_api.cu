@@ -54,6 +54,14 @@ struct Context {
         cudaEvent_t evCopied = nullptr;
     } slot[2];
     int cur = 0;
+    // rc_frame_target_*: the whole frame on the composing GPU, written directly by every rank's kernels
+    struct FrameTarget {
+        uint32_t width = 0, height = 0, slots = 0;
+        uchar4* ptr[2] = {nullptr, nullptr};
+        bool owner = false;
+        uint32_t seq = 0;
+        int lastSlot = -1;
+    } target;
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evRendered = nullptr;
     float4* dRgba32f = nullptr;
@@ -124,6 +132,16 @@ void freeFrameBuffers() {
     g.dSeeds = nullptr;
     g.pixelCapacity = g.f32Capacity = g.hitCapacity = g.seedCapacity = 0;
     g.haveFrame = false;
+}
+
+void closeFrameTarget() {
+    for (int i = 0; i < 2; i++) {
+        if (!g.target.ptr[i]) continue;
+        if (g.target.owner) cudaFree(g.target.ptr[i]);
+        else cudaIpcCloseMemHandle(g.target.ptr[i]);
+        g.target.ptr[i] = nullptr;
+    }
+    g.target = Context::FrameTarget();
 }
 
 // gen_hemisphare_distrib.py:4-12 with num_pts = n, in double, rounded to fp32;
@@ -197,6 +215,7 @@ void rc_shutdown(void) {
     cudaStreamSynchronize(g.stream);
     freeWorld();
     freeFrameBuffers();
+    closeFrameTarget();
     release_hemisphere();
     if (g.dCounters) cudaFree(g.dCounters);
     if (g.hCounters) cudaFreeHost(g.hCounters);
@@ -611,6 +630,11 @@ int rc_render_frame(const rc_frame_params* params) {
     a.local_rows = localRows;
     a.n_local_bands = localBands;
     a.rgba8 = g.dRgba8;
+    g.target.lastSlot = -1;
+    if (g.target.slots && p.width == g.target.width && p.height == g.target.height) {
+        g.target.lastSlot = (int)(g.target.seq++ % g.target.slots);
+        a.frame_target = g.target.ptr[g.target.lastSlot];
+    }
     a.rgba32f = (p.flags & RC_F_RGBA32F) ? g.dRgba32f : nullptr;
     a.hits = (p.flags & RC_F_HITS) ? g.dHits : nullptr;
     a.ao_seeds = p.ao_samples > 0 ? g.dSeeds : nullptr;
@@ -637,6 +661,69 @@ int rc_render_frame(const rc_frame_params* params) {
     g.haveFrame = true;
     return RC_OK;
 }
+
+int rc_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void* handles_out) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_create: call rc_init first");
+    if (width == 0 || height == 0 || width > 65536 || height > 65536 || slots == 0 || slots > 2 || !handles_out)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_target_create: %ux%u, %u slots", width, height, slots);
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameTarget();
+    g.target.owner = true;
+    for (uint32_t i = 0; i < slots; i++) {
+        CUDA_TRY(cudaMalloc((void**)&g.target.ptr[i], (size_t)width * height * 4));
+        CUDA_TRY(cudaMemsetAsync(g.target.ptr[i], 0, (size_t)width * height * 4, g.stream));
+        cudaIpcMemHandle_t h;
+        CUDA_TRY(cudaIpcGetMemHandle(&h, g.target.ptr[i]));
+        static_assert(sizeof(h) == RC_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+        memcpy((uint8_t*)handles_out + (size_t)i * RC_IPC_HANDLE_BYTES, &h, sizeof(h));
+    }
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    g.target.width = width;
+    g.target.height = height;
+    g.target.slots = slots;
+    return RC_OK;
+}
+
+int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const void* handles) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_open: call rc_init first");
+    if (width == 0 || height == 0 || slots == 0 || slots > 2 || !handles)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_target_open: %ux%u, %u slots", width, height, slots);
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameTarget();
+    for (uint32_t i = 0; i < slots; i++) {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const uint8_t*)handles + (size_t)i * RC_IPC_HANDLE_BYTES, sizeof(h));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            closeFrameTarget();
+            return fail(RC_ERR_CUDA, "rc_frame_target_open: cudaIpcOpenMemHandle: %s (no peer access between the two GPUs?)",
+                        cudaGetErrorString(e));
+        }
+        g.target.ptr[i] = (uchar4*)p;
+    }
+    g.target.width = width;
+    g.target.height = height;
+    g.target.slots = slots;
+    return RC_OK;
+}
+
+int rc_frame_target_close(void) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_close: call rc_init first");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameTarget();
+    return RC_OK;
+}
+
+void* rc_frame_target_device(uint32_t slot) {
+    if (!g.initialized || !g.target.owner || slot >= g.target.slots) return nullptr;
+    return g.target.ptr[slot];
+}
+
+int rc_frame_target_last_slot(void) { return g.initialized ? g.target.lastSlot : -1; }
 
 int rc_sync(void) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_sync: call rc_init first");

@@ -1,12 +1,19 @@
 """Image-tile sharding across the GPUs of one box: one process per GPU (torch.distributed), every
-rank holds the whole flattened world, renders the 16-row bands with band % world_size == rank
-(librc: rc_set_shard) into compact device buffers, and the finished bands are gathered to rank 0
-over NCCL / NVLink and de-interleaved into the frame by one librc kernel (rc_compose_frame).
+rank holds the whole flattened world and renders the 16-row bands with band % world_size == rank
+(librc: rc_set_shard).  Two ways for the bands to become one frame on rank 0:
 
-There is no data-path collective other than that gather.  torch is plumbing here:
-process group, device memory for the gathered bands, streams.  The same code runs on the gloo
-backend with CPU tensors (tests/test_multi_gpu_cpu.py), where the per-rank bands come from the
-test's renderer instead of librc.
+  direct (default on CUDA): rank 0 owns the whole frame (rc_frame_target_create), the other ranks
+      map it through CUDA IPC (rc_frame_target_open) and every rank's kernels store each finished
+      pixel straight into it over NVLink peer memory -- the transfer is fused into the tracing
+      kernels, there is no gather and no compose pass.  The only collective is a one-element
+      all-reduce after the kernels: the cross-process "frame complete" signal on the streams.
+  gather: the compact band buffers are gathered to rank 0 over NCCL and de-interleaved by one
+      librc kernel (rc_compose_frame).  Kept as the comparison baseline and for hosts without
+      peer access.
+
+torch is plumbing here: process group, handle exchange, streams.  The gather / compose logic also
+runs on the gloo backend with CPU tensors (tests/test_multi_gpu_cpu.py), where the per-rank bands
+come from the test's renderer instead of librc.
 """
 import numpy as np
 import torch
@@ -63,7 +70,11 @@ class ShardedRayCaster:
     """rc.RayCaster for one rank of a one-process-per-GPU job. All ranks call render(); rank 0's
     frame() returns the composed RGBA8 frame as a device tensor [height, width, 4]."""
 
-    def __init__(self, device_index, rank=None, world_size=None, group=None):
+    def __init__(self, device_index, rank=None, world_size=None, group=None, mode="direct", slots=2):
+        if mode not in ("direct", "gather"):
+            raise ValueError("mode must be 'direct' or 'gather'")
+        self.mode = mode
+        self.slots = slots
         self.group = group
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world_size is None else world_size
@@ -77,25 +88,81 @@ class ShardedRayCaster:
         self._frame = None
         self._gathered = None
         self._dims = None
+        self._token = None
+        self._frames = None
+        self._target_open = False
+        self._copy_stream = None
+        self._pending = {}  # frame slot -> event of the read-back still reading it (rank 0)
 
     def close(self):
+        if self._target_open:
+            self._close_target()
         self.caster.close()
+
+    def _meet(self):
+        """All ranks' streams have drained (device-side all-reduce + host sync): safe to map / unmap."""
+        dist.all_reduce(self._token, group=self.group)
+        torch.cuda.synchronize(self.device)
+
+    def _close_target(self):
+        # nobody may unmap / free while a peer's kernels can still write
+        self._meet()
+        self.caster.frame_target_close()
+        self._frames = None
+        self._target_open = False
+
+    def _open_target(self, w, h):
+        """Rank 0 allocates the frame(s), everyone else maps them (CUDA IPC handles travel as bytes)."""
+        if self._token is None:
+            self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if self._target_open:
+            self._close_target()
+        box = [self.caster.frame_target_create(w, h, self.slots) if self.rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=self.group)
+        if self.rank == 0:
+            self._frames = [device_bytes(self.caster.frame_target_ptr(s), h * w * 4, self.device).view(h, w, 4)
+                            for s in range(self.slots)]
+        else:
+            self.caster.frame_target_open(w, h, self.slots, box[0])
+        self._target_open = True
+        self._meet()  # every peer has the frame mapped before anyone renders into it
 
     def upload_world(self, desc):
         return self.caster.upload_world(desc)  # replicated: every rank uploads the same host world
 
     def render(self, params):
-        """Enqueue: local bands -> gather to rank 0 -> compose. Asynchronous on self.stream."""
+        """Enqueue one frame on self.stream (asynchronous): direct = kernels (storing into rank 0's frame) +
+        completion all-reduce; gather = kernels -> NCCL gather to rank 0 -> compose."""
         with torch.cuda.stream(self.stream):
             self._render(params)
 
     def _render(self, params):
         w, h = params.width, params.height
+        direct = self.world > 1 and self.mode == "direct"
+        if direct and self._dims != (w, h):
+            self._open_target(w, h)
+            self._dims = (w, h)
         self.caster.render_frame(params)
         pr = padded_rows(h, self.world)
         local = device_bytes(self.caster.device_image_ptr(rc.RC_RGBA8), pr * w * 4, self.device)
         if self.world == 1:
             self._frame = local[: h * w * 4].view(h, w, 4)
+            return
+        if direct:
+            # frame complete on rank 0 <=> every rank's kernels have finished: a one-element all-reduce queued
+            # behind them on each rank's stream (peer stores are visible when the storing kernel has completed)
+            slot = self.caster.frame_target_last_slot()
+            if self.rank == 0:
+                # once this all-reduce completes the peers may start the NEXT frame, which overwrites the other
+                # slot: a read-back still copying out of it must have finished before rank 0 lets them go
+                nxt = (slot + 1) % self.slots
+                ev = self._pending.pop(nxt, None)
+                if ev is not None:
+                    torch.cuda.current_stream(self.device).wait_event(ev)
+            dist.all_reduce(self._token, group=self.group)
+            if self.rank == 0:
+                self._frame = self._frames[slot]
+                self._slot = slot
             return
         if self._dims != (w, h):
             self._dims = (w, h)
@@ -110,6 +177,25 @@ class ShardedRayCaster:
 
     def frame(self):
         return self._frame if self.rank == 0 else None
+
+    def read_frame_async(self, pinned):
+        """Rank 0, direct mode: queues the copy of the last frame into `pinned` ([h, w, 4] uint8, pinned) on a
+        copy stream and returns an event; the next frame renders (on every rank) meanwhile into the other slot."""
+        if self.rank != 0:
+            return None
+        if self.world == 1 or self.mode != "direct":
+            raise RuntimeError("read_frame_async is the multi-GPU direct-mode read-back; world 1: RayCaster.read_image_async")
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(self.stream)
+        self._copy_stream.wait_event(ready)
+        with torch.cuda.stream(self._copy_stream):
+            pinned.copy_(self._frame, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(self._copy_stream)
+        self._pending[self._slot] = done
+        return done
 
     def stats(self):
         return self.caster.stats()

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(PKG_DIR, "librc.so")
 
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F = 1, 2, 4, 8
 RC_RGBA8, RC_RGBA32F = 0, 1
+RC_IPC_HANDLE_BYTES = 64
 RC_ALL_BLOCKS = 0xFFFFFFFF
 KIND_SKY, KIND_HIT, KIND_CAMERA_INSIDE, KIND_CROSSHAIR, KIND_HIGHLIGHT, KIND_DEBUG = range(6)
 HF_SHADOWED, HF_REFLECTED, HF_REFRACTED, HF_FACING_SUN = 1, 2, 4, 8
@@ -137,6 +138,11 @@ ABI = {
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_image_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int)]),
     "rc_wait_image": (ctypes.c_int, [ctypes.c_int]),
+    "rc_frame_target_create": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_frame_target_open": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_frame_target_close": (ctypes.c_int, []),
+    "rc_frame_target_device": (ctypes.c_void_p, [ctypes.c_uint32]),
+    "rc_frame_target_last_slot": (ctypes.c_int, []),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
     "rc_sync": (ctypes.c_int, []),
     "rc_frame_stats_get": (ctypes.c_int, [ctypes.POINTER(FrameStats)]),
@@ -310,6 +316,24 @@ class RayCaster:
 
     def wait_image(self, ticket):
         _check(self.lib, self.lib.rc_wait_image(ticket))
+
+    def frame_target_create(self, width, height, slots=2):
+        """rc_frame_target_create -> the IPC handles (bytes) the other ranks pass to frame_target_open."""
+        buf = ctypes.create_string_buffer(RC_IPC_HANDLE_BYTES * slots)
+        _check(self.lib, self.lib.rc_frame_target_create(width, height, slots, buf))
+        return buf.raw
+
+    def frame_target_open(self, width, height, slots, handles):
+        _check(self.lib, self.lib.rc_frame_target_open(width, height, slots, ctypes.create_string_buffer(handles, len(handles))))
+
+    def frame_target_close(self):
+        _check(self.lib, self.lib.rc_frame_target_close())
+
+    def frame_target_ptr(self, slot):
+        return self.lib.rc_frame_target_device(slot)
+
+    def frame_target_last_slot(self):
+        return self.lib.rc_frame_target_last_slot()
 
     def read_hits(self, out=None):
         w, h = self._last

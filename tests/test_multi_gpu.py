@@ -52,3 +52,67 @@ def test_sharded_frame_equals_single_gpu_frame(rcmod, caster, defaults, world, w
         assert torch.equal(ref, img)
     finally:
         caster.set_shard(0, 1)
+
+
+@pytest.mark.parametrize("world,w,h,slots", [(2, 640, 360, 1), (3, 333, 200, 2), (8, 1280, 720, 1), (8, 50, 40, 2)])
+def test_direct_frame_target_equals_single_gpu_frame(rcmod, caster, defaults, world, w, h, slots):
+    """rc_frame_target_*: every rank's kernels store their pixels straight into ONE whole frame (on a real box:
+    rank 0's, mapped by the peers over CUDA IPC / NVLink; here one process plays all ranks into its own
+    target).  The result must be the single-GPU frame byte for byte, with no gather and no compose."""
+    import torch
+
+    from raytracing_test_b200 import frame_gather as fg
+
+    pos, d, sun = defaults
+    p = rcmod.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=16)
+    caster.set_shard(0, 1)
+    caster.render_frame(p)
+    full_img = caster.read_image()
+    dev = torch.device("cuda", 0)
+    try:
+        handles = caster.frame_target_create(w, h, slots)
+        assert len(handles) == 64 * slots and any(handles)
+        frames = [fg.device_bytes(caster.frame_target_ptr(s), h * w * 4, dev).view(h, w, 4) for s in range(slots)]
+        assert caster.frame_target_ptr(slots) is None
+        for rounds in range(2):  # with 2 slots: the two rounds land in different frames only if world is odd
+            used = set()
+            for r in range(world):
+                caster.set_shard(r, world)
+                caster.render_frame(p)
+                used.add(caster.frame_target_last_slot())
+            caster.sync()
+            got = torch.zeros((h, w, 4), dtype=torch.uint8, device=dev)
+            for s in used:  # one process playing all ranks advances the slot per call: merge what each slot received
+                got |= frames[s]
+            assert np.array_equal(got.cpu().numpy(), full_img)
+            for s in range(slots):
+                frames[s].zero_()
+        # another resolution does not touch the target; the compact per-rank buffer still works beside it
+        caster.set_shard(0, 1)
+        caster.render_frame(rcmod.frame_params(w + 16, h, pos, d, sun, shadows=False))
+        assert caster.frame_target_last_slot() == -1
+        caster.render_frame(p)
+        assert caster.frame_target_last_slot() >= 0 and np.array_equal(caster.read_image(), full_img)
+    finally:
+        caster.set_shard(0, 1)
+        caster.frame_target_close()
+    caster.render_frame(p)
+    assert caster.frame_target_last_slot() == -1 and np.array_equal(caster.read_image(), full_img)
+
+
+def test_direct_frame_across_processes():
+    """tests/multi_gpu_direct.py under torchrun, one rank per GPU (needs >= 2 GPUs: `gpurun --gpus 2`)."""
+    import os
+    import subprocess
+    import sys
+
+    import torch
+
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("one GPU: the cross-process IPC path needs two (run with gpurun --gpus 2)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+                        "127.0.0.1", "--master-port", "29533", os.path.join(root, "tests", "multi_gpu_direct.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "direct frame ok" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
