@@ -384,6 +384,33 @@ def run_b200_arm(args, workload):
                 prev.synchronize()
             torch.cuda.synchronize(dev)
 
+        sink = {"frames": None, "next": 0}
+
+        def run_host_direct():
+            # N>1, no device-side gather at all: every rank reads ITS bands back into one shared, page-locked host
+            # frame (POSIX shared memory mapped by all ranks; rc_read_image_async scatters a sharded frame's rows to
+            # their place), all PCIe links at once; frame i travels while frame i+1 is traced.  Rank 0 consumes.
+            sh = sink["frames"]
+            prev = None
+
+            def finish(ticket, i):
+                sc.caster.wait_image(ticket)
+                sh.mark_landed(i)
+                if rank == 0:
+                    sh.acquire(i)
+                    sh.release(i)
+
+            for _ in range(args.steps):
+                i = sink["next"]
+                sink["next"] += 1
+                sc.caster.render_frame(params)
+                sh.wait_slot_free(i)
+                t = sc.caster.read_image_async(sh.frames[i % 2])
+                if prev is not None:
+                    finish(*prev)
+                prev = (t, i)
+            finish(*prev)
+
         for _ in range(3):
             sync_step()
         sync_s = timed(run_sync)
@@ -397,16 +424,24 @@ def run_b200_arm(args, workload):
             assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
         elif args.frame_path == "direct":
             run_pipelined_sharded()
-            e2e_s = timed(run_pipelined_sharded)
-            how = ("every rank: rc_render_frame(host params), kernels store into rank 0's frame over NVLink; rank 0: "
-                   "asynchronous copy of the whole frame into one of two pinned host frames, every step, while all ranks "
-                   "trace the next frame into the other frame slot")
+            rank0_s = timed(run_pipelined_sharded)
             if rank == 0:
                 assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
+            sink["frames"] = fg.SharedHostFrames(w, h, rank, world_size, slots=2, pin=sc.caster)
+            run_host_direct()
+            e2e_s = timed(run_host_direct)
+            if rank == 0:
+                for f in sink["frames"].frames:
+                    assert np.array_equal(f, host_imgs[0]), "frame assembled in shared host memory differs from rank 0's frame"
+            sink["frames"].close()
+            how = ("every rank: rc_render_frame(host params) + rc_read_image_async of ITS bands into one shared page-locked "
+                   "host frame (POSIX shared memory, two frame slots), every step; rank 0 consumes each complete frame; no "
+                   "device-side gather, all PCIe links in parallel")
         e2e = {"value": frame_rays * args.steps / e2e_s / 1e6, "unit": UNIT,
                "h2d_bytes_per_step": 104, "d2h_bytes_per_step": w * h * 4,
                "ms_per_step": e2e_s / args.steps * 1e3,
                "sync_ms_per_step": sync_s / args.steps * 1e3,
+               **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if world_size > 1 and args.frame_path == "direct" else {}),
                "sync_value": frame_rays * args.steps / sync_s / 1e6,
                "what": how + ("; includes the NCCL band gather + compose on rank 0"
                               if world_size > 1 and args.frame_path == "gather" else "")}

@@ -291,6 +291,14 @@ int rc_read_image(void* dst, size_t dst_bytes, int format);
 int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket);
 int rc_wait_image(int ticket);
 
+/* Page-locks host memory the caller owns (malloc, mmap, POSIX shared memory) for asynchronous copies.
+ * Multi-GPU hosts: map ONE shared-memory frame into every process, register it in each, and let every
+ * process rc_read_image_async into it -- a sharded frame's read-back writes only this rank's rows, at
+ * their place in the whole frame (rc_read_image does the same), so the frame assembles itself in host
+ * memory over all the GPUs' PCIe links at once, with no device-side gather at all. */
+int rc_host_register(void* ptr, size_t bytes);
+int rc_host_unregister(void* ptr);
+
 /* Parity records of the last frame rendered with RC_F_HITS; n >= width*height. */
 int rc_read_hits(rc_hit* dst, size_t n);
 

@@ -740,15 +740,24 @@ static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel, cuda
     if (g.worldSize == 1) {
         CUDA_TRY(cudaMemcpyAsync(dst, src, rowBytes * p.height, cudaMemcpyDeviceToHost, stream));
     } else {
+        // band lb of this rank is band lb * worldSize + rank of the frame: one strided copy for the full bands,
+        // one more for a partial last band
+        const size_t bandBytes = (size_t)BAND_ROWS * rowBytes;
+        uint32_t fullBands = 0, tailRows = 0;
         for (uint32_t lb = 0; lb < g.localBands; lb++) {
-            const uint32_t band = lb * g.worldSize + g.rank;
-            const uint32_t row0 = band * BAND_ROWS;
+            const uint32_t row0 = (lb * g.worldSize + g.rank) * BAND_ROWS;
             if (row0 >= p.height) break;
-            const uint32_t rows = (row0 + BAND_ROWS <= p.height) ? BAND_ROWS : (p.height - row0);
-            CUDA_TRY(cudaMemcpyAsync((uint8_t*)dst + (size_t)row0 * rowBytes,
-                                     (const uint8_t*)src + (size_t)lb * BAND_ROWS * rowBytes, rows * rowBytes,
-                                     cudaMemcpyDeviceToHost, stream));
+            if (row0 + BAND_ROWS <= p.height) fullBands++;
+            else tailRows = p.height - row0;
         }
+        uint8_t* first = (uint8_t*)dst + (size_t)g.rank * bandBytes;
+        if (fullBands)
+            CUDA_TRY(cudaMemcpy2DAsync(first, bandBytes * g.worldSize, src, bandBytes, bandBytes, fullBands,
+                                       cudaMemcpyDeviceToHost, stream));
+        if (tailRows)
+            CUDA_TRY(cudaMemcpyAsync(first + (size_t)fullBands * bandBytes * g.worldSize,
+                                     (const uint8_t*)src + (size_t)fullBands * bandBytes, tailRows * rowBytes,
+                                     cudaMemcpyDeviceToHost, stream));
     }
     if (wait) CUDA_TRY(cudaStreamSynchronize(stream));
     return RC_OK;
@@ -774,6 +783,22 @@ int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket) {
     CUDA_TRY(cudaEventRecord(g.slot[g.cur].evCopied, g.copyStream));
     g.slot[g.cur].copyPending = true;
     *ticket = g.cur;
+    return RC_OK;
+}
+
+int rc_host_register(void* ptr, size_t bytes) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_host_register: call rc_init first");
+    if (!ptr || bytes == 0) return fail(RC_ERR_INVALID_ARGUMENT, "rc_host_register: null / empty range");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return RC_OK;
+}
+
+int rc_host_unregister(void* ptr) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_host_unregister: call rc_init first");
+    if (!ptr) return fail(RC_ERR_INVALID_ARGUMENT, "rc_host_unregister: null");
+    if (g.copyStream) CUDA_TRY(cudaStreamSynchronize(g.copyStream));
+    CUDA_TRY(cudaHostUnregister(ptr));
     return RC_OK;
 }
 

@@ -209,3 +209,83 @@ def numpy_bands(full_frame, rank, world_size):
     rows = rc.band_rows_of_rank(h, rank, world_size)
     out[: len(rows)] = full_frame[rows]
     return out
+
+
+class SharedHostFrames:
+    """Host delivery without any device-side gather: `slots` whole RGBA8 frames in POSIX shared memory, mapped
+    by every rank of the box and page-locked in each (rc_host_register), plus two small counter arrays.  Every
+    rank reads its own bands back into the shared frame (rc_read_image_async scatters a sharded frame's rows to
+    their place), so a frame assembles itself in host memory over all the GPUs' PCIe links at once.
+
+    Protocol (single writer per counter, so plain stores are enough on one coherent host):
+      landed[r]  = number of frames rank r has completely delivered        (written by rank r)
+      consumed   = number of frames the consumer (rank 0) has released      (written by rank 0)
+    Rank r may start delivering frame i (into slot i % slots) once consumed >= i - slots + 1; the consumer owns
+    frame i once min(landed) >= i + 1.
+
+    pin=None: no page-locking (CPU tests of the protocol)."""
+
+    COUNTER_BYTES = 4096
+    SPIN_TIMEOUT_S = 30.0  # a peer that died must not leave the others spinning for ever
+
+    def __init__(self, width, height, rank, world_size, group=None, slots=2, pin=None):
+        from multiprocessing import shared_memory
+
+        self.rank, self.world, self.slots, self.group = rank, world_size, slots, group
+        self.frame_bytes = width * height * 4
+        size = slots * self.frame_bytes + self.COUNTER_BYTES
+        box = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=size)
+            self.shm.buf[size - self.COUNTER_BYTES:size] = bytes(self.COUNTER_BYTES)
+            box[0] = self.shm.name
+        dist.broadcast_object_list(box, src=0, group=group)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=box[0])
+        self.whole = np.ndarray((size,), dtype=np.uint8, buffer=self.shm.buf)
+        self.frames = [self.whole[s * self.frame_bytes:(s + 1) * self.frame_bytes].reshape(height, width, 4) for s in range(slots)]
+        counters = self.whole[slots * self.frame_bytes:].view(np.int64)
+        self.landed = counters[:world_size]
+        self.consumed = counters[64:65]
+        self._pin = pin
+        if pin is not None:
+            pin.host_register(self.whole)
+        dist.barrier(group=group)
+
+    def _spin(self, ready, what):
+        import time
+
+        if ready():
+            return
+        deadline = time.monotonic() + self.SPIN_TIMEOUT_S
+        while not ready():
+            if time.monotonic() > deadline:
+                raise TimeoutError(f"SharedHostFrames rank {self.rank}: {what} (landed {self.landed.tolist()}, "
+                                   f"consumed {int(self.consumed[0])})")
+
+    def wait_slot_free(self, i):
+        """Producer side, before delivering frame i."""
+        need = i - self.slots + 1
+        self._spin(lambda: int(self.consumed[0]) >= need, f"frame {i}: its slot was never released")
+
+    def mark_landed(self, i):
+        """Producer side, after frame i is complete in host memory (rc_wait_image returned)."""
+        self.landed[self.rank] = i + 1
+
+    def acquire(self, i):
+        """Consumer (rank 0): blocks until frame i is complete; returns it (valid until release(i))."""
+        self._spin(lambda: int(self.landed.min()) >= i + 1, f"frame {i} never completed")
+        return self.frames[i % self.slots]
+
+    def release(self, i):
+        self.consumed[0] = i + 1
+
+    def close(self):
+        dist.barrier(group=self.group)
+        if self._pin is not None:
+            self._pin.host_unregister(self.whole)
+        self.frames = self.landed = self.consumed = self.whole = None
+        self.shm.close()
+        dist.barrier(group=self.group)
+        if self.rank == 0:
+            self.shm.unlink()

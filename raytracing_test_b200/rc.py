@@ -138,6 +138,8 @@ ABI = {
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_image_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int)]),
     "rc_wait_image": (ctypes.c_int, [ctypes.c_int]),
+    "rc_host_register": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
+    "rc_host_unregister": (ctypes.c_int, [ctypes.c_void_p]),
     "rc_frame_target_create": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
     "rc_frame_target_open": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
     "rc_frame_target_close": (ctypes.c_int, []),
@@ -316,6 +318,13 @@ class RayCaster:
 
     def wait_image(self, ticket):
         _check(self.lib, self.lib.rc_wait_image(ticket))
+
+    def host_register(self, array):
+        """rc_host_register: page-locks the memory under a numpy array (e.g. over POSIX shared memory)."""
+        _check(self.lib, self.lib.rc_host_register(array.ctypes.data, array.nbytes))
+
+    def host_unregister(self, array):
+        _check(self.lib, self.lib.rc_host_unregister(array.ctypes.data))
 
     def frame_target_create(self, width, height, slots=2):
         """rc_frame_target_create -> the IPC handles (bytes) the other ranks pass to frame_target_open."""

@@ -6,7 +6,9 @@
 Every rank renders its bands; rank 0's frame, written by all ranks' kernels through CUDA IPC peer memory
 (frame_gather.ShardedRayCaster mode "direct"), must equal (a) the frame the NCCL gather + compose path
 produces and (b) the frame one GPU renders alone, byte for byte -- for several frames in a row (the two
-frame slots alternate), after a change of resolution, and through the pipelined read-back.
+frame slots alternate), after a change of resolution, and through the pipelined read-back; and so must the
+frame that assembles itself in shared page-locked HOST memory when every rank reads back only its own bands
+(frame_gather.SharedHostFrames: no device-side gather at all).
 Prints "direct frame ok" on rank 0."""
 import os
 import sys
@@ -64,6 +66,32 @@ def main():
         prev[0].synchronize()
         landed.append((prev[2], prev[1].numpy().copy()))
     torch.cuda.synchronize()
+
+    # host delivery with no device-side gather: every rank reads its own bands back into ONE shared page-locked
+    # host frame; rank 0 sees each frame complete and intact
+    sink = fg.SharedHostFrames(w, h, rank, world, slots=2, pin=direct.caster)
+    host_ok, prev = 0, None
+
+    def finish(ticket, i, yaw):
+        nonlocal host_ok
+        direct.caster.wait_image(ticket)
+        sink.mark_landed(i)
+        if rank == 0:
+            frame = sink.acquire(i)
+            assert np.array_equal(frame, alone[(1280, 720, yaw)]), f"shared host frame {i} (yaw {yaw}) differs"
+            host_ok += 1
+            sink.release(i)
+
+    for i, yaw in enumerate(yaws):
+        direct.caster.render_frame(rc.frame_params(w, h, pos, camera_dir(yaw, 15.0), sun, shadows=True, ao_samples=16))
+        sink.wait_slot_free(i)
+        t = direct.caster.read_image_async(sink.frames[i % 2])
+        if prev is not None:
+            finish(*prev)
+        prev = (t, i, yaw)
+    finish(*prev)
+    assert rank != 0 or host_ok == len(yaws)
+    sink.close()
     direct.close()
 
     gather = fg.ShardedRayCaster(local, rank, world, mode="gather")
@@ -83,7 +111,7 @@ def main():
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
-        print(f"direct frame ok: {len(views)} views x {world} ranks, {len(yaws)} pipelined frames")
+        print(f"direct frame ok: {len(views)} views x {world} ranks, {len(yaws)} pipelined frames, {host_ok} shared host frames")
 
 
 if __name__ == "__main__":

@@ -4,6 +4,7 @@ version of the same test lives in test_multi_gpu.py and renders them with librc)
 import os
 import socket
 import sys
+import time
 
 import numpy as np
 import pytest
@@ -88,6 +89,54 @@ def test_gloo_sharded_frame_equals_single_frame(world, w, h):
     q = ctx.Queue()
     port = _free_port()
     procs = [ctx.Process(target=_worker, args=(r, world, port, w, h, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
+
+
+def _host_frames_worker(rank, world, port, w, h, n_frames, q):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from raytracing_test_b200 import frame_gather as fg
+        from raytracing_test_b200 import rc
+
+        sink = fg.SharedHostFrames(w, h, rank, world, slots=2, pin=None)
+        rows = rc.band_rows_of_rank(h, rank, world)
+        ok = True
+        for i in range(n_frames):
+            # frame i: every pixel = i + 1 in the rows this rank owns; what rc_read_image_async does with a sharded
+            # frame (this rank's rows to their place, the others untouched), here by a numpy store
+            sink.wait_slot_free(i)
+            if rank == 1 and i % 3 == 0:
+                time.sleep(0.01)  # a slow producer: the consumer must wait for it, the fast ones must not lap it
+            sink.frames[i % 2][rows] = (i + 1) & 0xFF
+            sink.mark_landed(i)
+            if rank == 0:
+                frame = sink.acquire(i)
+                ok = ok and bool((frame == ((i + 1) & 0xFF)).all())
+                sink.release(i)
+        sink.close()
+        if rank == 0:
+            q.put(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h", [(2, 64, 100), (4, 33, 70)])
+def test_shared_host_frames_assemble_without_a_gather(world, w, h):
+    """SharedHostFrames: every rank delivers its bands into one shared-memory frame; the consumer sees each
+    frame complete and no producer overwrites a frame that has not been released (2 slots, 40 frames)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_host_frames_worker, args=(r, world, port, w, h, 40, q)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
