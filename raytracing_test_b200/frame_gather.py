@@ -242,6 +242,14 @@ class SharedHostFrames:
         dist.broadcast_object_list(box, src=0, group=group)
         if rank != 0:
             self.shm = shared_memory.SharedMemory(name=box[0])
+            # Python < 3.13 registers attached segments with this process's resource tracker too, which would
+            # unlink the creator's segment (and warn) when this process exits: rank 0 alone owns the name
+            try:
+                from multiprocessing import resource_tracker
+
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
         self.whole = np.ndarray((size,), dtype=np.uint8, buffer=self.shm.buf)
         self.frames = [self.whole[s * self.frame_bytes:(s + 1) * self.frame_bytes].reshape(height, width, 4) for s in range(slots)]
         counters = self.whole[slots * self.frame_bytes:].view(np.int64)
