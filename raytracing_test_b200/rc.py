@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "librc.so")
+LIB_PATH = os.environ.get("RC_LIBRC") or os.path.join(PKG_DIR, "librc.so")  # RC_LIBRC: a variant build (kernel tuning)
 
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F = 1, 2, 4, 8
 RC_RGBA8, RC_RGBA32F = 0, 1
