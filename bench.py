@@ -211,6 +211,49 @@ def run_reference_arm(args, workload):
     print(json.dumps(line), flush=True)
 
 
+def reference_ray_caster_sample(workload, target_rays=40000):
+    """The reference's OWN CPU traversal -- RAY_CASTER::castRayFromCam (src/ray_caster.cpp:54-87: double deltas, one
+    getBlock descent from the root per step), compiled unmodified into oracle/_ref/libref_world.so -- run with the
+    frame's step budget over a regular sample of this frame's primary ray directions, over the reference-built default
+    world.  BASELINE.json configs[0] names it as the reference CPU path.  One thread by construction (the camera is a
+    global of the reference).  None when the library was not built (needs /root/reference once, in the build container)."""
+    from oracle import bindings as ob  # checker side, timed as a baseline only
+    from raytracing_test_b200 import voxel_host as vh
+
+    if workload.startswith("config4"):
+        return None  # the reference's tree cannot hold the 2048^2 world (maxDepth 6)
+    try:
+        rw = ob.RefWorld()
+    except (FileNotFoundError, OSError):
+        return None
+    w, h, _, _, _ = WORKLOADS[workload]
+    pos, d, _ = vh.default_camera()
+    f = np.float32
+    step = max(1, int(np.sqrt(w * h / target_rays)))
+    px, py = np.meshgrid(np.arange(step // 2, w, step), np.arange(step // 2, h, step))
+    u = ((px.astype(f) + f(0.5)) * f(f(1.0) / f(w))).ravel()
+    v = ((py.astype(f) + f(0.5)) * f(f(1.0) / f(h))).ravel()
+    cam = d.astype(f)
+    left = np.cross(cam, np.array([0, 1, 0], dtype=f)).astype(f)  # low_res.frag:279-285
+    up = np.cross(cam, left).astype(f)
+    ppx, ppy = f(np.tan(np.radians(45.0))), f(np.tan(np.radians(45.0)) * f(h) / w)
+    dirs = cam[None, :] + left[None, :] * (-(ppx * (u - f(0.5))))[:, None] + up[None, :] * ((-v + f(0.5)) * ppy)[:, None]
+    dirs = (dirs / np.sqrt((dirs * dirs).sum(axis=1, keepdims=True))).astype(f)
+    dirs = np.ascontiguousarray(dirs)
+    out = np.zeros((len(dirs), 7), dtype=np.int32)
+    p = np.ascontiguousarray(pos, dtype=f)
+    best = None
+    for _ in range(3):
+        t = time.perf_counter()
+        rw.lib.refworld_pick_batch(p.ctypes.data, dirs.ctypes.data, len(dirs), 300, out.ctypes.data)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return {"value": len(dirs) / best / 1e6, "unit": "Mrays/s (primary rays only)", "cores": 1, "kind": "reference",
+            "sample": f"castRayFromCam(300) for every {step}th pixel of every {step}th row of the {w}x{h} frame ({len(dirs)} rays), "
+                      f"best of 3 ({best * 1e3:.0f} ms)",
+            "hits": int((out[:, 6] > 0).sum())}
+
+
 def cpu_baseline_leg(workload):
     """cpu_baseline object of the default arm: about 10-30 s of CPU work on rank 0."""
     w, h, shadows, ao, _ = WORKLOADS[workload]
@@ -224,12 +267,20 @@ def cpu_baseline_leg(workload):
         spent += dt
         reps += 1
     one_rays, one_dt, _ = cpu_render_sample(workload, max(stride, 4), threads=1)
-    return {
+    port = {
         "value": rays / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
         "sample": f"{'whole' if stride == 1 else f'every {stride}th 16-row band of the'} {w}x{h} frame, all passes, "
                   f"best of {reps} ({best * 1e3:.0f} ms), OpenMP x{cores}",
         "frame_ms": best * 1e3 * stride, "single_thread_value": one_rays / one_dt / 1e6,
     }
+    ref = reference_ray_caster_sample(workload)
+    if ref is not None:
+        if not shadows and not ao:
+            # config 1 (primary rays only) is exactly what the reference's own CPU ray caster does: it IS the baseline
+            ref = dict(ref, unit=UNIT, port=port)
+            return ref
+        port["reference_ray_caster"] = ref  # the reference's own compiled CPU traversal, primary rays only, beside the port
+    return port
 
 
 # ---------------------------------------------------------------------------------------------
