@@ -1145,9 +1145,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                         if (slice == 0u) continue;
 #pragma unroll
                         for (int y2 = 0; y2 < 4; y2++) {
-                            const uint32_t nib = (slice >> (4 * y2)) & 15u;
+                            // bits are stored MSB-first inside a word: bit p of the window = bit 31 - (p & 31), so that
+                            // the ray loop tests it with one shift into the sign bit
+                            const uint32_t nib = __brev((slice >> (4 * y2)) & 15u);  // the nibble reversed, in bits 28..31
                             const int p0 = pBrick + strideY * y2 + strideZ * z2;
-                            sWin[p0 >> 5][tid] |= nib << (p0 & 31);
+                            sWin[p0 >> 5][tid] |= nib >> (p0 & 31);
                         }
                     }
                 }
@@ -1209,7 +1211,10 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
             if (by) { qf += qyf; py = FADD(py, ady); }
             if (bz) { qf += qzf; pz = FADD(pz, adz); }
             const uint32_t q = __float_as_uint(qf);  // 0x4B000000 | index
-            hit = (win[((q >> 5) & 63u) * AO_THREADS] >> (q & 31u)) & 1u;
+            // word (q >> 5) & 63 of this thread's column; bit q & 31 sits at 31 - (q & 31): one shift into the sign bit
+            // (the column address cannot be OR-ed in: shared addresses start at 1024 on sm_100, whatever __align__ says)
+            const uint32_t word = win[((q >> 5) & 63u) * AO_THREADS];
+            hit = (uint32_t)((int32_t)(word << (q & 31u)) < 0);
             if (hit) break;
         }
         if (!covered)
