@@ -82,6 +82,16 @@ def golden_counters(case):
     return None
 
 
+def measured_instructions(workload, kernel):
+    """smsp__inst_executed.sum (warp instructions) of one launch of `kernel` from the same ncu capture; the count is
+    a property of the frame (same rays, same steps), not of the run."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[workload][kernel].get("warp_instructions_per_launch")
+    except Exception:
+        return None
+
+
 def measured_traffic(workload, kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full`
     capture of this workload (profiles/traffic.json, written by tools/ncu_traffic.py); None if not captured."""
@@ -520,6 +530,16 @@ def run_b200_arm(args, workload):
             if ms > 0:
                 ach = bytes_ / (ms * 1e-3) / 1e9
                 roof_all[name] = {"algorithmic_bytes_per_launch": bytes_, "ms": ms, "achieved": ach, "frac": ach / peak}
+        # what really bounds these kernels (profiles/*_ncu_full_summary.txt): instruction issue.  Issue-slot use of the
+        # launches timed here = warp instructions of the launch (ncu capture) / (launch time x 4 schedulers x SMs x clock)
+        sm_clock = (clocks or {}).get("sm_mhz")
+        if world_size == 1 and sm_clock:
+            slots_per_s = 4 * torch.cuda.get_device_properties(dev).multi_processor_count * sm_clock * 1e6
+            for name, r in roof_all.items():
+                inst = measured_instructions(workload, name)
+                if inst:
+                    r["issue_slots"] = {"warp_instructions_per_launch": inst, "peak_per_s": slots_per_s,
+                                        "frac": inst / (r["ms"] * 1e-3) / slots_per_s}
         dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
         if dom:
             roof = {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak, "unit": "GB/s",

@@ -18,22 +18,29 @@ def main():
     col = {h: i for i, h in enumerate(hdr)}
     acc = {}
     for r in rows[2:]:
-        name = r[col["Kernel Name"]].split("(")[0]
+        name = r[col["Kernel Name"]].split("(")[0].split("<")[0].replace("void ", "")
         tot = 0.0
         for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
             tot += float(r[col[m]].replace(",", "")) * UNIT[units[col[m]]]
         t_us = float(r[col["gpu__time_duration.sum"]].replace(",", ""))
         t_us *= {"us": 1.0, "ms": 1e3, "ns": 1e-3, "s": 1e6}.get(units[col["gpu__time_duration.sum"]], 1.0)
-        a = acc.setdefault(name, {"bytes": [], "us": []})
+        a = acc.setdefault(name, {"bytes": [], "us": [], "inst": [], "issue": []})
         a["bytes"].append(tot)
         a["us"].append(t_us)
+        if "smsp__inst_executed.sum" in col:
+            a["inst"].append(float(r[col["smsp__inst_executed.sum"]].replace(",", "")))
+        if "smsp__issue_active.avg.pct_of_peak_sustained_active" in col:
+            a["issue"].append(float(r[col["smsp__issue_active.avg.pct_of_peak_sustained_active"]].replace(",", "")))
     out_path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         out = json.load(open(out_path))
     except Exception:
         out = {}
     out[workload] = {k: {"dram_bytes_per_launch": sum(v["bytes"]) / len(v["bytes"]), "launches": len(v["bytes"]),
-                         "ncu_duration_us": sum(v["us"]) / len(v["us"]), "source": os.path.basename(path)}
+                         "ncu_duration_us": sum(v["us"]) / len(v["us"]),
+                         "warp_instructions_per_launch": sum(v["inst"]) / len(v["inst"]) if v["inst"] else None,
+                         "ncu_issue_active_pct": sum(v["issue"]) / len(v["issue"]) if v["issue"] else None,
+                         "source": os.path.basename(path)}
                      for k, v in acc.items()}
     json.dump(out, open(out_path, "w"), indent=1)
     print(json.dumps(out[workload], indent=1))
