@@ -344,7 +344,7 @@ def run_b200_arm(args, workload):
     barrier()
     st = sc.stats()
     local_rays = int(st.primary_rays + st.shadow_rays + st.ao_rays)
-    launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0 and args.frame_path == "gather") else 0)
+    launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0 and sc.mode == "gather") else 0)
 
     # ---- timed: K steps, device time by CUDA events on the launching stream, L2 flushed between steps ----
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -483,29 +483,37 @@ def run_b200_arm(args, workload):
             how = ("rc_render_frame(host params) + rc_read_image_async into one of two pinned host frames + rc_wait_image, "
                    "every step; frame N+1 is traced while frame N is copied (double-buffered like the reference's swap chain)")
             assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
-        elif args.frame_path == "direct":
+        elif sc.mode == "direct":
             run_pipelined_sharded()
             rank0_s = timed(run_pipelined_sharded)
             if rank == 0:
                 assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
-            sink["frames"] = fg.SharedHostFrames(w, h, rank, world_size, slots=2, pin=sc.caster)
-            run_host_direct()
-            e2e_s = timed(run_host_direct)
-            if rank == 0:
-                for f in sink["frames"].frames:
-                    assert np.array_equal(f, host_imgs[0]), "frame assembled in shared host memory differs from rank 0's frame"
-            sink["frames"].close()
-            how = ("every rank: rc_render_frame(host params) + rc_read_image_async of ITS bands into one shared page-locked "
-                   "host frame (POSIX shared memory, two frame slots), every step; rank 0 consumes each complete frame; no "
-                   "device-side gather, all PCIe links in parallel")
+            try:
+                sink["frames"] = fg.SharedHostFrames(w, h, rank, world_size, slots=2, pin=sc.caster)
+            except RuntimeError as e:  # raised on every rank together (no room in /dev/shm)
+                sink["frames"] = None
+                e2e_s = rank0_s
+                how = ("every rank: rc_render_frame(host params), kernels store into rank 0's frame over NVLink; rank 0: "
+                       "asynchronous copy of the whole frame into one of two pinned host frames, every step, while all ranks "
+                       f"trace the next frame (shared host frame unavailable: {e})")
+            if sink["frames"] is not None:
+                run_host_direct()
+                e2e_s = timed(run_host_direct)
+                if rank == 0:
+                    for f in sink["frames"].frames:
+                        assert np.array_equal(f, host_imgs[0]), "frame assembled in shared host memory differs from rank 0's frame"
+                sink["frames"].close()
+                how = ("every rank: rc_render_frame(host params) + rc_read_image_async of ITS bands into one shared page-locked "
+                       "host frame (POSIX shared memory, two frame slots), every step; rank 0 consumes each complete frame; no "
+                       "device-side gather, all PCIe links in parallel")
         e2e = {"value": frame_rays * args.steps / e2e_s / 1e6, "unit": UNIT,
                "h2d_bytes_per_step": 104, "d2h_bytes_per_step": w * h * 4,
                "ms_per_step": e2e_s / args.steps * 1e3,
                "sync_ms_per_step": sync_s / args.steps * 1e3,
-               **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if world_size > 1 and args.frame_path == "direct" else {}),
+               **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if world_size > 1 and sc.mode == "direct" else {}),
                "sync_value": frame_rays * args.steps / sync_s / 1e6,
                "what": how + ("; includes the NCCL band gather + compose on rank 0"
-                              if world_size > 1 and args.frame_path == "gather" else "")}
+                              if world_size > 1 and sc.mode == "gather" else "")}
         if rank == 0:
             assert host_img.any(), "e2e frame is empty"
 
@@ -562,7 +570,7 @@ def run_b200_arm(args, workload):
                    "l2": "flushed between steps (256 MB memset, outside the timed events)",
                    "sharding": f"16-row bands round-robin over {world_size} GPUs, " + (
                        "kernels store into rank 0's frame over NVLink peer memory (CUDA IPC), one-element all-reduce as the "
-                       "completion signal" if args.frame_path == "direct" else "NCCL gather to rank 0 + compose kernel")
+                       "completion signal" if sc.mode == "direct" else "NCCL gather to rank 0 + compose kernel")
                                if world_size > 1 else "none"},
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "kernel_ms": kern_ms,
         "roofline": roof, "roofline_kernels": roof_all, "clocks": clocks,

@@ -117,15 +117,41 @@ class ShardedRayCaster:
             self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         if self._target_open:
             self._close_target()
-        box = [self.caster.frame_target_create(w, h, self.slots) if self.rank == 0 else None]
-        dist.broadcast_object_list(box, src=0, group=self.group)
+        box = [None]
         if self.rank == 0:
+            try:
+                box[0] = self.caster.frame_target_create(w, h, self.slots)
+            except rc.RcError as e:
+                box[0] = e  # every rank must learn of it, or the others wait in the broadcast for ever
+        dist.broadcast_object_list(box, src=0, group=self.group)
+        ok = torch.ones(1, dtype=torch.int32, device=self.device)
+        if isinstance(box[0], Exception):
+            ok.zero_()
+        elif self.rank == 0:
             self._frames = [device_bytes(self.caster.frame_target_ptr(s), h * w * 4, self.device).view(h, w, 4)
                             for s in range(self.slots)]
         else:
-            self.caster.frame_target_open(w, h, self.slots, box[0])
+            try:
+                self.caster.frame_target_open(w, h, self.slots, box[0])
+            except rc.RcError as e:  # no peer access to rank 0's GPU from this one
+                self._open_error = e
+                ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        torch.cuda.synchronize(self.device)
+        if int(ok.item()) == 0:
+            # some rank cannot map the frame: all ranks fall back to the gather path together
+            self.caster.frame_target_close()
+            self._frames = None
+            self.mode = "gather"
+            self.fallback_reason = str(getattr(self, "_open_error", box[0] if isinstance(box[0], Exception) else "a peer rank"))
+            if self.rank == 0:
+                import sys
+
+                print(f"frame_gather: direct frame unavailable ({self.fallback_reason}); using the NCCL gather path", file=sys.stderr)
+            return False
         self._target_open = True
         self._meet()  # every peer has the frame mapped before anyone renders into it
+        return True
 
     def upload_world(self, desc):
         return self.caster.upload_world(desc)  # replicated: every rank uploads the same host world
@@ -140,8 +166,8 @@ class ShardedRayCaster:
         w, h = params.width, params.height
         direct = self.world > 1 and self.mode == "direct"
         if direct and self._dims != (w, h):
-            self._open_target(w, h)
-            self._dims = (w, h)
+            direct = self._open_target(w, h)
+            self._dims = (w, h) if direct else None
         self.caster.render_frame(params)
         pr = padded_rows(h, self.world)
         local = device_bytes(self.caster.device_image_ptr(rc.RC_RGBA8), pr * w * 4, self.device)
@@ -236,10 +262,15 @@ class SharedHostFrames:
         size = slots * self.frame_bytes + self.COUNTER_BYTES
         box = [None]
         if rank == 0:
-            self.shm = shared_memory.SharedMemory(create=True, size=size)
-            self.shm.buf[size - self.COUNTER_BYTES:size] = bytes(self.COUNTER_BYTES)
-            box[0] = self.shm.name
+            try:
+                self.shm = shared_memory.SharedMemory(create=True, size=size)
+                self.shm.buf[size - self.COUNTER_BYTES:size] = bytes(self.COUNTER_BYTES)
+                box[0] = self.shm.name
+            except OSError as e:  # /dev/shm too small for two frames
+                box[0] = e
         dist.broadcast_object_list(box, src=0, group=group)
+        if isinstance(box[0], Exception):
+            raise RuntimeError(f"SharedHostFrames: rank 0 could not create the shared segment: {box[0]}")
         if rank != 0:
             self.shm = shared_memory.SharedMemory(name=box[0])
             # Python < 3.13 registers attached segments with this process's resource tracker too, which would
