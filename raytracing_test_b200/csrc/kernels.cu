@@ -1098,15 +1098,20 @@ __device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, in
 // NSTEPS: ao_steps known at compile time (the loop unrolls), 0 = read it from the frame parameters.
 template <uint32_t NSTEPS>
 __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_constant__ FrameArgs A, const AoDir* __restrict__ table) {
-    __shared__ uint32_t sWin[AOW_WORDS][AO_THREADS];
+    // one window per DISTINCT (hit voxel, face, normal sign) of the warp, 48 words each.  Neighbouring pixels mostly see
+    // the same voxel face (1.14 distinct windows per 8x4 pixel tile of the benchmark frame), and the window depends on
+    // nothing else, so the warp builds each one ONCE, cooperatively (one lane per 4^3 brick), instead of 32 times.
+    __shared__ uint32_t sWin[AO_THREADS / 32][32][AOW_WORDS];
+    __shared__ uint32_t sLiquid[AO_THREADS / 32];
 
     const uint32_t nSeeds = A.counters->ao_seed_count;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= nSeeds) return;
-    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if ((t & ~31u) >= nSeeds) return;  // whole warp beyond the list
+    const bool valid = t < nSeeds;
     const rc_frame_params& P = A.p;
     const DeviceWorld& W = A.world;
-    const AoSeed s = A.ao_seeds[t];
+    const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];  // idle lanes of the last warp shadow a real seed
     const int face = (int)(s.face_sign & 3u);
     const bool negNormal = (s.face_sign & 4u) != 0u;
     const bool f0 = face == 0, f1 = face == 1;
@@ -1118,27 +1123,45 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const int b0x = (s.x + (f0 ? nOff : -4)) >> 2;
     const int b0y = (s.y + (f1 ? nOff : -4)) >> 2;
     const int b0z = (s.z + ((!f0 && !f1) ? nOff : -4)) >> 2;
-    const int nbx = f0 ? 2 : 3, nby = f1 ? 2 : 3, nbz = (!f0 && !f1) ? 2 : 3;
 
-#pragma unroll
-    for (int k = 0; k < AOW_WORDS; k++) sWin[k][tid] = 0u;
+    // lanes with the same window: exact match on (x, y | z, face_sign)
+    const unsigned long long k1 = (unsigned long long)(uint32_t)s.x | ((unsigned long long)(uint32_t)s.y << 32);
+    const unsigned long long k2 = (unsigned long long)(uint32_t)s.z | ((unsigned long long)s.face_sign << 32);
+    const unsigned peers = __match_any_sync(0xffffffffu, k1) & __match_any_sync(0xffffffffu, k2);
+    const uint32_t leader = (uint32_t)__ffs(peers) - 1u;
+    const unsigned leaders = __ballot_sync(0xffffffffu, lane == leader);
+    const uint32_t slot = (uint32_t)__popc(leaders & ((1u << leader) - 1u));
+    const uint32_t nSlots = (uint32_t)__popc(leaders);
 
-    // fill: one region fetch per brick (siblings share the cached parent node)
-    bool liquid = false;
+    uint32_t* const warpWin = &sWin[warp][0][0];
+    for (uint32_t i = lane; i < nSlots * AOW_WORDS; i += 32u) warpWin[i] = 0u;
+    if (lane == 0u) sLiquid[warp] = 0u;
+    __syncwarp();
+
+    // fill: task = (window, brick); 18 bricks per window (2 along the normal, 3 x 3 across)
     {
-        Cursor cur;
-        cursor_reset(W, cur);
-        Region r;
-        for (int bz = 0; bz < nbz; bz++) {
-            const int wz = wrap_coord(W, (b0z + bz) << 2);
-            for (int by = 0; by < nby; by++) {
-                const int wy = wrap_coord(W, (b0y + by) << 2);
-                for (int bx = 0; bx < nbx; bx++) {
-                    const int wx = wrap_coord(W, (b0x + bx) << 2);
-                    fetch_region(W, cur, wx, wy, wz, r);
-                    if (r.mask == 0ull) continue;
-                    if (r.info & BR_LIQUID) liquid = true;
-                    const int pBrick = (bx << 2) + strideY * (by << 2) + strideZ * (bz << 2);
+        const uint32_t nTasks = nSlots * 18u;
+        for (uint32_t base = 0; base < nTasks; base += 32u) {
+            const uint32_t task = base + lane;
+            const bool work = task < nTasks;
+            const uint32_t sl = work ? task / 18u : 0u, b = work ? task - sl * 18u : 0u;
+            const int src = (int)__fns(leaders, 0u, (int)sl + 1);  // lane of the sl-th leader
+            const int lb0x = __shfl_sync(0xffffffffu, b0x, src), lb0y = __shfl_sync(0xffffffffu, b0y, src);
+            const int lb0z = __shfl_sync(0xffffffffu, b0z, src);
+            const int lface = __shfl_sync(0xffffffffu, face, src);
+            if (work) {
+                // brick b of a window whose extent is 2 bricks along its normal axis and 3 along the others
+                const int nbx = lface == 0 ? 2 : 3, nby = lface == 1 ? 2 : 3;
+                const int bx = (int)b % nbx, by = ((int)b / nbx) % nby, bz = (int)b / (nbx * nby);
+                const int sY = aow_stride_y(lface), sZ = aow_stride_z(lface);
+                Cursor cur;
+                cursor_reset(W, cur);
+                Region r;
+                fetch_region(W, cur, wrap_coord(W, (lb0x + bx) << 2), wrap_coord(W, (lb0y + by) << 2), wrap_coord(W, (lb0z + bz) << 2), r);
+                if (r.mask != 0ull) {
+                    if (r.info & BR_LIQUID) atomicOr(&sLiquid[warp], 1u << sl);
+                    uint32_t* win = warpWin + sl * AOW_WORDS;
+                    const int pBrick = (bx << 2) + sY * (by << 2) + sZ * (bz << 2);
 #pragma unroll
                     for (int z2 = 0; z2 < 4; z2++) {
                         const uint32_t slice = (uint32_t)(r.mask >> (16 * z2)) & 0xFFFFu;
@@ -1148,14 +1171,17 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                             // bits are stored MSB-first inside a word: bit p of the window = bit 31 - (p & 31), so that
                             // the ray loop tests it with one shift into the sign bit
                             const uint32_t nib = __brev((slice >> (4 * y2)) & 15u);  // the nibble reversed, in bits 28..31
-                            const int p0 = pBrick + strideY * y2 + strideZ * z2;
-                            sWin[p0 >> 5][tid] |= nib >> (p0 & 31);
+                            const int p0 = pBrick + sY * y2 + sZ * z2;
+                            if (nib) atomicOr(&win[p0 >> 5], nib >> (p0 & 31));
                         }
                     }
                 }
             }
         }
     }
+    __syncwarp();
+    if (!valid) return;
+    const bool liquid = ((sLiquid[warp] >> slot) & 1u) != 0u;
 
     const float fx = (float)s.x, fy = (float)s.y, fz = (float)s.z;
     // (pos.exact - pos.round) for a positive and for a negative step sign (exact is biased by -1)
@@ -1166,7 +1192,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float q0f = 8388608.0f + (float)q0;
     const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
-    const uint32_t* win = &sWin[0][tid];
+    const uint32_t* win = warpWin + slot * AOW_WORDS;
 
     uint32_t occluded = 0;
     for (uint32_t k = 0; k < nSamples; k++) {
@@ -1212,8 +1238,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
             if (bz) { qf += qzf; pz = FADD(pz, adz); }
             const uint32_t q = __float_as_uint(qf);  // 0x4B000000 | index
             // word (q >> 5) & 63 of this thread's column; bit q & 31 sits at 31 - (q & 31): one shift into the sign bit
-            // (the column address cannot be OR-ed in: shared addresses start at 1024 on sm_100, whatever __align__ says)
-            const uint32_t word = win[((q >> 5) & 63u) * AO_THREADS];
+            const uint32_t word = win[(q >> 5) & 63u];
             hit = (uint32_t)((int32_t)(word << (q & 31u)) < 0);
             if (hit) break;
         }
