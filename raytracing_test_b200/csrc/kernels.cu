@@ -1063,7 +1063,8 @@ constexpr int AOW_WORDS = 48;
 // from the direction, precomputed on the host with the same IEEE operations.
 struct AoDir {
     float ix, iy, iz;   // ray.delta = 1 / dir
-    float qx, qy, qz;   // window stride of one step along each axis: sign(dir) * stride(face), as floats
+    float qx, qy, qz;   // window stride of one step along each axis, sign(dir) * stride(face), as the fp32 DENORMAL whose
+                        // bit pattern is that integer: denormals add like integers, and the sum's bits are the index itself
     float dx, dy;       // unused by the kernel (kept for debugging), pads the entry to 32 bytes
 };
 static_assert(sizeof(AoDir) == 32, "AoDir is two 128-bit loads");
@@ -1168,11 +1169,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                         if (slice == 0u) continue;
 #pragma unroll
                         for (int y2 = 0; y2 < 4; y2++) {
-                            // bits are stored MSB-first inside a word: bit p of the window = bit 31 - (p & 31), so that
-                            // the ray loop tests it with one shift into the sign bit
-                            const uint32_t nib = __brev((slice >> (4 * y2)) & 15u);  // the nibble reversed, in bits 28..31
-                            const int p0 = pBrick + sY * y2 + sZ * z2;
-                            if (nib) atomicOr(&win[p0 >> 5], nib >> (p0 & 31));
+                            // bits are stored MSB-first inside each BYTE: bit p of the window = bit 7 - (p & 7) of byte p >> 3,
+                            // so that the ray loop loads one byte at address (index >> 3) and shifts the bit into the sign
+                            const uint32_t nib = __brev((slice >> (4 * y2)) & 15u) >> 28;  // the nibble, reversed
+                            const int p0 = pBrick + sY * y2 + sZ * z2;                      // multiple of 4
+                            if (nib) atomicOr(&win[p0 >> 5], nib << ((p0 & 24) + 4 - (p0 & 4)));
                         }
                     }
                 }
@@ -1189,10 +1190,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
     const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
     const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
-    const float q0f = 8388608.0f + (float)q0;
+    // index of the hit voxel's bit, counted from shared address 0: 8 * (address of this lane's window) + q0, carried as
+    // the fp32 denormal with that bit pattern (< 2^23)
+    const float q0f = __uint_as_float(8u * (uint32_t)__cvta_generic_to_shared(warpWin + slot * AOW_WORDS) + (uint32_t)q0);
     const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
-    const uint32_t* win = warpWin + slot * AOW_WORDS;
 
     uint32_t occluded = 0;
     for (uint32_t k = 0; k < nSamples; k++) {
@@ -1214,9 +1216,9 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                                        qz < 0 ? -1 : 1, nSteps);
             continue;
         }
-        // The window index lives in the mantissa of a float (2^23 + q, exact): a step is a predicated
-        // FADD on the FMA pipe instead of select + integer add on the half-rate ALU pipe, and the word /
-        // bit indices are read straight from the bit pattern.
+        // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated
+        // FADD on the FMA pipe instead of select + integer add on the half-rate ALU pipe, and the byte address /
+        // bit number are read straight from the bit pattern.
         float qf = q0f;
         const float qxf = qx, qyf = qy, qzf = qz;
         uint32_t hit = 0u;
@@ -1236,10 +1238,11 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
             if (bx) { qf += qxf; px = FADD(px, adx); }
             if (by) { qf += qyf; py = FADD(py, ady); }
             if (bz) { qf += qzf; pz = FADD(pz, adz); }
-            const uint32_t q = __float_as_uint(qf);  // 0x4B000000 | index
-            // word (q >> 5) & 63 of this thread's column; bit q & 31 sits at 31 - (q & 31): one shift into the sign bit
-            const uint32_t word = win[(q >> 5) & 63u];
-            hit = (uint32_t)((int32_t)(word << (q & 31u)) < 0);
+            const uint32_t q = __float_as_uint(qf);  // 8 * shared address + bit number
+            uint32_t byte;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
+            // the byte in all four lanes of a word: a shift by q & 31 = 8 * k + (q & 7) then leaves bit 7 - (q & 7) in the sign
+            hit = (uint32_t)((int32_t)((byte * 0x01010101u) << (q & 31u)) < 0);
             if (hit) break;
         }
         if (!covered)
@@ -1358,9 +1361,15 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 o.ix = iv[0];
                 o.iy = iv[1];
                 o.iz = iv[2];
-                o.qx = (float)(d[0] < 0.0f ? -strides[0] : strides[0]);
-                o.qy = (float)(d[1] < 0.0f ? -strides[1] : strides[1]);
-                o.qz = (float)(d[2] < 0.0f ? -strides[2] : strides[2]);
+                auto denorm = [](bool neg, int stride) {
+                    const uint32_t bits = (neg ? 0x80000000u : 0u) | (uint32_t)stride;
+                    float f;
+                    memcpy(&f, &bits, 4);
+                    return f;
+                };
+                o.qx = denorm(d[0] < 0.0f, strides[0]);
+                o.qy = denorm(d[1] < 0.0f, strides[1]);
+                o.qz = denorm(d[2] < 0.0f, strides[2]);
                 o.dx = d[0];
                 o.dy = d[1];
             }
