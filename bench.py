@@ -541,17 +541,20 @@ def run_b200_arm(args, workload):
         # what really bounds these kernels (profiles/*_ncu_full_summary.txt): instruction issue.  Issue-slot use of the
         # launches timed here = warp instructions of the launch (ncu capture) / (launch time x 4 schedulers x SMs x clock)
         sm_clock = (clocks or {}).get("sm_mhz")
-        if world_size == 1 and sm_clock:
+        if sm_clock:
             slots_per_s = 4 * torch.cuda.get_device_properties(dev).multi_processor_count * sm_clock * 1e6
             for name, r in roof_all.items():
                 inst = measured_instructions(workload, name)
                 if inst:
+                    inst /= world_size
                     r["issue_slots"] = {"warp_instructions_per_launch": inst, "peak_per_s": slots_per_s,
                                         "frac": inst / (r["ms"] * 1e-3) / slots_per_s}
         dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
         if dom:
             roof = {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
-                    "frac": roof_all[dom]["frac"], "traffic": measured_traffic(workload, dom), "peak_source": peak_src,
+                    "frac": roof_all[dom]["frac"],
+                    # the capture is of one GPU rendering the whole frame; a rank of N renders 1/N of its bands
+                    "traffic": (measured_traffic(workload, dom) or 0) / world_size or None, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": roof_all[dom]["algorithmic_bytes_per_launch"],
                     "launch_ms": roof_all[dom]["ms"],
                     "note": "algorithmic bytes = what the REFERENCE algorithm fetches for this frame (16 B per nodes[] read + "

@@ -1,5 +1,5 @@
 """Developer probe for ncu: renders a few frames of one BASELINE config on cuda:0 and exits.
-python tools/profile_frame.py [width height shadows ao_samples frames max_steps]"""
+python tools/profile_frame.py [width height shadows ao_samples frames max_steps world_columns]"""
 import os
 import sys
 
@@ -12,10 +12,13 @@ sh = bool(int(a[2])) if len(a) >= 3 else True
 ao = int(a[3]) if len(a) >= 4 else 64
 frames = int(a[4]) if len(a) >= 5 else 4
 max_steps = int(a[5]) if len(a) >= 6 else 300
-host = vh.World.default()
+world = int(a[6]) if len(a) >= 7 else 200  # columns per side; 2048 = config 4's world (depth 7), generated on the device
 pos, d, sun = vh.default_camera()
 with rc.RayCaster(0) as c:
-    c.upload_world(host.describe())
+    if world == 200:
+        c.upload_world(vh.World.default().describe())
+    else:
+        c.generate_world(world, world, 7)
     p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao, max_steps=max_steps)
     for _ in range(frames):
         c.render_frame(p)
