@@ -582,23 +582,53 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 const float rem0 = (float)(numSteps - steps);
                 float rem = rem0;
                 float tx = pos.tx, ty = pos.ty, tz = pos.tz;
-                do {
-                    ax.x = tx < ty && tx < tz;
-                    ax.y = !ax.x && ty < tz;
-                    const bool az = !ax.x && !ax.y;
-                    if (ax.x) { tx = FADD(tx, ray.adx); fnx -= 1.0f; }
-                    if (ax.y) { ty = FADD(ty, ray.ady); fny -= 1.0f; }
-                    if (az) { tz = FADD(tz, ray.adz); fnz -= 1.0f; }
-                    rem -= 1.0f;
-                } while ((fnx * fny) * (fnz * rem) != 0.0f);
+                // An empty 4^3 cell is a child of the cursor's 16^3 node, whose mask says which of its 64 cells are empty:
+                // when the ray crosses into a sibling cell that is empty too, the walk goes on without a region change
+                // (no descent, no count_cell, no position recovery) -- five of a ray's nine region changes are of this kind.
+                // The cell's coordinates in the node (0..3) are kept biased by 4 in byte fields: a step out of the node shows
+                // up as a 3 or an 8 in its field and never borrows from the next one.
+                const bool walk = rg.r.shift == 2;
+                const uint32_t cell0 = 0x040404u + (uint32_t)((pos.x >> 2) & 3) + ((uint32_t)((pos.y >> 2) & 3) << 8) +
+                                       ((uint32_t)((pos.z >> 2) & 3) << 16);
+                uint32_t cell = cell0;
+                bool outOfSteps = false;
+                for (;;) {
+                    do {
+                        ax.x = tx < ty && tx < tz;
+                        ax.y = !ax.x && ty < tz;
+                        const bool az = !ax.x && !ax.y;
+                        if (ax.x) { tx = FADD(tx, ray.adx); fnx -= 1.0f; }
+                        if (ax.y) { ty = FADD(ty, ray.ady); fny -= 1.0f; }
+                        if (az) { tz = FADD(tz, ray.adz); fnz -= 1.0f; }
+                        rem -= 1.0f;
+                    } while ((fnx * fny) * (fnz * rem) != 0.0f);
+                    // keeps the compiler from folding the code below into the 16-instruction loop above (it would carry
+                    // pre-decrement copies of the countdowns through it: 22 instructions per step)
+                    asm volatile("" : "+f"(fnx), "+f"(fny), "+f"(fnz), "+f"(rem));
+                    if ((fnx * fny) * fnz != 0.0f) {  // out of steps inside the empty cell
+                        outOfSteps = true;
+                        break;
+                    }
+                    if (!walk) break;
+                    // the axis that stepped last reached its cell face: the ray is in the next cell along it
+                    const bool wz = !ax.x && !ax.y;  // the loop's own three predicates
+                    if (ax.x) { cell += (uint32_t)ray.sx; fnx = 4.0f; }
+                    if (ax.y) { cell += (uint32_t)ray.sy << 8; fny = 4.0f; }
+                    if (wz) { cell += (uint32_t)ray.sz << 16; fnz = 4.0f; }
+                    if (rem == 0.0f) break;                             // that was the last step of the budget
+                    if ((cell & 0x0C0C0Cu) != 0x040404u) break;         // left the 16^3 node
+                    const uint32_t ci = (cell & 3u) | ((cell >> 6) & 0xCu) | ((cell >> 12) & 0x30u);
+                    if ((cur.mask >> ci) & 1ull) break;                 // the next cell is not empty
+                }
                 pos.tx = tx;
                 pos.ty = ty;
                 pos.tz = tz;
-                pos.x += ray.sx * (n.nx - (int)fnx);
-                pos.y += ray.sy * (n.ny - (int)fny);
-                pos.z += ray.sz * (n.nz - (int)fnz);
+                // steps along an axis = first countdown + 4 per cell crossed - what is left of the current one
+                pos.x += ray.sx * (n.nx - (int)fnx) + 4 * ((int)(cell & 0xFFu) - (int)(cell0 & 0xFFu));
+                pos.y += ray.sy * (n.ny - (int)fny) + 4 * ((int)((cell >> 8) & 0xFFu) - (int)((cell0 >> 8) & 0xFFu));
+                pos.z += ray.sz * (n.nz - (int)fnz) + 4 * ((int)((cell >> 16) & 0xFFu) - (int)((cell0 >> 16) & 0xFFu));
                 steps += (uint32_t)(rem0 - rem);
-                if ((fnx * fny) * fnz != 0.0f) break;  // out of steps inside the empty cell
+                if (outOfSteps) break;
                 enter_region(W, cur, rg, pos);
             } else {
                 ax = dda_step_bl(ray, pos);
