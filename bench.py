@@ -13,8 +13,9 @@ default generated world (initTetraHexaTree + genWorld: seeds 42/64/100, 200 x 20
 One JSON line on stdout (rank 0). `value` = rays cast by all ranks / device time (max over ranks) with
 everything resident in HBM; `e2e` = the same through the C-ABI with the frame read back into pinned
 host memory every step (rc_render_frame + rc_read_image).
-`--impl reference` times the reference algorithm's CPU restatement (oracle/, all host threads) on a
-bounded sample of the same workload.
+`--impl reference` times the reference's CPU side on all host threads: for the workload its live shader covers
+in full (config 2) the shader's own source compiled as C++ (oracle/_ref/libref_shader.so); where AO is on -- a pass
+the reference never implemented -- the restatement (oracle/oracle_render.cpp) on a bounded sample of the workload.
 """
 import argparse
 import json
@@ -191,6 +192,8 @@ def run_reference_arm(args, workload):
         return
     w, h, shadows, ao, _ = WORKLOADS[workload]
     cores = os.cpu_count() or 1
+    if shadows and not ao and reference_shader_sample(workload, reps=1) is not None:
+        return run_reference_shader_arm(args, workload)  # config 2 = the live shader: time the reference's own source
     stride = max(1, (w * h) // (1920 * 1080) * 8)
     # keep the whole run within a few minutes whatever K is
     rays, dt, _ = cpu_render_sample(workload, stride)
@@ -217,6 +220,38 @@ def run_reference_arm(args, workload):
         "gpu_launches": 0,
         "note": "the reference renders frames only in GLSL (unavailable on this box); this is its traversal restated in "
                 "C++ (oracle/oracle_render.cpp, IEEE fp32) on all host threads",
+    }
+    shader = reference_shader_sample(workload)
+    if shader is not None:
+        # beside the port: the reference's own shader source on the same cores, for the passes it implements
+        line["cpu_baseline"]["reference_shader"] = shader
+    print(json.dumps(line), flush=True)
+
+
+def run_reference_shader_arm(args, workload):
+    """--impl reference for the workload the reference's live shader covers in full (primary + shadow rays):
+    each step is one pass of low_res.frag, compiled as C++, over the frame on all host threads."""
+    w, h, shadows, ao, _ = WORKLOADS[workload]
+    for _ in range(args.warmup):
+        reference_shader_sample(workload, reps=1)
+    total_rays, total_s, last = 0, 0.0, None
+    for _ in range(args.steps):
+        last = reference_shader_sample(workload, reps=1)
+        total_rays += last["rays"]
+        total_s += last["seconds"]
+    value = total_rays / total_s / 1e6
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao,
+                   "world": "default generated world (seeds 42/64/100, 200x200), built by the reference's own code",
+                   "sample": last["sample"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "reference", "sample": last["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference's own fragment shader (src/shaders/low_res.frag) compiled as C++ for the host cores "
+                "(oracle/ref_shader.cpp); GLSL on a GL driver is unavailable on this box",
     }
     print(json.dumps(line), flush=True)
 
@@ -264,6 +299,52 @@ def reference_ray_caster_sample(workload, target_rays=40000):
             "hits": int((out[:, 6] > 0).sum())}
 
 
+def reference_shader_sample(workload, threads=0, reps=3, state={}):
+    """The reference's OWN renderer on the host cores: src/shaders/low_res.frag compiled as C++ (oracle/ref_shader.cpp ->
+    oracle/_ref/libref_shader.so; GLSL itself cannot run on this box), one instance per pixel, OpenMP over rows, over the
+    world the reference's unmodified putBlock / genWorld built.  It is the live shader as it stands: primary + sun-shadow
+    rays (BASELINE configs 1-2; the reference has no AO pass to time).  Rays = pixels + shadow rays cast, the latter
+    counted by the oracle on the same frame (tests/test_ref_shader_cpu.py: same traversal float for float).
+    None when the library was not built (needs /root/reference once, in the build container)."""
+    from oracle import bindings as ob  # checker side, timed as a baseline only
+    from raytracing_test_b200 import voxel_host as vh
+
+    if workload.startswith("config4"):
+        return None  # MAX_DEPTH = 6 is a constant of the shader (low_res.frag:110)
+    w, h, _, _, _ = WORKLOADS[workload]
+    try:
+        if "world" not in state:
+            rw = ob.RefWorld()
+            state["world"] = (rw, ob.RefShader(rw.nodes, rw.arrays, oracle_math=False),
+                              ob.make_world(rw.nodes, rw.arrays, rw.max_depth))
+    except (FileNotFoundError, OSError):
+        return None
+    rw, shader, oworld = state["world"]
+    pos, d, sun = vh.default_camera()
+    row_stride = max(1, (w * h) // (1920 * 1080) // 2)  # 8K: every 8th row (about one 1080p frame of work)
+    key = (w, h, row_stride)
+    if key not in state:
+        # the oracle renders bands of rows; row_stride-spaced single rows = bands of 1 row with that stride
+        frame = ob.make_frame(w, h, pos, d, sun, shadows=True, ao_samples=0, bands=(1, row_stride, 0) if row_stride > 1 else None)
+        c = ob.render(oworld, frame, want_hits=False, want_rgba8=False)["counters"]
+        rays = int(c.rays[0] + c.rays[1])
+        assert int(c.rays[0]) == len(range(0, h, row_stride)) * w
+        state[key] = rays
+    rays = state[key]
+    best = None
+    for _ in range(reps):
+        t = time.perf_counter()
+        n = shader.render(w, h, pos, d, sun, row_stride=row_stride, threads=threads, want_state=False)["fragments"]
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    cores = threads if threads > 0 else (os.cpu_count() or 1)
+    what = "whole" if row_stride == 1 else f"every {row_stride}th row of the"
+    return {"value": rays / best / 1e6, "unit": "Mrays/s (primary + shadow rays: the live shader)", "cores": cores,
+            "kind": "reference", "rays": rays, "seconds": best, "fragments": n,
+            "sample": f"low_res.frag compiled as C++, {what} {w}x{h} frame ({n} fragments, {rays} rays), best of {reps} "
+                      f"({best * 1e3:.0f} ms), OpenMP x{cores}"}
+
+
 def cpu_baseline_leg(workload):
     """cpu_baseline object of the default arm: about 10-30 s of CPU work on rank 0."""
     w, h, shadows, ao, _ = WORKLOADS[workload]
@@ -284,12 +365,23 @@ def cpu_baseline_leg(workload):
         "frame_ms": best * 1e3 * stride, "single_thread_value": one_rays / one_dt / 1e6,
     }
     ref = reference_ray_caster_sample(workload)
+    shader = reference_shader_sample(workload)
+    if shader is not None and shadows and not ao:
+        # config 2 (primary + shadow) is exactly the reference's live shader: its own source, compiled for the host, IS the baseline
+        out = dict(shader, unit=UNIT, port=port)
+        if ref is not None:
+            out["reference_ray_caster"] = ref
+        return out
+    if ref is not None and not shadows and not ao:
+        # config 1 (primary rays only) is exactly what the reference's own CPU ray caster does: it IS the baseline
+        out = dict(ref, unit=UNIT, port=port)
+        if shader is not None:
+            out["reference_shader"] = shader
+        return out
     if ref is not None:
-        if not shadows and not ao:
-            # config 1 (primary rays only) is exactly what the reference's own CPU ray caster does: it IS the baseline
-            ref = dict(ref, unit=UNIT, port=port)
-            return ref
         port["reference_ray_caster"] = ref  # the reference's own compiled CPU traversal, primary rays only, beside the port
+    if shader is not None:
+        port["reference_shader"] = shader   # the reference's own shader source on the host cores: primary + shadow rays (no AO pass exists)
     return port
 
 

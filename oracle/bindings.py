@@ -6,6 +6,8 @@ ctypes bindings for the two checker libraries:
   (oracle_render.cpp)
 * ``oracle/_ref/libref_world.so`` -- the reference's own unmodified CPU sources
   (world builder, getBlock/putBlock, CPU picking ray), compiled by oracle/Makefile
+* ``oracle/_ref/libref_shader.so`` -- the reference's fragment shader src/shaders/low_res.frag compiled as C++
+  (oracle/ref_shader.cpp + oracle/shim/glsl/), one instance per pixel on the host cores
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 legs may import this module.  The product package never does.
@@ -19,6 +21,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "_build", "liboracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libref_world.so")
+REF_SHADER_SO = os.path.join(HERE, "_ref", "libref_shader.so")
 
 F_CROSSHAIR = 1
 F_SHADOWS = 2
@@ -274,3 +277,93 @@ def get_blocks(world, xyz):
     out = np.zeros((len(xyz), 2), dtype=np.uint64)
     oracle_lib().oracle_get_block_batch(ctypes.addressof(world), xyz.ctypes.data, len(xyz), out.ctypes.data)
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# The reference's own fragment shader on the host cores (oracle/ref_shader.cpp)
+class RefShaderFrame(ctypes.Structure):
+    _fields_ = [
+        ("origin", ctypes.c_float * 3), ("camera_dir", ctypes.c_float * 3), ("sun_dir", ctypes.c_float * 3),
+        ("mouse_pos", ctypes.c_float * 2), ("proj_plane", ctypes.c_float * 2), ("delta_time", ctypes.c_float),
+        ("looking_at", ctypes.c_int32 * 3), ("render_pos_data", ctypes.c_int32),
+        ("width", ctypes.c_uint32), ("height", ctypes.c_uint32),
+        ("row_begin", ctypes.c_uint32), ("row_end", ctypes.c_uint32),
+        ("col_stride", ctypes.c_uint32), ("row_stride", ctypes.c_uint32),
+        ("threads", ctypes.c_int32),
+    ]
+
+
+REF_SHADER_STATE = np.dtype(
+    [
+        ("round", "<i4", 3), ("exact", "<f4", 3), ("last_hit", "<u4"), ("reflected", "<u4"),
+        ("block_empty", "<u4"), ("refractive_index", "<f4"), ("color_mod", "<f4", 3),
+    ]
+)
+
+_ref_shader = None
+_MATH_FN = ctypes.CFUNCTYPE(ctypes.c_float, ctypes.c_float)
+
+
+def ref_shader_lib():
+    """low_res.frag as compiled C++.  Raises FileNotFoundError if it was never built here."""
+    global _ref_shader
+    if _ref_shader is None:
+        if not os.path.exists(REF_SHADER_SO):
+            if os.path.isdir("/root/reference/src"):
+                build(("ref",))
+            else:
+                raise FileNotFoundError(REF_SHADER_SO)
+        L = ctypes.CDLL(REF_SHADER_SO)
+        L.refshader_set_world.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.refshader_set_math.argtypes = [ctypes.c_void_p] * 3
+        L.refshader_render.restype = ctypes.c_longlong
+        L.refshader_render.argtypes = [ctypes.c_void_p] * 3
+        assert L.refshader_sizeof_frame() == ctypes.sizeof(RefShaderFrame)
+        assert L.refshader_sizeof_state() == REF_SHADER_STATE.itemsize
+        _ref_shader = L
+    return _ref_shader
+
+
+class RefShader:
+    """The reference's shader over flat copies of the host pools (what updateSsboData puts in the two SSBOs,
+    src/voxel_data/voxel_allocator.hpp:38-91).  `nodes` / `arrays` are kept alive here."""
+
+    def __init__(self, nodes, arrays, oracle_math=True):
+        self.lib = ref_shader_lib()
+        self.nodes = np.ascontiguousarray(nodes, dtype=np.uint64)
+        self.arrays = np.ascontiguousarray(arrays, dtype=np.uint32)
+        self.use_oracle_math(oracle_math)
+
+    def use_oracle_math(self, on):
+        """sin / exp of the shader: the oracle's deterministic ones (bit-for-bit colour comparisons) or libm."""
+        if on:
+            O = oracle_lib()
+            addr = lambda f: ctypes.cast(f, ctypes.c_void_p)
+            self.lib.refshader_set_math(addr(O.oracle_sinf), None, addr(O.oracle_expf))
+        else:
+            self.lib.refshader_set_math(None, None, None)
+
+    def render(self, width, height, origin, camera_dir, sun_dir, *, mouse_pos=None,
+               looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0, render_pos_data=0, rows=None,
+               col_stride=1, row_stride=1, threads=0, proj_plane=None, want_state=True):
+        f = RefShaderFrame()
+        f.origin[:] = [float(v) for v in origin]
+        f.camera_dir[:] = [float(v) for v in camera_dir]
+        f.sun_dir[:] = [float(v) for v in sun_dir]
+        # the reference always evaluates the crosshair test; "disabled" = a mouse position far off the frame
+        f.mouse_pos[:] = [float(v) for v in (mouse_pos if mouse_pos is not None else (-1.0e6, -1.0e6))]
+        f.proj_plane[:] = [float(v) for v in (proj_plane or default_proj_plane(width, height))]
+        f.delta_time = delta_time
+        f.looking_at[:] = list(looking_at)
+        f.render_pos_data = render_pos_data
+        f.width, f.height = width, height
+        f.row_begin, f.row_end = (0, height) if rows is None else rows
+        f.col_stride, f.row_stride, f.threads = col_stride, row_stride, threads
+        rgba = np.zeros((height, width, 4), dtype=np.float32)
+        state = np.zeros((height, width), dtype=REF_SHADER_STATE) if want_state else None
+        self.lib.refshader_set_world(self.nodes.ctypes.data, self.arrays.ctypes.data)
+        n = self.lib.refshader_render(ctypes.addressof(f), rgba.ctypes.data,
+                                      state.ctypes.data if state is not None else None)
+        if n < 0:
+            raise RuntimeError("refshader_render failed")
+        return {"rgba32f": rgba, "state": state, "fragments": int(n)}

@@ -6,14 +6,19 @@
  * box).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs may load it.  The product (librc.so) never does.
  *
- * PARITY STATUS: the reference holds no golden vectors for frames;
- * the oracle is pinned on everything the reference does let us pin here:
- * the world it traverses is built by the reference's own unmodified CPU code
- * (oracle/_ref), its getBlock state machine is checked voxel-for-voxel against
- * the reference's getBlock, its DDA against the reference's test.cpp scenario
- * and against RAY_CASTER::castRayFromCam.  The shader's own fp behaviour on a
- * GL driver is "unavailable on this box": frame parity is therefore "unpinned"
- * beyond those anchors, and says so in DESIGN.md.
+ * PARITY STATUS: pinned against the reference's shader SOURCE, unpinned at the GL
+ * driver.  oracle/ref_shader.cpp compiles src/shaders/low_res.frag itself as C++
+ * (oracle/_ref/libref_shader.so) and tests/test_ref_shader_cpu.py holds this
+ * restatement to it float for float (FragColor, the pos.exact / pos.round debug
+ * outputs, the globals' final state) over the baseline frames, a camera sweep and
+ * a material-zoo world.  The world it traverses is built by the reference's own
+ * unmodified CPU code (oracle/_ref/libref_world.so); its getBlock state machine
+ * is checked voxel for voxel against the reference's getBlock, its DDA against
+ * the reference's test.cpp scenario and RAY_CASTER::castRayFromCam.  What a GLSL
+ * compiler would do to the shader's float arithmetic (contraction, sin / exp /
+ * normalize) is "unavailable on this box" and stays unpinned; the reference holds
+ * no golden frames.  The AO pass has no reference implementation: its semantics
+ * are defined by this build.
  */
 #ifndef ORACLE_RENDER_H
 #define ORACLE_RENDER_H

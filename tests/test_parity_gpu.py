@@ -74,6 +74,37 @@ def test_config3_1080p_ao64(ob, rcmod, caster, oracle_world, defaults):
 
 
 
+def test_cuda_frame_equals_the_reference_shader_frame(ob, rcmod, caster, ref_world, defaults):
+    """No oracle in between: the CUDA frame against src/shaders/low_res.frag itself, compiled as C++
+    (oracle/_ref/libref_shader.so, see tests/test_ref_shader_cpu.py) -- FragColor float for float at config 2's
+    1920x1080, hit voxels / faces against the state the shader's globals are left in."""
+    try:
+        shader = ob.RefShader(ref_world.nodes, ref_world.arrays, oracle_math=True)
+    except FileNotFoundError:
+        pytest.skip("oracle/_ref/libref_shader.so not built (needs /root/reference once)")
+    pos, d, sun = defaults
+    w, h = 1920, 1080
+    look, _, _ = ref_world.pick(pos, d, 30)
+    look = tuple(int(v) for v in look)
+    ref = shader.render(w, h, pos, d, sun, looking_at=look, mouse_pos=(960.0, 540.0), delta_time=0.5)
+    caster.render_frame(rcmod.frame_params(w, h, pos, d, sun, hits=True, rgba32f=True, shadows=True, looking_at=look,
+                                           mouse_pos=(960.0, 540.0), delta_time=0.5))
+    img = caster.read_image(fmt=rcmod.RC_RGBA32F)
+    hits = caster.read_hits().reshape(h, w)
+    assert np.array_equal(ref["rgba32f"].view(np.uint32), img.view(np.uint32))
+    primary_only = (hits["shadow_steps"] == 0) & np.isin(hits["kind"], [0, 1, 4])
+    assert primary_only.sum() > w * h // 2
+    for k, n in enumerate("xyz"):
+        assert np.array_equal(ref["state"]["round"][..., k][primary_only], hits[n][primary_only])
+    stepped = primary_only & (hits["steps"] > 0)
+    assert np.array_equal(ref["state"]["last_hit"][stepped], hits["face"][stepped])
+    # and the debug outputs: pos.exact (one rounded product per DDA step) and pos.round of EVERY pixel
+    for mode in (1, 2):
+        ref = shader.render(w, h, pos, d, sun, render_pos_data=mode, want_state=False)
+        caster.render_frame(rcmod.frame_params(w, h, pos, d, sun, rgba32f=True, shadows=True, render_pos_data=mode))
+        assert np.array_equal(ref["rgba32f"].view(np.uint32), caster.read_image(fmt=rcmod.RC_RGBA32F).view(np.uint32))
+
+
 @pytest.mark.parametrize("cam", range(len(CAMERAS)))
 def test_camera_sweep(ob, rcmod, caster, oracle_world, defaults, cam):
     origin, yaw, pitch = CAMERAS[cam]
