@@ -1095,7 +1095,7 @@ struct AoDir {
     float ix, iy, iz;   // ray.delta = 1 / dir
     float qx, qy, qz;   // window stride of one step along each axis, sign(dir) * stride(face), as the fp32 DENORMAL whose
                         // bit pattern is that integer: denormals add like integers, and the sum's bits are the index itself
-    float dx, dy;       // unused by the kernel (kept for debugging), pads the entry to 32 bytes
+    float lx, ly;       // absDelta[face] when the face is x (lx) or y (ly), else 0: what deltaPos[face] is lowered by
 };
 static_assert(sizeof(AoDir) == 32, "AoDir is two 128-bit loads");
 
@@ -1145,7 +1145,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];  // idle lanes of the last warp shadow a real seed
     const int face = (int)(s.face_sign & 3u);
     const bool negNormal = (s.face_sign & 4u) != 0u;
-    const bool f0 = face == 0, f1 = face == 1;
+    const bool f0 = face == 0, f1 = face == 1, f2 = face >= 2;
     const int strideY = aow_stride_y(face), strideZ = aow_stride_z(face);
 
     // window origin in bricks (raw coordinates): tangent axes cover h-4 .. h+4, the normal axis
@@ -1226,59 +1226,59 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
 
+    // the index after the forced first step (through the hit face): q0 + sign(normal) * stride(face)
+    const float q1f = q0f + __uint_as_float((negNormal ? 0x80000000u : 0u) | (uint32_t)(f0 ? 1 : (f1 ? strideY : strideZ)));
+
     uint32_t occluded = 0;
     for (uint32_t k = 0; k < nSamples; k++) {
         const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
         const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
-        const float ix = v0.x, iy = v0.y, iz = v0.z;
+        const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
         const float qx = v0.w, qy = v1.x, qz = v1.y;  // never 0: the sign says which way the ray steps
         const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
-        // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face]
-        float px = FSUB(adx, FMUL(qx < 0 ? a1x : a0x, ix));
-        float py = FSUB(ady, FMUL(qy < 0 ? a1y : a0y, iy));
+        // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face].  The table holds absDelta[face]
+        // for the x and y faces and 0 otherwise (v - 0 = v exactly), so no branch on the face here
+        float px = FSUB(FSUB(adx, FMUL(qx < 0 ? a1x : a0x, ix)), v1.z);
+        float py = FSUB(FSUB(ady, FMUL(qy < 0 ? a1y : a0y, iy)), v1.w);
         float pz = FSUB(adz, FMUL(qz < 0 ? a1z : a0z, iz));
-        if (f0) px = FSUB(px, adx);
-        else if (f1) py = FSUB(py, ady);
-        else pz = FSUB(pz, adz);
+        if (f2) pz = FSUB(pz, adz);
 
-        if (liquid) {
-            occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
-                                       qz < 0 ? -1 : 1, nSteps);
-            continue;
-        }
-        // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated
-        // FADD on the FMA pipe instead of select + integer add on the half-rate ALU pipe, and the byte address /
-        // bit number are read straight from the bit pattern.
+        // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated FADD on the FMA
+        // pipe instead of select + integer add on the half-rate ALU pipe, and the byte address / bit number are read
+        // straight from the bit pattern.  No early exit on a hit: the warp runs until its last ray is done anyway, a ray
+        // that has hit stays inside the window (it covers every position ao_steps steps can reach), and without the
+        // branch the load of one step overlaps the compares of the next.
         float qf = q0f;
-        const float qxf = qx, qyf = qy, qzf = qz;
-        uint32_t hit = 0u;
-        const float px0 = px, py0 = py, pz0 = pz;
-        bool covered = true;
+        uint32_t acc = 0u;
+        bool window = !liquid;
 #pragma unroll
         for (uint32_t i = 0; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
             if (NSTEPS == 0 && i >= nSteps) break;
             const bool bx = px < py && px < pz;
             const bool by = !bx && py < pz;
             const bool bz = !bx && !by;
-            // the first step must be the forced one through the hit face, else the window does not cover the ray
             if (i == 0) {
-                covered = f0 ? bx : (f1 ? by : bz);
-                if (!covered) break;  // q would walk out of the window
+                if (!window) break;
+                // the first step must be the forced one through the hit face, else the window does not cover the ray
+                // (possible only through accumulated rounding of pos.exact): look where the index would go
+                const float qn = qf + (bx ? qx : (by ? qy : qz));
+                window = qn == q1f;  // compared as numbers = as bit patterns: both are positive denormals
+                if (!window) break;
             }
-            if (bx) { qf += qxf; px = FADD(px, adx); }
-            if (by) { qf += qyf; py = FADD(py, ady); }
-            if (bz) { qf += qzf; pz = FADD(pz, adz); }
+            if (bx) { qf += qx; px = FADD(px, adx); }
+            if (by) { qf += qy; py = FADD(py, ady); }
+            if (bz) { qf += qz; pz = FADD(pz, adz); }
             const uint32_t q = __float_as_uint(qf);  // 8 * shared address + bit number
             uint32_t byte;
             asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
             // the byte in all four lanes of a word: a shift by q & 31 = 8 * k + (q & 7) then leaves bit 7 - (q & 7) in the sign
-            hit = (uint32_t)((int32_t)((byte * 0x01010101u) << (q & 31u)) < 0);
-            if (hit) break;
+            acc |= (byte * 0x01010101u) << (q & 31u);
         }
-        if (!covered)
-            hit = ao_ray_general(W, s.x, s.y, s.z, px0, py0, pz0, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
-                                 qz < 0 ? -1 : 1, nSteps);
-        occluded += hit;
+        if (window)
+            occluded += acc >> 31;
+        else  // nothing has moved yet: (px, py, pz) is the state before the first step
+            occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
+                                       qz < 0 ? -1 : 1, nSteps);
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
     store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
@@ -1400,8 +1400,8 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 o.qx = denorm(d[0] < 0.0f, strides[0]);
                 o.qy = denorm(d[1] < 0.0f, strides[1]);
                 o.qz = denorm(d[2] < 0.0f, strides[2]);
-                o.dx = d[0];
-                o.dy = d[1];
+                o.lx = face == 0 ? fabsf(iv[0]) : 0.0f;
+                o.ly = face == 1 ? fabsf(iv[1]) : 0.0f;
             }
     }
     if (!g_aoTable) {
