@@ -41,6 +41,11 @@ namespace rc {
 
 __constant__ float c_hemi[3 * RC_MAX_AO_SAMPLES];      // (x, y, up) per sample
 __constant__ float c_hemi_inv[3 * RC_MAX_AO_SAMPLES];  // (1/x, 1/y, 1/up)
+// The window kernel's oriented table lists the samples grouped by the signs of their two tangent components:
+// c_aoSeg[g] .. c_aoSeg[g + 1] is group g = (x < 0) | (y < 0) << 1.  Inside a group every ray of a pixel steps the same
+// way along all three axes (the normal component's sign is the pixel's), so the per-axis choice between the two
+// (exact - round) values leaves the ray loop.  The order of the samples does not matter: occlusion is a count.
+__constant__ uint32_t c_aoSeg[5];
 
 struct F3 {
     float x, y, z;
@@ -1230,7 +1235,13 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float q1f = q0f + __uint_as_float((negNormal ? 0x80000000u : 0u) | (uint32_t)(f0 ? 1 : (f1 ? strideY : strideZ)));
 
     uint32_t occluded = 0;
-    for (uint32_t k = 0; k < nSamples; k++) {
+    for (uint32_t g = 0; g < 4u; g++) {
+    const uint32_t kBegin = c_aoSeg[g], kEnd = c_aoSeg[g + 1u];
+    if (kBegin == kEnd) continue;
+    // every sample of the group steps the same way along each axis: (exact - round) is chosen once, from the first one
+    const AoDir first = dirs[kBegin];
+    const float ax = first.qx < 0 ? a1x : a0x, ay = first.qy < 0 ? a1y : a0y, az = first.qz < 0 ? a1z : a0z;
+    for (uint32_t k = kBegin; k < kEnd; k++) {
         const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
         const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
         const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
@@ -1238,9 +1249,9 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
         const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
         // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face].  The table holds absDelta[face]
         // for the x and y faces and 0 otherwise (v - 0 = v exactly), so no branch on the face here
-        float px = FSUB(FSUB(adx, FMUL(qx < 0 ? a1x : a0x, ix)), v1.z);
-        float py = FSUB(FSUB(ady, FMUL(qy < 0 ? a1y : a0y, iy)), v1.w);
-        float pz = FSUB(adz, FMUL(qz < 0 ? a1z : a0z, iz));
+        float px = FSUB(FSUB(adx, FMUL(ax, ix)), v1.z);
+        float py = FSUB(FSUB(ady, FMUL(ay, iy)), v1.w);
+        float pz = FSUB(adz, FMUL(az, iz));
         if (f2) pz = FSUB(pz, adz);
 
         // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated FADD on the FMA
@@ -1279,6 +1290,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
         else  // nothing has moved yet: (px, py, pz) is the state before the first step
             occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
                                        qz < 0 ? -1 : 1, nSteps);
+    }
     }
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
     store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
@@ -1373,12 +1385,26 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
     e = cudaMemcpyToSymbolAsync(c_hemi_inv, inv, 3 * n * sizeof(float), 0, cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
 
-    // oriented table of the window kernel: d[face] = sg*up, d[(face+1)%3] = x, d[(face+2)%3] = y
+    // oriented table of the window kernel: d[face] = sg*up, d[(face+1)%3] = x, d[(face+2)%3] = y; samples grouped by
+    // the signs of (x, y), see c_aoSeg
     static AoDir host[6 * RC_MAX_AO_SAMPLES];
+    uint32_t order[RC_MAX_AO_SAMPLES], seg[5] = {0, 0, 0, 0, 0};
+    {
+        uint32_t m = 0;
+        for (uint32_t g = 0; g < 4; g++) {
+            seg[g] = m;
+            for (uint32_t k = 0; k < n; k++)
+                if ((uint32_t)(dirs[3 * k + 0] < 0.0f) + 2u * (uint32_t)(dirs[3 * k + 1] < 0.0f) == g) order[m++] = k;
+        }
+        seg[4] = m;  // == n
+    }
+    e = cudaMemcpyToSymbolAsync(c_aoSeg, seg, sizeof(seg), 0, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
     for (int face = 0; face < 3; face++) {
         const int strides[3] = {1, face == 0 ? 8 : 16, face == 0 ? 96 : (face == 1 ? 128 : 192)};
         for (int neg = 0; neg < 2; neg++)
-            for (uint32_t k = 0; k < n; k++) {
+            for (uint32_t slot = 0; slot < n; slot++) {
+                const uint32_t k = order[slot];
                 float d[3], iv[3];
                 const float up = dirs[3 * k + 2], iup = inv[3 * k + 2];
                 d[face] = neg ? -up : up;
@@ -1387,7 +1413,7 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 iv[(face + 1) % 3] = inv[3 * k + 0];
                 d[(face + 2) % 3] = dirs[3 * k + 1];
                 iv[(face + 2) % 3] = inv[3 * k + 1];
-                AoDir& o = host[(size_t)(face * 2 + neg) * RC_MAX_AO_SAMPLES + k];
+                AoDir& o = host[(size_t)(face * 2 + neg) * RC_MAX_AO_SAMPLES + slot];
                 o.ix = iv[0];
                 o.iy = iv[1];
                 o.iz = iv[2];
