@@ -1093,6 +1093,8 @@ __global__ void __launch_bounds__(AO_THREADS) ao_cached_kernel(const __grid_cons
 // ---------------------------------------------------------------------------
 constexpr uint32_t AOW_MAX_STEPS = 5;
 constexpr int AOW_WORDS = 48;
+constexpr uint32_t AOW_BYTE_SLOTS = 4;    // windows per warp in byte mode ...
+constexpr uint32_t AOW_BYTE_WORDS = 384;  // ... of 16 x 12 x 8 bytes: 4 * 384 = 32 * 48 words, the warp's share of sWin
 
 // One table entry per (orientation = face*2 + negative normal, sample): what buildRay derives
 // from the direction, precomputed on the host with the same IEEE operations.
@@ -1129,6 +1131,85 @@ __device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, in
         state = occlusion_state(W, g.r, p.x, p.y, p.z);
     }
     return state != 0u ? 1u : 0u;
+}
+
+// The rays of one pixel through its window.  BYTES: one byte per voxel (the window index is the shared-memory byte
+// address itself), else one bit per voxel, MSB-first inside each byte (index = 8 * address + bit number).
+struct AowRayArgs {
+    int x, y, z;                           // hit voxel
+    float q0f, q1f;                        // window index of the hit voxel / after the forced first step, as fp32 denormals
+    float a0x, a1x, a0y, a1y, a0z, a1z;    // (pos.exact - pos.round) for a positive / negative step sign
+    uint32_t nSteps;
+    bool liquid, f2;
+};
+
+template <uint32_t NSTEPS, bool BYTES>
+__device__ __forceinline__ uint32_t aow_cast_rays(const DeviceWorld& W, const AoDir* __restrict__ dirs, const AowRayArgs& a) {
+    const uint32_t nSteps = a.nSteps;
+    uint32_t occluded = 0;
+    for (uint32_t g = 0; g < 4u; g++) {
+        const uint32_t kBegin = c_aoSeg[g], kEnd = c_aoSeg[g + 1u];
+        if (kBegin == kEnd) continue;
+        // every sample of the group steps the same way along each axis: (exact - round) is chosen once, from the first one
+        const AoDir first = dirs[kBegin];
+        const float ax = first.qx < 0 ? a.a1x : a.a0x, ay = first.qy < 0 ? a.a1y : a.a0y, az = first.qz < 0 ? a.a1z : a.a0z;
+        for (uint32_t k = kBegin; k < kEnd; k++) {
+            const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
+            const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
+            const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
+            const float qx = v0.w, qy = v1.x, qz = v1.y;  // never 0: the sign says which way the ray steps
+            const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
+            // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face].  The table holds
+            // absDelta[face] for the x and y faces and 0 otherwise (v - 0 = v exactly), so no branch on the face here
+            float px = FSUB(FSUB(adx, FMUL(ax, ix)), v1.z);
+            float py = FSUB(FSUB(ady, FMUL(ay, iy)), v1.w);
+            float pz = FSUB(adz, FMUL(az, iz));
+            if (a.f2) pz = FSUB(pz, adz);
+
+            // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated FADD on the
+            // FMA pipe instead of select + integer add on the half-rate ALU pipe, and the address (and bit number) are
+            // read straight from the bit pattern.  No early exit on a hit: the warp runs until its last ray is done anyway,
+            // a ray that has hit stays inside the window (it covers every position ao_steps steps can reach), and without
+            // the branch the load of one step overlaps the compares of the next.
+            float qf = a.q0f;
+            uint32_t acc = 0u;
+            bool window = !a.liquid;
+#pragma unroll
+            for (uint32_t i = 0; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
+                if (NSTEPS == 0 && i >= nSteps) break;
+                const bool bx = px < py && px < pz;
+                const bool by = !bx && py < pz;
+                const bool bz = !bx && !by;
+                if (i == 0) {
+                    if (!window) break;
+                    // the first step must be the forced one through the hit face, else the window does not cover the ray
+                    // (possible only through accumulated rounding of pos.exact): look where the index would go
+                    const float qn = qf + (bx ? qx : (by ? qy : qz));
+                    window = qn == a.q1f;  // compared as numbers = as bit patterns: both are positive denormals
+                    if (!window) break;
+                }
+                if (bx) { qf += qx; px = FADD(px, adx); }
+                if (by) { qf += qy; py = FADD(py, ady); }
+                if (bz) { qf += qz; pz = FADD(pz, adz); }
+                const uint32_t q = __float_as_uint(qf);
+                uint32_t byte;
+                if (BYTES) {
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q) : "memory");
+                    acc |= byte;  // 0 or 1
+                } else {
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
+                    // the byte in all four lanes of a word: a shift by q & 31 = 8 * k + (q & 7) leaves bit 7 - (q & 7) in the sign
+                    acc |= (byte * 0x01010101u) << (q & 31u);
+                }
+            }
+            if (window)
+                occluded += BYTES ? acc : acc >> 31;
+            else  // nothing has moved yet: (px, py, pz) is the state before the first step
+                occluded += ao_ray_general(W, a.x, a.y, a.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
+                                           qz < 0 ? -1 : 1, nSteps);
+        }
+    }
+    return occluded;
 }
 
 // NSTEPS: ao_steps known at compile time (the loop unrolls), 0 = read it from the frame parameters.
@@ -1169,8 +1250,12 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const uint32_t slot = (uint32_t)__popc(leaders & ((1u << leader) - 1u));
     const uint32_t nSlots = (uint32_t)__popc(leaders);
 
+    // Few distinct windows (the usual case): one BYTE per voxel, AOW_BYTE_SLOTS windows of AOW_BYTE_WORDS words fill the
+    // warp's share exactly; a DDA step then needs no shift / mask to reach its voxel.  More: one bit per voxel.
+    const bool byteMode = nSlots <= AOW_BYTE_SLOTS;
+    const uint32_t slotWords = byteMode ? AOW_BYTE_WORDS : (uint32_t)AOW_WORDS;
     uint32_t* const warpWin = &sWin[warp][0][0];
-    for (uint32_t i = lane; i < nSlots * AOW_WORDS; i += 32u) warpWin[i] = 0u;
+    for (uint32_t i = lane; i < nSlots * slotWords; i += 32u) warpWin[i] = 0u;
     if (lane == 0u) sLiquid[warp] = 0u;
     __syncwarp();
 
@@ -1196,7 +1281,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                 fetch_region(W, cur, wrap_coord(W, (lb0x + bx) << 2), wrap_coord(W, (lb0y + by) << 2), wrap_coord(W, (lb0z + bz) << 2), r);
                 if (r.mask != 0ull) {
                     if (r.info & BR_LIQUID) atomicOr(&sLiquid[warp], 1u << sl);
-                    uint32_t* win = warpWin + sl * AOW_WORDS;
+                    uint32_t* win = warpWin + sl * slotWords;
                     const int pBrick = (bx << 2) + sY * (by << 2) + sZ * (bz << 2);
 #pragma unroll
                     for (int z2 = 0; z2 < 4; z2++) {
@@ -1204,11 +1289,17 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                         if (slice == 0u) continue;
 #pragma unroll
                         for (int y2 = 0; y2 < 4; y2++) {
-                            // bits are stored MSB-first inside each BYTE: bit p of the window = bit 7 - (p & 7) of byte p >> 3,
-                            // so that the ray loop loads one byte at address (index >> 3) and shifts the bit into the sign
-                            const uint32_t nib = __brev((slice >> (4 * y2)) & 15u) >> 28;  // the nibble, reversed
-                            const int p0 = pBrick + sY * y2 + sZ * z2;                      // multiple of 4
-                            if (nib) atomicOr(&win[p0 >> 5], nib << ((p0 & 24) + 4 - (p0 & 4)));
+                            const uint32_t row = (slice >> (4 * y2)) & 15u;   // the 4 voxels of one x-row of the brick
+                            const int p0 = pBrick + sY * y2 + sZ * z2;        // multiple of 4
+                            if (row == 0u) continue;
+                            if (byteMode) {
+                                // one word = exactly this row (bit i of the nibble -> byte i): no other task writes it
+                                win[p0 >> 2] = (row * 0x00204081u) & 0x01010101u;
+                            } else {
+                                // bits are stored MSB-first inside each BYTE: bit p of the window = bit 7 - (p & 7) of byte
+                                // p >> 3, so that the ray loop loads one byte at (index >> 3) and shifts the bit into the sign
+                                atomicOr(&win[p0 >> 5], (__brev(row) >> 28) << ((p0 & 24) + 4 - (p0 & 4)));
+                            }
                         }
                     }
                 }
@@ -1225,73 +1316,18 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
     const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
     const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
-    // index of the hit voxel's bit, counted from shared address 0: 8 * (address of this lane's window) + q0, carried as
-    // the fp32 denormal with that bit pattern (< 2^23)
-    const float q0f = __uint_as_float(8u * (uint32_t)__cvta_generic_to_shared(warpWin + slot * AOW_WORDS) + (uint32_t)q0);
-    const uint32_t nSamples = P.ao_samples, nSteps = NSTEPS ? NSTEPS : P.ao_steps;
+    // index of the hit voxel, counted from shared address 0: (8 *) address of this lane's window + q0, carried as the
+    // fp32 denormal with that bit pattern (< 2^23)
+    const uint32_t winAddr = (uint32_t)__cvta_generic_to_shared(warpWin + slot * slotWords);
+    const float q0f = __uint_as_float((byteMode ? winAddr : 8u * winAddr) + (uint32_t)q0);
+    const uint32_t nSteps = NSTEPS ? NSTEPS : P.ao_steps;
     const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
 
     // the index after the forced first step (through the hit face): q0 + sign(normal) * stride(face)
     const float q1f = q0f + __uint_as_float((negNormal ? 0x80000000u : 0u) | (uint32_t)(f0 ? 1 : (f1 ? strideY : strideZ)));
 
-    uint32_t occluded = 0;
-    for (uint32_t g = 0; g < 4u; g++) {
-    const uint32_t kBegin = c_aoSeg[g], kEnd = c_aoSeg[g + 1u];
-    if (kBegin == kEnd) continue;
-    // every sample of the group steps the same way along each axis: (exact - round) is chosen once, from the first one
-    const AoDir first = dirs[kBegin];
-    const float ax = first.qx < 0 ? a1x : a0x, ay = first.qy < 0 ? a1y : a0y, az = first.qz < 0 ? a1z : a0z;
-    for (uint32_t k = kBegin; k < kEnd; k++) {
-        const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
-        const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
-        const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
-        const float qx = v0.w, qy = v1.x, qz = v1.y;  // never 0: the sign says which way the ray steps
-        const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
-        // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face].  The table holds absDelta[face]
-        // for the x and y faces and 0 otherwise (v - 0 = v exactly), so no branch on the face here
-        float px = FSUB(FSUB(adx, FMUL(ax, ix)), v1.z);
-        float py = FSUB(FSUB(ady, FMUL(ay, iy)), v1.w);
-        float pz = FSUB(adz, FMUL(az, iz));
-        if (f2) pz = FSUB(pz, adz);
-
-        // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated FADD on the FMA
-        // pipe instead of select + integer add on the half-rate ALU pipe, and the byte address / bit number are read
-        // straight from the bit pattern.  No early exit on a hit: the warp runs until its last ray is done anyway, a ray
-        // that has hit stays inside the window (it covers every position ao_steps steps can reach), and without the
-        // branch the load of one step overlaps the compares of the next.
-        float qf = q0f;
-        uint32_t acc = 0u;
-        bool window = !liquid;
-#pragma unroll
-        for (uint32_t i = 0; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
-            if (NSTEPS == 0 && i >= nSteps) break;
-            const bool bx = px < py && px < pz;
-            const bool by = !bx && py < pz;
-            const bool bz = !bx && !by;
-            if (i == 0) {
-                if (!window) break;
-                // the first step must be the forced one through the hit face, else the window does not cover the ray
-                // (possible only through accumulated rounding of pos.exact): look where the index would go
-                const float qn = qf + (bx ? qx : (by ? qy : qz));
-                window = qn == q1f;  // compared as numbers = as bit patterns: both are positive denormals
-                if (!window) break;
-            }
-            if (bx) { qf += qx; px = FADD(px, adx); }
-            if (by) { qf += qy; py = FADD(py, ady); }
-            if (bz) { qf += qz; pz = FADD(pz, adz); }
-            const uint32_t q = __float_as_uint(qf);  // 8 * shared address + bit number
-            uint32_t byte;
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
-            // the byte in all four lanes of a word: a shift by q & 31 = 8 * k + (q & 7) then leaves bit 7 - (q & 7) in the sign
-            acc |= (byte * 0x01010101u) << (q & 31u);
-        }
-        if (window)
-            occluded += acc >> 31;
-        else  // nothing has moved yet: (px, py, pz) is the state before the first step
-            occluded += ao_ray_general(W, s.x, s.y, s.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
-                                       qz < 0 ? -1 : 1, nSteps);
-    }
-    }
+    const AowRayArgs ra{s.x, s.y, s.z, q0f, q1f, a0x, a1x, a0y, a1y, a0z, a1z, nSteps, liquid, f2};
+    const uint32_t occluded = byteMode ? aow_cast_rays<NSTEPS, true>(W, dirs, ra) : aow_cast_rays<NSTEPS, false>(W, dirs, ra);
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
     store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
