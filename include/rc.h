@@ -99,6 +99,9 @@ typedef struct rc_frame_params {
 #define RC_F_SHADOWS   0x2u  /* sun shadow ray (low_res.frag:373-391) */
 #define RC_F_HITS      0x4u  /* also write the per-pixel parity records (rc_read_hits) */
 #define RC_F_RGBA32F   0x8u  /* also keep the unclamped float colour (glReadPixels GL_FLOAT, main.cpp:38) */
+#define RC_F_NO_FREE_FLIGHT 0x10u /* tests / measurements: primary rays that rise above everything they can still reach
+                                     keep walking cells instead of finishing their steps in the free-flight loop
+                                     (same frame, same hit records either way) */
 
 #define RC_MAX_AO_SAMPLES 256u
 
@@ -142,7 +145,7 @@ typedef struct rc_frame_stats {
     uint64_t hit_pixels;     /* RC_KIND_HIT */
     uint64_t primary_steps;  /* DDA steps, summed (0 unless RC_F_HITS) */
     uint32_t kernel_launches;/* kernels launched by the last rc_render_frame */
-    uint32_t reserved;
+    uint32_t free_flight_rays; /* primary rays that finished their step budget in free flight (kernels.cu, loop A) */
     float primary_ms;        /* device time of each kernel of the last frame (CUDA events */
     float ao_ms;             /*   on the library's stream); valid after rc_sync/rc_read_* */
     float total_ms;

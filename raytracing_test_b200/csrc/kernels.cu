@@ -575,14 +575,32 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         StepAxis ax;
         ax.x = ax.y = false;
         bool act = live && word == 0u && numSteps != 0u;
+        bool freeFlight = false;
         while (act) {
             if (rg.r.mask == 0ull) {
+                // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach
+                // (A.sky_gate) has nothing left to hit: the remaining steps only move it, and run after this loop without
+                // cells, countdowns or the tree.  gateDist > 0: that far above the gate; <= 0: 1 - gateDist steps up to go.
+                int gateDist = -0x10000;
+                if (A.sky_gate && ray.sy > 0 && (uint32_t)pos.x <= W.wrap && (uint32_t)pos.z <= W.wrap) {
+                    const uint32_t q = (ray.sx < 0 ? 1u : 0u) | (ray.sz < 0 ? 2u : 0u);
+                    gateDist = pos.y - (int)__ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)pos.z >> A.sky_shift)) * SKY_GRID +
+                                                             ((uint32_t)pos.x >> A.sky_shift)]);
+                    if (gateDist > 0) {
+                        freeFlight = true;
+                        break;
+                    }
+                }
                 // Empty cell.  The integer side of a step (position, cell test, step budget) is kept
                 // as float countdowns -- voxels left to the cell's faces per axis, steps left -- so the
                 // loop body is FADD/FMUL on the FMA pipes plus five compares, instead of integer/logic
                 // work on the half-rate ALU pipe.  All values are small integers: exact in fp32.
                 CellCount n;
                 count_cell(n, ray, pos, rg.r.shift);
+                // a big cell that reaches above the gate: the countdown stops where the ray rises above it, the region is
+                // entered again there and the test above fires (4^3 cells keep their full count: the sibling walk below
+                // relies on it)
+                if (rg.r.shift > 2) n.ny = min(n.ny, 1 - gateDist);
                 float fnx = (float)n.nx, fny = (float)n.ny, fnz = (float)n.nz;
                 const float rem0 = (float)(numSteps - steps);
                 float rem = rem0;
@@ -645,6 +663,39 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
             }
             act = word == 0u && steps < numSteps;
+        }
+        if (freeFlight) {
+            // same comparisons, same additions (nextIntersectDDA, low_res.frag:446-491); nothing else per step
+            {
+                const unsigned m = __activemask();
+                if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&A.counters->free_flight_rays, (unsigned)__popc(m));
+            }
+            float tx = pos.tx, ty = pos.ty, tz = pos.tz;
+            const uint32_t left = numSteps - steps;  // >= 1
+#pragma unroll 4
+            for (uint32_t k = 0; k < left; k++) {
+                ax.x = tx < ty && tx < tz;
+                ax.y = !ax.x && ty < tz;
+                const bool az = !ax.x && !ax.y;
+                if (ax.x) tx = FADD(tx, ray.adx);
+                if (ax.y) ty = FADD(ty, ray.ady);
+                if (az) tz = FADD(tz, ray.adz);
+            }
+            // Steps per axis from the growth of deltaPos: n rounded additions of absDelta moved it by n * absDelta give or
+            // take n half-ulps of its final value -- with deltaPos <= 1.74 * max_steps + absDelta, absDelta >= 1 and
+            // max_steps <= 1024 (ff_enable) at most 0.11 * absDelta, so the quotient rounds to n.  An axis that never steps (absDelta = inf, deltaPos
+            // inf or NaN) has a difference of 0 or NaN.
+            const float gx = FSUB(tx, pos.tx), gy = FSUB(ty, pos.ty);
+            const int nx = gx > 0.0f ? (int)rintf(FDIV(gx, ray.adx)) : 0;
+            const int ny = gy > 0.0f ? (int)rintf(FDIV(gy, ray.ady)) : 0;
+            const int nz = (int)left - nx - ny;
+            pos.x += ray.sx * nx;
+            pos.y += ray.sy * ny;
+            pos.z += ray.sz * nz;
+            pos.tx = tx;
+            pos.ty = ty;
+            pos.tz = tz;
+            steps = numSteps;
         }
         if (!live) return;
         // the shader's counter: `while (empty && i++ < numSteps)` leaves numSteps + 1 behind when it runs out
@@ -1393,6 +1444,78 @@ __global__ void pick_kernel(DeviceWorld W, PickArgs a, int* out) {
     out[6] = left;
 }
 
+// Highest occupied y per column block (edge 2^bs voxels, SKY_GRID x SKY_GRID blocks over the torus), the input of the
+// sky gates (FrameArgs::sky_gate).  Thread (i, j) walks the subtree under child j of the root's child i depth-first with
+// an explicit stack; a uniform cell counts for every block it covers, a brick for the block it lies in (bs >= 2) with
+// its highest occupied layer.  Only nodes reachable from the root are seen, so runs abandoned by rc_update_world do
+// not count.
+struct TopsFrame {
+    unsigned long long mask, todo;
+    uint32_t base, kind;
+    int ox, oy, oz;
+};
+constexpr int TOPS_MAX_LEVELS = 12;
+__device__ __forceinline__ void tops_add_cell(int* tops, int bs, int x0, int z0, int edge, int top) {
+    const int bx0 = x0 >> bs, bx1 = (x0 + edge - 1) >> bs, bz0 = z0 >> bs, bz1 = (z0 + edge - 1) >> bs;
+    for (int bz = bz0; bz <= bz1; bz++)
+        for (int bx = bx0; bx <= bx1; bx++) atomicMax(&tops[(bz & (SKY_GRID - 1)) * SKY_GRID + (bx & (SKY_GRID - 1))], top);
+}
+__global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, int* tops) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;  // 4096 threads
+    const int ti = (int)(t >> 6), tj = (int)(t & 63u);
+    TopsFrame st[TOPS_MAX_LEVELS];
+    int sp = 0;
+    {
+        const uint4 n = __ldg(&W.nodes[0]);
+        st[0].mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        st[0].base = n.z;
+        st[0].kind = n.w;
+        st[0].ox = st[0].oy = st[0].oz = 0;
+        // this thread's share: child ti of the root and, one level down, child tj of that
+        st[0].todo = st[0].mask & (1ull << ti);
+    }
+    while (sp >= 0) {
+        TopsFrame& f = st[sp];
+        const int shift = W.root_shift - 2 * sp;  // log2 of the edge of this node's child cells
+        if ((f.kind & PK_KIND_MASK) == PK_BRICK || shift <= 0) {
+            // a brick (the root itself: thread 0 alone counts it)
+            if ((sp > 0 || t == 0u) && f.mask != 0ull) {
+                int ymax = 0;
+                for (int k = 1; k < 4; k++)
+                    if (f.mask & (0x000F000F000F000Full << (4 * k))) ymax = k;
+                tops_add_cell(tops, bs, f.ox, f.oz, 4, f.oy + ymax);
+            }
+            sp--;
+            continue;
+        }
+        if (f.todo == 0ull) {
+            sp--;
+            continue;
+        }
+        const int idx = __ffsll((long long)f.todo) - 1;
+        f.todo &= f.todo - 1ull;
+        const int cx = f.ox + ((idx & 3) << shift), cy = f.oy + (((idx >> 2) & 3) << shift), cz = f.oz + ((idx >> 4) << shift);
+        const uint32_t rank = (uint32_t)__popcll(f.mask & ((1ull << idx) - 1ull));
+        const uint4 n = __ldg(&W.nodes[f.base + rank]);
+        const uint32_t kind = n.w & PK_KIND_MASK;
+        if (kind == PK_LEAF) {
+            if (sp >= 1 || tj == 0) tops_add_cell(tops, bs, cx, cz, 1 << shift, cy + (1 << shift) - 1);
+            continue;
+        }
+        if (sp == 0 && kind == PK_BRICK && tj != 0) continue;  // a brick right under the root: thread (ti, 0) counts it
+        if (sp + 1 >= TOPS_MAX_LEVELS) continue;
+        TopsFrame& c = st[sp + 1];
+        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        c.base = n.z;
+        c.kind = n.w;
+        c.ox = cx;
+        c.oy = cy;
+        c.oz = cz;
+        c.todo = (sp == 0 && kind != PK_BRICK) ? (c.mask & (1ull << tj)) : c.mask;
+        sp++;
+    }
+}
+
 __global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -1521,6 +1644,13 @@ cudaError_t launch_pick(const DeviceWorld& world, const float* p, const float* d
     w.leak = 0u;  // the host's getBlock shifts signed ints: plain torus
     PickArgs a{p[0], p[1], p[2], d[0], d[1], d[2], steps};
     pick_kernel<<<1, 32, 0, stream>>>(w, a, out7);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_world_tops(const DeviceWorld& world, int skyShift, int* tops, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(tops, 0xFF, SKY_GRID * SKY_GRID * sizeof(int), stream);  // -1: empty
+    if (e != cudaSuccess) return e;
+    world_tops_kernel<<<32, 128, 0, stream>>>(world, skyShift, tops);
     return cudaGetLastError();
 }
 

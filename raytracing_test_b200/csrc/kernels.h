@@ -41,7 +41,8 @@ struct FrameCounters {
     unsigned long long primary_steps;
     unsigned int ao_seed_count;
     unsigned int tile_cursor;  // persistent-kernel work queue
-    unsigned int pad[2];
+    unsigned int free_flight_rays;  // primary rays that ended in the free-flight loop
+    unsigned int pad;
 };
 
 struct FrameArgs {
@@ -49,6 +50,13 @@ struct FrameArgs {
     DeviceWorld world;
     uint32_t rank, world_size;
     float inv_width, inv_height;  // 1.0f / width, 1.0f / height (low_res.frag:264: 1.0 / resolution)
+    // Free flight (primary loop A).  The world's columns are summarised in a SKY_GRID x SKY_GRID grid of column blocks
+    // (edge 2^sky_shift voxels); sky_gate[q][bz][bx] is the highest occupied y over every block a ray in block (bx, bz)
+    // can reach within max_steps steps when it heads the way of quadrant q = (step.x < 0) | (step.z < 0) << 1, or 32767
+    // when that window runs off the grid (torus wrap).  A ray that steps UP and is above its gate has nothing but empty
+    // space ahead.  Null: no gating (camera y + max_steps leaves the torus, max_steps too large, tree too shallow).
+    const short* sky_gate;
+    int sky_shift;
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
     uchar4* rgba8;           // [local_rows][width]
@@ -76,6 +84,11 @@ cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint
 // castRayFromCam (src/ray_caster.cpp:54-87) as a 1-thread kernel; out = device int[7]: pos, lastPos, steps left.
 cudaError_t launch_pick(const DeviceWorld& world, const float* cam_pos3, const float* cam_dir3, int steps, int* out7,
                         cudaStream_t stream);
+
+// Highest occupied y per column block of the packed tree -> tops = device int[SKY_GRID * SKY_GRID] ([bz][bx], -1 = empty);
+// block edge = 2^sky_shift voxels.  One depth-first walk per 64^3 subtree.
+constexpr int SKY_GRID = 64;
+cudaError_t launch_world_tops(const DeviceWorld& world, int sky_shift, int* tops, cudaStream_t stream);
 
 // Single-voxel lookups through the same device code path the kernels use (tests).
 cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,

@@ -69,6 +69,13 @@ struct Context {
     AoSeed* dSeeds = nullptr;
     size_t f32Capacity = 0, hitCapacity = 0, seedCapacity = 0;
     FrameCounters* dCounters = nullptr;
+    // sky gates (kernels.h, FrameArgs::sky_gate): column-block tops of the current world, the gate table built from them
+    int* dSkyTops = nullptr;
+    short* dSkyGate = nullptr;
+    std::vector<int> skyTops;
+    std::vector<short> skyGate;
+    int skyShift = 0;
+    uint32_t skyGateSteps = 0xFFFFFFFFu;  // max_steps the table on the device was built for (none)
     FrameCounters* hCounters = nullptr;  // pinned
     int* dPick = nullptr;
     int* hPick = nullptr;  // pinned
@@ -218,6 +225,11 @@ void rc_shutdown(void) {
     closeFrameTarget();
     release_hemisphere();
     if (g.dCounters) cudaFree(g.dCounters);
+    if (g.dSkyTops) cudaFree(g.dSkyTops);
+    if (g.dSkyGate) cudaFree(g.dSkyGate);
+    g.dSkyTops = nullptr;
+    g.dSkyGate = nullptr;
+    g.skyGateSteps = 0xFFFFFFFFu;
     if (g.hCounters) cudaFreeHost(g.hCounters);
     g.dCounters = nullptr;
     g.hCounters = nullptr;
@@ -331,6 +343,54 @@ static int ensureHostCopy() {
     return RC_OK;
 }
 
+// Column-block tops of the packed tree as it stands on the device (after every upload, update, load or generation).
+static int refreshSky() {
+    g.skyGateSteps = 0xFFFFFFFFu;
+    g.skyShift = (int)g.world.root_shift + 2 - 6;  // torus edge / SKY_GRID
+    g.skyTops.assign((size_t)SKY_GRID * SKY_GRID, -1);
+    if (g.skyShift < 2) return RC_OK;  // a brick would straddle blocks: no gating for such a shallow tree
+    if (!g.dSkyTops) CUDA_TRY(cudaMalloc((void**)&g.dSkyTops, g.skyTops.size() * sizeof(int)));
+    CUDA_TRY(launch_world_tops(g.world, g.skyShift, g.dSkyTops, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.skyTops.data(), g.dSkyTops, g.skyTops.size() * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    return RC_OK;
+}
+
+// Gate table for a step budget: per quadrant of horizontal headings, the highest top over the blocks within reach.
+static int ensureSkyGate(uint32_t maxSteps) {
+    if (g.skyGateSteps == maxSteps) return RC_OK;
+    const int G = SKY_GRID, OFF = 32767;
+    const int nb = (int)(((1u << g.skyShift) - 1u + maxSteps) >> g.skyShift);  // blocks a ray can cross along one axis
+    g.skyGate.assign((size_t)4 * G * G, (short)OFF);
+    std::vector<int> row((size_t)G * G);
+    for (int q = 0; q < 4; q++) {
+        const int dx = (q & 1) ? -1 : 1, dz = (q & 2) ? -1 : 1;
+        for (int bz = 0; bz < G; bz++)
+            for (int bx = 0; bx < G; bx++) {
+                int m = -1;
+                const int last = bx + dx * nb;
+                if (last < 0 || last >= G) m = OFF;  // the window runs off the grid: the ray may wrap around the torus
+                else
+                    for (int k = 0; k <= nb; k++) m = std::max(m, g.skyTops[(size_t)bz * G + bx + dx * k]);
+                row[(size_t)bz * G + bx] = m;
+            }
+        for (int bz = 0; bz < G; bz++)
+            for (int bx = 0; bx < G; bx++) {
+                int m = -1;
+                const int last = bz + dz * nb;
+                if (last < 0 || last >= G) m = OFF;
+                else
+                    for (int k = 0; k <= nb; k++) m = std::max(m, row[(size_t)(bz + dz * k) * G + bx]);
+                g.skyGate[((size_t)q * G + bz) * G + bx] = (short)std::min(m, OFF);
+            }
+    }
+    if (!g.dSkyGate) CUDA_TRY(cudaMalloc((void**)&g.dSkyGate, g.skyGate.size() * sizeof(short)));
+    CUDA_TRY(cudaMemcpyAsync(g.dSkyGate, g.skyGate.data(), g.skyGate.size() * sizeof(short), cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));  // pageable source
+    g.skyGateSteps = maxSteps;
+    return RC_OK;
+}
+
 // Replaces the device world with pw (arrays get slack for later appends) and fills g.info.
 static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     auto t1 = std::chrono::steady_clock::now();
@@ -362,7 +422,7 @@ static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     g.packed = std::move(pw);
     g.hostCopyStale = false;
     g.haveWorld = true;
-    return RC_OK;
+    return refreshSky();
 }
 
 int rc_upload_world(const rc_world_desc* desc) {
@@ -476,6 +536,7 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
         g.info.packed_materials = pw.palette.size();
         g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
         g.info.ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
+        if ((rcode = refreshSky()) != RC_OK) return rcode;
     }
     auto t2 = std::chrono::steady_clock::now();
     ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -548,7 +609,7 @@ int rc_generate_world(const rc_gen_params* params, rc_gen_info* info) {
     g.haveWorld = true;
     g.haveFrame = false;
     if (info) *info = gw.info;
-    return RC_OK;
+    return refreshSky();
 }
 
 int rc_write_ppm(const char* path) {
@@ -627,6 +688,17 @@ int rc_render_frame(const rc_frame_params* params) {
     a.inv_width = 1.0f / (float)p.width;
     a.inv_height = 1.0f / (float)p.height;
     a.world_size = g.worldSize;
+    {
+        // free flight needs: step counts recoverable from fp32 sums (kernels.cu, loop A: max_steps <= 1024), a tree deep
+        // enough for the column grid, and a camera whose y + max_steps stays on the torus (no wrap along y)
+        const float oy = floorf(p.origin[1]);
+        if (!(p.flags & RC_F_NO_FREE_FLIGHT) && p.max_steps <= 1024u && g.skyShift >= 2 && oy >= 0.0f &&
+            oy + (float)p.max_steps <= (float)g.world.wrap) {
+            if ((rcode = ensureSkyGate(p.max_steps)) != RC_OK) return rcode;
+            a.sky_gate = g.dSkyGate;
+            a.sky_shift = g.skyShift;
+        }
+    }
     a.local_rows = localRows;
     a.n_local_bands = localBands;
     a.rgba8 = g.dRgba8;
@@ -847,6 +919,7 @@ int rc_frame_stats_get(rc_frame_stats* out) {
     out->ao_rays = (uint64_t)g.hCounters->ao_seed_count * g.frame.ao_samples;
     out->primary_steps = g.hCounters->primary_steps;
     out->kernel_launches = g.launches;
+    out->free_flight_rays = g.hCounters->free_flight_rays;
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, g.evStart, g.evPrimary) == cudaSuccess) out->primary_ms = ms;
     if (cudaEventElapsedTime(&ms, g.evPrimary, g.evEnd) == cudaSuccess) out->ao_ms = ms;

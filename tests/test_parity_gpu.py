@@ -72,6 +72,33 @@ def test_config3_1080p_ao64(ob, rcmod, caster, oracle_world, defaults):
     assert np.array_equal(ref["rgba8"], got["rgba8"])
 
 
+def test_free_flight_changes_nothing(rcmod, caster, defaults):
+    """Primary rays that rise above every column they can still reach finish their step budget in the free-flight loop
+    (kernels.cu, loop A; FrameArgs::sky_gate).  Same frame, same hit records -- the final voxel of a sky ray after its 300
+    steps included -- with the loop on and off; and the loop does run for most sky rays of the default view."""
+    pos, d, sun = defaults
+    frames = {}
+    for ff in (True, False):
+        caster.render_frame(rcmod.frame_params(1920, 1080, pos, d, sun, shadows=True, ao_samples=16, hits=True, rgba32f=True,
+                                               free_flight=ff))
+        frames[ff] = (caster.read_image().copy(), caster.read_image(fmt=rcmod.RC_RGBA32F).copy(), caster.read_hits().copy(),
+                      caster.stats())
+    a, b = frames[True], frames[False]
+    assert a[2].tobytes() == b[2].tobytes()
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    assert b[3].free_flight_rays == 0
+    sky = int((a[2]["kind"] == 0).sum())  # RC_KIND_SKY
+    assert a[3].free_flight_rays > 0.5 * sky, (a[3].free_flight_rays, sky)
+    assert a[3].primary_steps == b[3].primary_steps
+    # other step budgets (the gate table is rebuilt per budget), a camera looking down, one high above the terrain
+    for steps, o, dd in ((64, pos, d), (1000, pos, d), (300, (100.5, 120.25, 100.5), camera_dir(30.0, -50.0)),
+                         (300, (60.5, 90.5, 20.5), camera_dir(-120.0, 20.0))):
+        got = []
+        for ff in (True, False):
+            caster.render_frame(rcmod.frame_params(640, 360, o, dd, sun, shadows=True, hits=True, max_steps=steps, free_flight=ff))
+            got.append((caster.read_image().copy(), caster.read_hits().copy()))
+        assert got[0][1].tobytes() == got[1][1].tobytes(), (steps, o)
+        assert np.array_equal(got[0][0], got[1][0])
 
 
 def test_cuda_frame_equals_the_reference_shader_frame(ob, rcmod, caster, ref_world, defaults):
