@@ -469,6 +469,63 @@ __device__ __forceinline__ F3 gen_sky(float dirX, float dirY, float dirZ, F3 sun
     return out;
 }
 
+// Free flight in closed form.  With nothing to test per step, the DDA is a merge of three independent sequences of event
+// times, t_a, fl(t_a + absDelta_a), fl(fl(t_a + absDelta_a) + absDelta_a), ...: it always fires the smallest, so its first
+// N steps are exactly the events earlier than some time T, whatever the tie order, and "every event before T has fired"
+// is a state the step-by-step loop passes through.  leap_axis fires those events for one axis without walking them:
+// inside one binade [2^e, 2^(e+1)) (ulp u) the rounded addition moves t by the same whole number of ulps every time,
+// c = RN(absDelta / u), as long as the exact sum stays below 2^(e+1) -- a half-way case (frac = 1/2) rounds to the even
+// mantissa, which is the same c every time once the mantissa is even, so an odd mantissa takes one real step first.  The
+// k additions up to min(T, 2^(e+1) - absDelta) are one multiply-add in fp64 (all values are multiples of 2^-24 below 2^12:
+// exact), the addition that crosses into the next binade is the real one.  Returns false outside that range (the caller
+// walks instead).  n += events fired.
+__device__ __forceinline__ bool leap_axis(float& t, const float a, const float T, int& n) {
+    if (!(t < T)) return true;  // nothing fires (t = inf / NaN: an axis that never steps)
+    if (!(a < 4096.0f)) {       // T < 2048: one event, the next one far beyond T (absDelta = inf included)
+        t = FADD(t, a);
+        n++;
+        return true;
+    }
+    if (!(t >= 0.5f && a >= 0.5f)) return false;
+    while (t < T) {
+        const int bits = __float_as_int(t);
+        const int e = (bits >> 23) - 127;  // t in [2^e, 2^(e+1)), u = 2^(e-23)
+        const double u = __longlong_as_double((long long)(e - 23 + 1023) << 52);
+        const double iu = __longlong_as_double((long long)(23 - e + 1023) << 52);
+        const double q = (double)a * iu;  // absDelta in ulps of t, exact
+        if ((bits & 1) && q - floor(q) == 0.5) {
+            t = FADD(t, a);
+            n++;
+            continue;
+        }
+        const double S = rint(q) * u;  // what one addition moves t by (>= 2^12 ulps: a >= 0.5, t < 2048)
+        const double X = (double)t;
+        const double B = fmin((double)T, u * 16777216.0 - (double)a);
+        if (B > X) {
+            const double k = ceil((B - X) / S);  // operands < 2^53 ulps apart and k <= 2^12: the quotient's rounding cannot reach the next integer
+            t = (float)(X + k * S);
+            n += (int)k;
+        }
+        if (t < T) {
+            t = FADD(t, a);
+            n++;
+        }
+    }
+    return true;
+}
+
+// The three axes of one ray; a real call (once per sky ray) so that the fp64 temporaries do not count against the
+// registers of the loops around it.  t[] in / out; returns the events fired, or -1 (walk instead).
+__device__ __noinline__ int leap_axes(float* t, float ax, float ay, float az, float T) {
+    float lx = t[0], ly = t[1], lz = t[2];
+    int fired = 0;
+    if (!(leap_axis(lx, ax, T, fired) && leap_axis(ly, ay, T, fired) && leap_axis(lz, az, T, fired))) return -1;
+    t[0] = lx;
+    t[1] = ly;
+    t[2] = lz;
+    return fired;
+}
+
 struct PixelResult {
     F3 color;
     rc_hit hit;
@@ -671,7 +728,27 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&A.counters->free_flight_rays, (unsigned)__popc(m));
             }
             float tx = pos.tx, ty = pos.ty, tz = pos.tz;
-            const uint32_t left = numSteps - steps;  // >= 1
+            const uint32_t total = numSteps - steps;  // >= 1
+            uint32_t left = total;
+            if (left >= 24u && !(P.flags & RC_F_NO_LEAP)) {
+                // T = a time by which at most left - 4 events have fired: an axis fires at most (T - T0) / absDelta * (1 + 2^-13)
+                // + 1 events from T0 on (its additions are off by at most half an ulp of t < 2048 each), and the three
+                // 1 / absDelta add up to |dir.x| + |dir.y| + |dir.z|
+                const float T0 = fminf(fminf(tx, ty), tz);
+                const float rate = (fabsf(ray.dx) + fabsf(ray.dy)) + fabsf(ray.dz);
+                const float T = T0 + (float)(left - 7u) / rate;
+                // a NaN deltaPos (0 * inf in buildRay) on y or z makes the else-branch axis fire every time: not a merge
+                if (rate >= 0.5f && T < 2048.0f && ty == ty && tz == tz) {
+                    float t3[3] = {tx, ty, tz};
+                    const int fired = leap_axes(t3, ray.adx, ray.ady, ray.adz, T);
+                    if (fired >= 0 && (uint32_t)fired < left) {
+                        tx = t3[0];
+                        ty = t3[1];
+                        tz = t3[2];
+                        left -= (uint32_t)fired;
+                    }
+                }
+            }
 #pragma unroll 4
             for (uint32_t k = 0; k < left; k++) {
                 ax.x = tx < ty && tx < tz;
@@ -688,7 +765,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
             const float gx = FSUB(tx, pos.tx), gy = FSUB(ty, pos.ty);
             const int nx = gx > 0.0f ? (int)rintf(FDIV(gx, ray.adx)) : 0;
             const int ny = gy > 0.0f ? (int)rintf(FDIV(gy, ray.ady)) : 0;
-            const int nz = (int)left - nx - ny;
+            const int nz = (int)total - nx - ny;
             pos.x += ray.sx * nx;
             pos.y += ray.sy * ny;
             pos.z += ray.sz * nz;
@@ -936,7 +1013,10 @@ __device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, ui
 
 // grid.x = ceil(width/16), grid.y = local_rows/8 ; block = 128 threads = 4 warps,
 // each warp an 8x4 pixel tile, the block a 16x8 tile.
-__global__ void __launch_bounds__(128) primary_kernel(const __grid_constant__ FrameArgs A) {
+#ifndef RC_PRIMARY_MIN_BLOCKS
+#define RC_PRIMARY_MIN_BLOCKS 8  // 64 registers: 8 CTAs of 128 threads per SM
+#endif
+__global__ void __launch_bounds__(128, RC_PRIMARY_MIN_BLOCKS) primary_kernel(const __grid_constant__ FrameArgs A) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
     const uint32_t localRow = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);

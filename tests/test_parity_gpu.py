@@ -73,32 +73,42 @@ def test_config3_1080p_ao64(ob, rcmod, caster, oracle_world, defaults):
 
 
 def test_free_flight_changes_nothing(rcmod, caster, defaults):
-    """Primary rays that rise above every column they can still reach finish their step budget in the free-flight loop
-    (kernels.cu, loop A; FrameArgs::sky_gate).  Same frame, same hit records -- the final voxel of a sky ray after its 300
-    steps included -- with the loop on and off; and the loop does run for most sky rays of the default view."""
+    """Primary rays that rise above every column they can still reach finish their step budget in free flight
+    (kernels.cu, loop A; FrameArgs::sky_gate): most of the remaining steps in closed form (leap_axis), the last few one by
+    one.  Same frame, same hit records -- the final voxel and last face of a sky ray after its 300 steps included -- with
+    free flight off, with the leap off (every step walked), and with both on; and both do run for most sky rays of the
+    default view."""
     pos, d, sun = defaults
+    modes = {"on": {}, "walk": {"leap": False}, "off": {"free_flight": False}}
     frames = {}
-    for ff in (True, False):
-        caster.render_frame(rcmod.frame_params(1920, 1080, pos, d, sun, shadows=True, ao_samples=16, hits=True, rgba32f=True,
-                                               free_flight=ff))
-        frames[ff] = (caster.read_image().copy(), caster.read_image(fmt=rcmod.RC_RGBA32F).copy(), caster.read_hits().copy(),
-                      caster.stats())
-    a, b = frames[True], frames[False]
-    assert a[2].tobytes() == b[2].tobytes()
-    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    for name, kw in modes.items():
+        caster.render_frame(rcmod.frame_params(1920, 1080, pos, d, sun, shadows=True, ao_samples=16, hits=True, rgba32f=True, **kw))
+        frames[name] = (caster.read_image().copy(), caster.read_image(fmt=rcmod.RC_RGBA32F).copy(), caster.read_hits().copy(),
+                        caster.stats())
+    b = frames["off"]
+    for name in ("on", "walk"):
+        a = frames[name]
+        assert a[2].tobytes() == b[2].tobytes(), name
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), name
+        assert a[3].primary_steps == b[3].primary_steps
+        sky = int((a[2]["kind"] == 0).sum())  # RC_KIND_SKY
+        assert a[3].free_flight_rays > 0.5 * sky, (name, a[3].free_flight_rays, sky)
     assert b[3].free_flight_rays == 0
-    sky = int((a[2]["kind"] == 0).sum())  # RC_KIND_SKY
-    assert a[3].free_flight_rays > 0.5 * sky, (a[3].free_flight_rays, sky)
-    assert a[3].primary_steps == b[3].primary_steps
-    # other step budgets (the gate table is rebuilt per budget), a camera looking down, one high above the terrain
-    for steps, o, dd in ((64, pos, d), (1000, pos, d), (300, (100.5, 120.25, 100.5), camera_dir(30.0, -50.0)),
-                         (300, (60.5, 90.5, 20.5), camera_dir(-120.0, 20.0))):
+    # other step budgets (the gate table is rebuilt per budget), cameras looking down / high above the terrain / along an
+    # axis (absDelta = inf), all yaw / pitch combinations of the parity cameras
+    cams = [(64, pos, d), (1000, pos, d), (1024, pos, d), (300, (100.5, 120.25, 100.5), camera_dir(30.0, -50.0)),
+            (300, (60.5, 90.5, 20.5), camera_dir(-120.0, 20.0)), (300, (35.0, 50.0, 35.0), (0.0, 1.0, 0.0)),
+            (300, (35.5, 80.5, 35.5), (1.0, 0.0, 0.0)), (300, (100.0, 75.0, 100.0), (0.0, 0.0, 1.0)),
+            (500, (120.5, 60.5, 90.5), camera_dir(200.0, 5.0))]
+    cams += [(300, c[0], camera_dir(c[1], c[2])) for c in CAMERAS]
+    for steps, o, dd in cams:
         got = []
-        for ff in (True, False):
-            caster.render_frame(rcmod.frame_params(640, 360, o, dd, sun, shadows=True, hits=True, max_steps=steps, free_flight=ff))
+        for kw in modes.values():
+            caster.render_frame(rcmod.frame_params(640, 360, o, dd, sun, shadows=True, hits=True, max_steps=steps, **kw))
             got.append((caster.read_image().copy(), caster.read_hits().copy()))
-        assert got[0][1].tobytes() == got[1][1].tobytes(), (steps, o)
-        assert np.array_equal(got[0][0], got[1][0])
+        for g in got[:2]:
+            assert g[1].tobytes() == got[2][1].tobytes(), (steps, o, dd)
+            assert np.array_equal(g[0], got[2][0])
 
 
 def test_cuda_frame_equals_the_reference_shader_frame(ob, rcmod, caster, ref_world, defaults):
