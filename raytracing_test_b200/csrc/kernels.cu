@@ -472,14 +472,14 @@ __device__ __forceinline__ F3 gen_sky(float dirX, float dirY, float dirZ, F3 sun
 // Free flight in closed form.  With nothing to test per step, the DDA is a merge of three independent sequences of event
 // times, t_a, fl(t_a + absDelta_a), fl(fl(t_a + absDelta_a) + absDelta_a), ...: it always fires the smallest, so its first
 // N steps are exactly the events earlier than some time T, whatever the tie order, and "every event before T has fired"
-// is a state the step-by-step loop passes through.  leap_axis fires those events for one axis without walking them:
-// inside one binade [2^e, 2^(e+1)) (ulp u) the rounded addition moves t by the same whole number of ulps every time,
-// c = RN(absDelta / u), as long as the exact sum stays below 2^(e+1) -- a half-way case (frac = 1/2) rounds to the even
-// mantissa, which is the same c every time once the mantissa is even, so an odd mantissa takes one real step first.  The
-// k additions up to min(T, 2^(e+1) - absDelta) are one multiply-add in fp64 (all values are multiples of 2^-24 below 2^12:
-// exact), the addition that crosses into the next binade is the real one.  Returns false outside that range (the caller
-// walks instead).  n += events fired.
-__device__ __forceinline__ bool leap_axis(float& t, const float a, const float T, int& n) {
+// is a state the step-by-step loop passes through.  leap_axis fires those events for one axis without walking them.
+// Inside one binade [2^e, 2^(e+1)) t = m * u (u = one ulp, m its 24-bit mantissa) and absDelta = q + r / 2^sh ulps; as
+// long as the exact sum stays below 2^(e+1) the rounded addition moves m by the same integer every time, c = q or q + 1
+// (round to nearest; a half-way case r = 2^(sh-1) goes to the even mantissa, which is the same c every time once m is
+// even -- an odd m takes one real step first).  So the k additions that keep m below min(T / u, 2^24 - q) are
+// m += k * c, in 32-bit integers; the addition that crosses into the next binade is the real one.  Returns false outside
+// the range this covers (the caller walks instead).  n += events fired.
+__device__ __forceinline__ bool leap_axis(float& t, const float a, const float T, uint32_t& n) {
     if (!(t < T)) return true;  // nothing fires (t = inf / NaN: an axis that never steps)
     if (!(a < 4096.0f)) {       // T < 2048: one event, the next one far beyond T (absDelta = inf included)
         t = FADD(t, a);
@@ -487,24 +487,34 @@ __device__ __forceinline__ bool leap_axis(float& t, const float a, const float T
         return true;
     }
     if (!(t >= 0.5f && a >= 0.5f)) return false;
+    const uint32_t abits = __float_as_uint(a);
+    const int ea = (int)(abits >> 23);
+    const uint32_t ma = (abits & 0x7FFFFFu) | 0x800000u;
     while (t < T) {
-        const int bits = __float_as_int(t);
-        const int e = (bits >> 23) - 127;  // t in [2^e, 2^(e+1)), u = 2^(e-23)
-        const double u = __longlong_as_double((long long)(e - 23 + 1023) << 52);
-        const double iu = __longlong_as_double((long long)(23 - e + 1023) << 52);
-        const double q = (double)a * iu;  // absDelta in ulps of t, exact
-        if ((bits & 1) && q - floor(q) == 0.5) {
-            t = FADD(t, a);
-            n++;
-            continue;
-        }
-        const double S = rint(q) * u;  // what one addition moves t by (>= 2^12 ulps: a >= 0.5, t < 2048)
-        const double X = (double)t;
-        const double B = fmin((double)T, u * 16777216.0 - (double)a);
-        if (B > X) {
-            const double k = ceil((B - X) / S);  // operands < 2^53 ulps apart and k <= 2^12: the quotient's rounding cannot reach the next integer
-            t = (float)(X + k * S);
-            n += (int)k;
+        const uint32_t bits = __float_as_uint(t);
+        const int e = (int)(bits >> 23);  // biased; 126 <= e <= 137
+        const int sh = e - ea;            // <= 11
+        if (sh >= 1) {                    // else absDelta >= 2^23 ulps: the sum leaves the binade at once
+            const uint32_t m = (bits & 0x7FFFFFu) | 0x800000u;
+            const uint32_t q = ma >> sh, r = ma & ((1u << sh) - 1u), half = 1u << (sh - 1);
+            const bool tie = r == half;
+            if (!(tie && (m & 1u))) {
+                const uint32_t c = q + ((r > half || (tie && (q & 1u))) ? 1u : 0u);  // >= 2^12
+                // T in ulps, rounded up (m * u < T <=> m < ceil(T / u)), at most the top of the binade
+                const float tm = fminf(ceilf(FMUL(T, __uint_as_float((uint32_t)(277 - e) << 23))), 16777216.0f);
+                const int bm = min((int)tm, (int)(0x1000000u - q));
+                if (bm > (int)m) {
+                    // k = ceil((bm - m) / c): the fp32 quotient (operands < 2^24: exact, k < 2^12) floors to k - 2 .. k
+                    uint32_t k = __float2uint_rd(__fdividef((float)(bm - (int)m), (float)c));
+                    uint32_t m1 = m + k * c;
+                    while ((int)m1 < bm) {
+                        m1 += c;
+                        k++;
+                    }
+                    t = FMUL((float)m1, __uint_as_float((uint32_t)(e - 23) << 23));  // m1 <= 2^24, u = 2^(e - 127 - 23): exact
+                    n += k;
+                }
+            }
         }
         if (t < T) {
             t = FADD(t, a);
@@ -514,16 +524,18 @@ __device__ __forceinline__ bool leap_axis(float& t, const float a, const float T
     return true;
 }
 
-// The three axes of one ray; a real call (once per sky ray) so that the fp64 temporaries do not count against the
-// registers of the loops around it.  t[] in / out; returns the events fired, or -1 (walk instead).
-__device__ __noinline__ int leap_axes(float* t, float ax, float ay, float az, float T) {
+// The three axes of one ray.  t[] in / out; returns the events fired, or -1 (walk instead).
+#ifndef RC_LEAP_INLINE
+#define RC_LEAP_INLINE __forceinline__
+#endif
+__device__ RC_LEAP_INLINE int leap_axes(float* t, float ax, float ay, float az, float T) {
     float lx = t[0], ly = t[1], lz = t[2];
-    int fired = 0;
+    uint32_t fired = 0;
     if (!(leap_axis(lx, ax, T, fired) && leap_axis(ly, ay, T, fired) && leap_axis(lz, az, T, fired))) return -1;
     t[0] = lx;
     t[1] = ly;
     t[2] = lz;
-    return fired;
+    return (int)fired;
 }
 
 struct PixelResult {
