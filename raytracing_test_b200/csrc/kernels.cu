@@ -648,13 +648,29 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         while (act) {
             if (rg.r.mask == 0ull) {
                 // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach
-                // (A.sky_gate) has nothing left to hit: the remaining steps only move it, and run after this loop without
-                // cells, countdowns or the tree.  gateDist > 0: that far above the gate; <= 0: 1 - gateDist steps up to go.
+                // (A.sky_gate: near blocks as they are, farther rings less what the ray must have climbed before it can be
+                // there) has nothing left to hit: the remaining steps only move it, and run after this loop without cells,
+                // countdowns or the tree.  gateDist > 0: clear by that much; <= 0: 1 - gateDist steps up to go.
                 int gateDist = -0x10000;
                 if (A.sky_gate && ray.sy > 0 && (uint32_t)pos.x <= W.wrap && (uint32_t)pos.z <= W.wrap) {
                     const uint32_t q = (ray.sx < 0 ? 1u : 0u) | (ray.sz < 0 ? 2u : 0u);
-                    gateDist = pos.y - (int)__ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)pos.z >> A.sky_shift)) * SKY_GRID +
-                                                             ((uint32_t)pos.x >> A.sky_shift)]);
+                    const uint4 g = __ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)pos.z >> A.sky_shift)) * SKY_GRID +
+                                                      ((uint32_t)pos.x >> A.sky_shift)]);
+                    // climbed per voxel of horizontal (Chebyshev) distance: at least min(absDelta.x, absDelta.z) /
+                    // absDelta.y steps up per step sideways, give or take 2 for the phases and 1 for the rounding of
+                    // the sums; a ring whose nearest block is d blocks away is at least (d - 1) * B voxels away
+                    // (a NaN deltaPos on y or z -- 0 * inf in buildRay -- makes z fire every time, whatever the times: no
+                    // climb to count on; fmaxf / fminf also turn a NaN product into 0)
+                    const bool merge = pos.ty == pos.ty && pos.tz == pos.tz;
+                    const float slope = merge ? fminf(fmaxf(FMUL(fminf(ray.adx, ray.adz), fabsf(ray.dy)), 0.0f), 16.0f) *
+                                                    (float)(1 << A.sky_shift)
+                                              : 0.0f;
+                    const int y1 = pos.y + 1;
+                    gateDist = y1 - (int)(g.x & 0xFFFFu);
+                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope) - 3, 0) - (int)(g.x >> 16));
+                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 3.0f) - 3, 0) - (int)(g.y & 0xFFFFu));
+                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 7.0f) - 3, 0) - (int)(g.y >> 16));
+                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 15.0f) - 3, 0) - (int)g.z);
                     if (gateDist > 0) {
                         freeFlight = true;
                         break;
@@ -1608,6 +1624,26 @@ __global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, 
     }
 }
 
+// Gate table for one step budget (FrameArgs::sky_gate): thread = (quadrant, block); rings of Chebyshev block distance
+// 0-1, 2-3, 4-7, 8-15, 16+ inside the window a ray can cross in maxSteps steps.
+__global__ void __launch_bounds__(128) sky_gate_kernel(const int* __restrict__ tops, int bs, uint32_t maxSteps, uint4* __restrict__ gates) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 4u * SKY_GRID * SKY_GRID) return;
+    const int bx = (int)(t % SKY_GRID), bz = (int)((t / SKY_GRID) % SKY_GRID), q = (int)(t / (SKY_GRID * SKY_GRID));
+    const int dx = (q & 1) ? -1 : 1, dz = (q & 2) ? -1 : 1;
+    const int nb = (int)(((1u << bs) - 1u + maxSteps) >> bs);  // blocks a ray can cross along one axis
+    uint32_t g[5] = {0u, 0u, 0u, 0u, 0u};
+    for (int j = 0; j <= nb; j++)
+        for (int i = 0; i <= nb; i++) {
+            const int d = max(i, j);
+            const int ring = d < 2 ? 0 : (d < 4 ? 1 : (d < 8 ? 2 : (d < 16 ? 3 : 4)));
+            const int x = bx + dx * i, z = bz + dz * j;
+            const uint32_t v = (x < 0 || x >= SKY_GRID || z < 0 || z >= SKY_GRID) ? 65535u : (uint32_t)(tops[z * SKY_GRID + x] + 1);
+            g[ring] = max(g[ring], v);
+        }
+    gates[t] = make_uint4(g[0] | (g[1] << 16), g[2] | (g[3] << 16), g[4], 0u);
+}
+
 __global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -1743,6 +1779,11 @@ cudaError_t launch_world_tops(const DeviceWorld& world, int skyShift, int* tops,
     cudaError_t e = cudaMemsetAsync(tops, 0xFF, SKY_GRID * SKY_GRID * sizeof(int), stream);  // -1: empty
     if (e != cudaSuccess) return e;
     world_tops_kernel<<<32, 128, 0, stream>>>(world, skyShift, tops);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sky_gates(const int* tops, int skyShift, uint32_t maxSteps, uint4* gates, cudaStream_t stream) {
+    sky_gate_kernel<<<4 * SKY_GRID * SKY_GRID / 128, 128, 0, stream>>>(tops, skyShift, maxSteps, gates);
     return cudaGetLastError();
 }
 

@@ -51,11 +51,15 @@ struct FrameArgs {
     uint32_t rank, world_size;
     float inv_width, inv_height;  // 1.0f / width, 1.0f / height (low_res.frag:264: 1.0 / resolution)
     // Free flight (primary loop A).  The world's columns are summarised in a SKY_GRID x SKY_GRID grid of column blocks
-    // (edge 2^sky_shift voxels); sky_gate[q][bz][bx] is the highest occupied y over every block a ray in block (bx, bz)
-    // can reach within max_steps steps when it heads the way of quadrant q = (step.x < 0) | (step.z < 0) << 1, or 32767
-    // when that window runs off the grid (torus wrap).  A ray that steps UP and is above its gate has nothing but empty
-    // space ahead.  Null: no gating (camera y + max_steps leaves the torus, max_steps too large, tree too shallow).
-    const short* sky_gate;
+    // (edge B = 2^sky_shift voxels).  sky_gate[q][bz][bx] holds, for a ray in block (bx, bz) heading the way of quadrant
+    // q = (step.x < 0) | (step.z < 0) << 1, five gates: 1 + the highest occupied y over the blocks at Chebyshev distance
+    // 0-1, 2-3, 4-7, 8-15 and 16+ blocks in that quadrant, as far as max_steps steps can reach (u16 x 8, one 128-bit load;
+    // 0 = nothing there, 65535 = the ring runs off the grid: torus wrap, never free).  A ray that steps UP is above
+    // everything it can still reach when its y clears the near gate and, for each farther ring, its y plus what it
+    // must have climbed before it can get there (slope x distance, rounded down, less 3) clears that ring's gate: then
+    // nothing but empty space lies ahead.  Null: no gating (camera y + max_steps leaves the torus, max_steps > 1024,
+    // tree too shallow).
+    const uint4* sky_gate;
     int sky_shift;
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
@@ -89,6 +93,8 @@ cudaError_t launch_pick(const DeviceWorld& world, const float* cam_pos3, const f
 // block edge = 2^sky_shift voxels.  One depth-first walk per 64^3 subtree.
 constexpr int SKY_GRID = 64;
 cudaError_t launch_world_tops(const DeviceWorld& world, int sky_shift, int* tops, cudaStream_t stream);
+// tops -> the gate table of FrameArgs::sky_gate for a step budget (4 * SKY_GRID * SKY_GRID entries of 16 bytes).
+cudaError_t launch_sky_gates(const int* tops, int sky_shift, uint32_t max_steps, uint4* gates, cudaStream_t stream);
 
 // Single-voxel lookups through the same device code path the kernels use (tests).
 cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,

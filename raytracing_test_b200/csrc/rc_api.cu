@@ -71,9 +71,7 @@ struct Context {
     FrameCounters* dCounters = nullptr;
     // sky gates (kernels.h, FrameArgs::sky_gate): column-block tops of the current world, the gate table built from them
     int* dSkyTops = nullptr;
-    short* dSkyGate = nullptr;
-    std::vector<int> skyTops;
-    std::vector<short> skyGate;
+    uint4* dSkyGate = nullptr;
     int skyShift = 0;
     uint32_t skyGateSteps = 0xFFFFFFFFu;  // max_steps the table on the device was built for (none)
     FrameCounters* hCounters = nullptr;  // pinned
@@ -343,50 +341,22 @@ static int ensureHostCopy() {
     return RC_OK;
 }
 
-// Column-block tops of the packed tree as it stands on the device (after every upload, update, load or generation).
+// Column-block tops of the packed tree as it stands on the device (after every upload, update, load or generation);
+// stream-ordered, nothing comes back to the host.
 static int refreshSky() {
     g.skyGateSteps = 0xFFFFFFFFu;
     g.skyShift = (int)g.world.root_shift + 2 - 6;  // torus edge / SKY_GRID
-    g.skyTops.assign((size_t)SKY_GRID * SKY_GRID, -1);
     if (g.skyShift < 2) return RC_OK;  // a brick would straddle blocks: no gating for such a shallow tree
-    if (!g.dSkyTops) CUDA_TRY(cudaMalloc((void**)&g.dSkyTops, g.skyTops.size() * sizeof(int)));
+    if (!g.dSkyTops) CUDA_TRY(cudaMalloc((void**)&g.dSkyTops, (size_t)SKY_GRID * SKY_GRID * sizeof(int)));
     CUDA_TRY(launch_world_tops(g.world, g.skyShift, g.dSkyTops, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(g.skyTops.data(), g.dSkyTops, g.skyTops.size() * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaStreamSynchronize(g.stream));
     return RC_OK;
 }
 
-// Gate table for a step budget: per quadrant of horizontal headings, the highest top over the blocks within reach.
+// Gate table for a step budget, built on the device from the tops.
 static int ensureSkyGate(uint32_t maxSteps) {
     if (g.skyGateSteps == maxSteps) return RC_OK;
-    const int G = SKY_GRID, OFF = 32767;
-    const int nb = (int)(((1u << g.skyShift) - 1u + maxSteps) >> g.skyShift);  // blocks a ray can cross along one axis
-    g.skyGate.assign((size_t)4 * G * G, (short)OFF);
-    std::vector<int> row((size_t)G * G);
-    for (int q = 0; q < 4; q++) {
-        const int dx = (q & 1) ? -1 : 1, dz = (q & 2) ? -1 : 1;
-        for (int bz = 0; bz < G; bz++)
-            for (int bx = 0; bx < G; bx++) {
-                int m = -1;
-                const int last = bx + dx * nb;
-                if (last < 0 || last >= G) m = OFF;  // the window runs off the grid: the ray may wrap around the torus
-                else
-                    for (int k = 0; k <= nb; k++) m = std::max(m, g.skyTops[(size_t)bz * G + bx + dx * k]);
-                row[(size_t)bz * G + bx] = m;
-            }
-        for (int bz = 0; bz < G; bz++)
-            for (int bx = 0; bx < G; bx++) {
-                int m = -1;
-                const int last = bz + dz * nb;
-                if (last < 0 || last >= G) m = OFF;
-                else
-                    for (int k = 0; k <= nb; k++) m = std::max(m, row[(size_t)(bz + dz * k) * G + bx]);
-                g.skyGate[((size_t)q * G + bz) * G + bx] = (short)std::min(m, OFF);
-            }
-    }
-    if (!g.dSkyGate) CUDA_TRY(cudaMalloc((void**)&g.dSkyGate, g.skyGate.size() * sizeof(short)));
-    CUDA_TRY(cudaMemcpyAsync(g.dSkyGate, g.skyGate.data(), g.skyGate.size() * sizeof(short), cudaMemcpyHostToDevice, g.stream));
-    CUDA_TRY(cudaStreamSynchronize(g.stream));  // pageable source
+    if (!g.dSkyGate) CUDA_TRY(cudaMalloc((void**)&g.dSkyGate, (size_t)4 * SKY_GRID * SKY_GRID * sizeof(uint4)));
+    CUDA_TRY(launch_sky_gates(g.dSkyTops, g.skyShift, maxSteps, g.dSkyGate, g.stream));
     g.skyGateSteps = maxSteps;
     return RC_OK;
 }
