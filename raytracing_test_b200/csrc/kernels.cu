@@ -1553,46 +1553,73 @@ __global__ void pick_kernel(DeviceWorld W, PickArgs a, int* out) {
 }
 
 // Highest occupied y per column block (edge 2^bs voxels, SKY_GRID x SKY_GRID blocks over the torus), the input of the
-// sky gates (FrameArgs::sky_gate).  Thread (i, j) walks the subtree under child j of the root's child i depth-first with
-// an explicit stack; a uniform cell counts for every block it covers, a brick for the block it lies in (bs >= 2) with
-// its highest occupied layer.  Only nodes reachable from the root are seen, so runs abandoned by rc_update_world do
-// not count.
+// sky gates (FrameArgs::sky_gate).  Thread (i, j, k) follows child i of the root, child j of that, child k of that (most
+// threads find a clear mask bit on the way and leave) and walks the subtree below -- a 16^3 cell at max_depth 6 --
+// depth-first with an explicit stack; a uniform cell counts for every block it covers, a brick for the block it lies in
+// (bs >= 2) with its highest occupied layer.  A uniform cell or brick met on the way down belongs to the thread whose
+// remaining digits are 0.  Only nodes reachable from the root are seen, so runs abandoned by rc_update_world do not count.
 struct TopsFrame {
     unsigned long long mask, todo;
     uint32_t base, kind;
     int ox, oy, oz;
 };
 constexpr int TOPS_MAX_LEVELS = 12;
+constexpr int TOPS_PREFIX = 3;  // levels resolved by the thread index: 64^3 threads
 __device__ __forceinline__ void tops_add_cell(int* tops, int bs, int x0, int z0, int edge, int top) {
     const int bx0 = x0 >> bs, bx1 = (x0 + edge - 1) >> bs, bz0 = z0 >> bs, bz1 = (z0 + edge - 1) >> bs;
     for (int bz = bz0; bz <= bz1; bz++)
         for (int bx = bx0; bx <= bx1; bx++) atomicMax(&tops[(bz & (SKY_GRID - 1)) * SKY_GRID + (bx & (SKY_GRID - 1))], top);
 }
+__device__ __forceinline__ void tops_add_brick(int* tops, int bs, unsigned long long mask, int ox, int oy, int oz) {
+    if (mask == 0ull) return;
+    int ymax = 0;
+    for (int k = 1; k < 4; k++)
+        if (mask & (0x000F000F000F000Full << (4 * k))) ymax = k;
+    tops_add_cell(tops, bs, ox, oz, 4, oy + ymax);
+}
 __global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, int* tops) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;  // 4096 threads
-    const int ti = (int)(t >> 6), tj = (int)(t & 63u);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;  // 64^3 threads
     TopsFrame st[TOPS_MAX_LEVELS];
-    int sp = 0;
     {
         const uint4 n = __ldg(&W.nodes[0]);
         st[0].mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
         st[0].base = n.z;
         st[0].kind = n.w;
         st[0].ox = st[0].oy = st[0].oz = 0;
-        // this thread's share: child ti of the root and, one level down, child tj of that
-        st[0].todo = st[0].mask & (1ull << ti);
     }
+    // the way down: digit l of the thread index picks the child at level l
+    for (int l = 0; l < TOPS_PREFIX; l++) {
+        TopsFrame& f = st[0];
+        const int shift = W.root_shift - 2 * l;  // log2 of the edge of this node's child cells
+        const uint32_t rest = l == 0 ? t : (t & ((1u << (6 * (TOPS_PREFIX - l))) - 1u));  // this digit and the ones below
+        if ((f.kind & PK_KIND_MASK) == PK_BRICK || shift <= 0) {
+            if (rest == 0u) tops_add_brick(tops, bs, f.mask, f.ox, f.oy, f.oz);
+            return;
+        }
+        const int idx = (int)(rest >> (6 * (TOPS_PREFIX - 1 - l)));
+        if (!((f.mask >> idx) & 1ull)) return;
+        const int cx = f.ox + ((idx & 3) << shift), cy = f.oy + (((idx >> 2) & 3) << shift), cz = f.oz + ((idx >> 4) << shift);
+        const uint4 n = __ldg(&W.nodes[f.base + (uint32_t)__popcll(f.mask & ((1ull << idx) - 1ull))]);
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+            if ((rest & ((1u << (6 * (TOPS_PREFIX - 1 - l))) - 1u)) == 0u)
+                tops_add_cell(tops, bs, cx, cz, 1 << shift, cy + (1 << shift) - 1);
+            return;
+        }
+        f.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        f.base = n.z;
+        f.kind = n.w;
+        f.ox = cx;
+        f.oy = cy;
+        f.oz = cz;
+    }
+    // the subtree below, depth-first
+    st[0].todo = st[0].mask;
+    int sp = 0;
     while (sp >= 0) {
         TopsFrame& f = st[sp];
-        const int shift = W.root_shift - 2 * sp;  // log2 of the edge of this node's child cells
+        const int shift = W.root_shift - 2 * (sp + TOPS_PREFIX);
         if ((f.kind & PK_KIND_MASK) == PK_BRICK || shift <= 0) {
-            // a brick (the root itself: thread 0 alone counts it)
-            if ((sp > 0 || t == 0u) && f.mask != 0ull) {
-                int ymax = 0;
-                for (int k = 1; k < 4; k++)
-                    if (f.mask & (0x000F000F000F000Full << (4 * k))) ymax = k;
-                tops_add_cell(tops, bs, f.ox, f.oz, 4, f.oy + ymax);
-            }
+            tops_add_brick(tops, bs, f.mask, f.ox, f.oy, f.oz);
             sp--;
             continue;
         }
@@ -1603,14 +1630,11 @@ __global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, 
         const int idx = __ffsll((long long)f.todo) - 1;
         f.todo &= f.todo - 1ull;
         const int cx = f.ox + ((idx & 3) << shift), cy = f.oy + (((idx >> 2) & 3) << shift), cz = f.oz + ((idx >> 4) << shift);
-        const uint32_t rank = (uint32_t)__popcll(f.mask & ((1ull << idx) - 1ull));
-        const uint4 n = __ldg(&W.nodes[f.base + rank]);
-        const uint32_t kind = n.w & PK_KIND_MASK;
-        if (kind == PK_LEAF) {
-            if (sp >= 1 || tj == 0) tops_add_cell(tops, bs, cx, cz, 1 << shift, cy + (1 << shift) - 1);
+        const uint4 n = __ldg(&W.nodes[f.base + (uint32_t)__popcll(f.mask & ((1ull << idx) - 1ull))]);
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+            tops_add_cell(tops, bs, cx, cz, 1 << shift, cy + (1 << shift) - 1);
             continue;
         }
-        if (sp == 0 && kind == PK_BRICK && tj != 0) continue;  // a brick right under the root: thread (ti, 0) counts it
         if (sp + 1 >= TOPS_MAX_LEVELS) continue;
         TopsFrame& c = st[sp + 1];
         c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
@@ -1619,7 +1643,7 @@ __global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, 
         c.ox = cx;
         c.oy = cy;
         c.oz = cz;
-        c.todo = (sp == 0 && kind != PK_BRICK) ? (c.mask & (1ull << tj)) : c.mask;
+        c.todo = c.mask;
         sp++;
     }
 }
@@ -1778,7 +1802,7 @@ cudaError_t launch_pick(const DeviceWorld& world, const float* p, const float* d
 cudaError_t launch_world_tops(const DeviceWorld& world, int skyShift, int* tops, cudaStream_t stream) {
     cudaError_t e = cudaMemsetAsync(tops, 0xFF, SKY_GRID * SKY_GRID * sizeof(int), stream);  // -1: empty
     if (e != cudaSuccess) return e;
-    world_tops_kernel<<<32, 128, 0, stream>>>(world, skyShift, tops);
+    world_tops_kernel<<<64 * 64 * 64 / 128, 128, 0, stream>>>(world, skyShift, tops);
     return cudaGetLastError();
 }
 
