@@ -26,6 +26,7 @@
 // their lookups hit the same L1 lines).
 #include "kernels.h"
 
+#include "free_flight.h"
 #include "packed_world.h"
 
 namespace rc {
@@ -469,75 +470,6 @@ __device__ __forceinline__ F3 gen_sky(float dirX, float dirY, float dirZ, F3 sun
     return out;
 }
 
-// Free flight in closed form.  With nothing to test per step, the DDA is a merge of three independent sequences of event
-// times, t_a, fl(t_a + absDelta_a), fl(fl(t_a + absDelta_a) + absDelta_a), ...: it always fires the smallest, so its first
-// N steps are exactly the events earlier than some time T, whatever the tie order, and "every event before T has fired"
-// is a state the step-by-step loop passes through.  leap_axis fires those events for one axis without walking them.
-// Inside one binade [2^e, 2^(e+1)) t = m * u (u = one ulp, m its 24-bit mantissa) and absDelta = q + r / 2^sh ulps; as
-// long as the exact sum stays below 2^(e+1) the rounded addition moves m by the same integer every time, c = q or q + 1
-// (round to nearest; a half-way case r = 2^(sh-1) goes to the even mantissa, which is the same c every time once m is
-// even -- an odd m takes one real step first).  So the k additions that keep m below min(T / u, 2^24 - q) are
-// m += k * c, in 32-bit integers; the addition that crosses into the next binade is the real one.  Returns false outside
-// the range this covers (the caller walks instead).  n += events fired.
-__device__ __forceinline__ bool leap_axis(float& t, const float a, const float T, uint32_t& n) {
-    if (!(t < T)) return true;  // nothing fires (t = inf / NaN: an axis that never steps)
-    if (!(a < 4096.0f)) {       // T < 2048: one event, the next one far beyond T (absDelta = inf included)
-        t = FADD(t, a);
-        n++;
-        return true;
-    }
-    if (!(t >= 0.5f && a >= 0.5f)) return false;
-    const uint32_t abits = __float_as_uint(a);
-    const int ea = (int)(abits >> 23);
-    const uint32_t ma = (abits & 0x7FFFFFu) | 0x800000u;
-    while (t < T) {
-        const uint32_t bits = __float_as_uint(t);
-        const int e = (int)(bits >> 23);  // biased; 126 <= e <= 137
-        const int sh = e - ea;            // <= 11
-        if (sh >= 1) {                    // else absDelta >= 2^23 ulps: the sum leaves the binade at once
-            const uint32_t m = (bits & 0x7FFFFFu) | 0x800000u;
-            const uint32_t q = ma >> sh, r = ma & ((1u << sh) - 1u), half = 1u << (sh - 1);
-            const bool tie = r == half;
-            if (!(tie && (m & 1u))) {
-                const uint32_t c = q + ((r > half || (tie && (q & 1u))) ? 1u : 0u);  // >= 2^12
-                // T in ulps, rounded up (m * u < T <=> m < ceil(T / u)), at most the top of the binade
-                const float tm = fminf(ceilf(FMUL(T, __uint_as_float((uint32_t)(277 - e) << 23))), 16777216.0f);
-                const int bm = min((int)tm, (int)(0x1000000u - q));
-                if (bm > (int)m) {
-                    // k = ceil((bm - m) / c): the fp32 quotient (operands < 2^24: exact, k < 2^12) floors to k - 2 .. k
-                    uint32_t k = __float2uint_rd(__fdividef((float)(bm - (int)m), (float)c));
-                    uint32_t m1 = m + k * c;
-                    while ((int)m1 < bm) {
-                        m1 += c;
-                        k++;
-                    }
-                    t = FMUL((float)m1, __uint_as_float((uint32_t)(e - 23) << 23));  // m1 <= 2^24, u = 2^(e - 127 - 23): exact
-                    n += k;
-                }
-            }
-        }
-        if (t < T) {
-            t = FADD(t, a);
-            n++;
-        }
-    }
-    return true;
-}
-
-// The three axes of one ray.  t[] in / out; returns the events fired, or -1 (walk instead).
-#ifndef RC_LEAP_INLINE
-#define RC_LEAP_INLINE __forceinline__
-#endif
-__device__ RC_LEAP_INLINE int leap_axes(float* t, float ax, float ay, float az, float T) {
-    float lx = t[0], ly = t[1], lz = t[2];
-    uint32_t fired = 0;
-    if (!(leap_axis(lx, ax, T, fired) && leap_axis(ly, ay, T, fired) && leap_axis(lz, az, T, fired))) return -1;
-    t[0] = lx;
-    t[1] = ly;
-    t[2] = lz;
-    return (int)fired;
-}
-
 struct PixelResult {
     F3 color;
     rc_hit hit;
@@ -755,51 +687,13 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 const unsigned m = __activemask();
                 if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&A.counters->free_flight_rays, (unsigned)__popc(m));
             }
-            float tx = pos.tx, ty = pos.ty, tz = pos.tz;
-            const uint32_t total = numSteps - steps;  // >= 1
-            uint32_t left = total;
-            if (left >= 24u && !(P.flags & RC_F_NO_LEAP)) {
-                // T = a time by which at most left - 4 events have fired: an axis fires at most (T - T0) / absDelta * (1 + 2^-13)
-                // + 1 events from T0 on (its additions are off by at most half an ulp of t < 2048 each), and the three
-                // 1 / absDelta add up to |dir.x| + |dir.y| + |dir.z|
-                const float T0 = fminf(fminf(tx, ty), tz);
-                const float rate = (fabsf(ray.dx) + fabsf(ray.dy)) + fabsf(ray.dz);
-                const float T = T0 + (float)(left - 7u) / rate;
-                // a NaN deltaPos (0 * inf in buildRay) on y or z makes the else-branch axis fire every time: not a merge
-                if (rate >= 0.5f && T < 2048.0f && ty == ty && tz == tz) {
-                    float t3[3] = {tx, ty, tz};
-                    const int fired = leap_axes(t3, ray.adx, ray.ady, ray.adz, T);
-                    if (fired >= 0 && (uint32_t)fired < left) {
-                        tx = t3[0];
-                        ty = t3[1];
-                        tz = t3[2];
-                        left -= (uint32_t)fired;
-                    }
-                }
-            }
-#pragma unroll 4
-            for (uint32_t k = 0; k < left; k++) {
-                ax.x = tx < ty && tx < tz;
-                ax.y = !ax.x && ty < tz;
-                const bool az = !ax.x && !ax.y;
-                if (ax.x) tx = FADD(tx, ray.adx);
-                if (ax.y) ty = FADD(ty, ray.ady);
-                if (az) tz = FADD(tz, ray.adz);
-            }
-            // Steps per axis from the growth of deltaPos: n rounded additions of absDelta moved it by n * absDelta give or
-            // take n half-ulps of its final value -- with deltaPos <= 1.74 * max_steps + absDelta, absDelta >= 1 and
-            // max_steps <= 1024 (ff_enable) at most 0.11 * absDelta, so the quotient rounds to n.  An axis that never steps (absDelta = inf, deltaPos
-            // inf or NaN) has a difference of 0 or NaN.
-            const float gx = FSUB(tx, pos.tx), gy = FSUB(ty, pos.ty);
-            const int nx = gx > 0.0f ? (int)rintf(FDIV(gx, ray.adx)) : 0;
-            const int ny = gy > 0.0f ? (int)rintf(FDIV(gy, ray.ady)) : 0;
-            const int nz = (int)total - nx - ny;
+            // free_flight.h: most of the remaining steps in closed form, the last few walked; the voxel the ray ends in
+            int nx, ny, nz;
+            free_flight(pos.tx, pos.ty, pos.tz, ray.adx, ray.ady, ray.adz, ray.dx, ray.dy, ray.dz, numSteps - steps,
+                        !(P.flags & RC_F_NO_LEAP), nx, ny, nz, ax.x, ax.y);
             pos.x += ray.sx * nx;
             pos.y += ray.sy * ny;
             pos.z += ray.sz * nz;
-            pos.tx = tx;
-            pos.ty = ty;
-            pos.tz = tz;
             steps = numSteps;
         }
         if (!live) return;
@@ -1041,13 +935,17 @@ __device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, ui
 
 // grid.x = ceil(width/16), grid.y = local_rows/8 ; block = 128 threads = 4 warps,
 // each warp an 8x4 pixel tile, the block a 16x8 tile.
-#ifndef RC_PRIMARY_MIN_BLOCKS
-#define RC_PRIMARY_MIN_BLOCKS 8  // 64 registers: 8 CTAs of 128 threads per SM
+#ifndef RC_PRIMARY_WARPS
+#define RC_PRIMARY_WARPS 4  // warps per CTA: 4 = a 16x8 pixel tile, 2 = 16x4, 1 = 8x4
 #endif
-__global__ void __launch_bounds__(128, RC_PRIMARY_MIN_BLOCKS) primary_kernel(const __grid_constant__ FrameArgs A) {
+#ifndef RC_PRIMARY_MIN_BLOCKS
+#define RC_PRIMARY_MIN_BLOCKS (32 / RC_PRIMARY_WARPS)  // 64 registers: 32 warps per SM
+#endif
+constexpr uint32_t PRIMARY_TILE_W = RC_PRIMARY_WARPS >= 2 ? 16u : 8u, PRIMARY_TILE_H = RC_PRIMARY_WARPS >= 4 ? 8u : 4u;
+__global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) primary_kernel(const __grid_constant__ FrameArgs A) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t localRow = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    const uint32_t px = blockIdx.x * PRIMARY_TILE_W + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t localRow = blockIdx.y * PRIMARY_TILE_H + (warp >> 1) * 4u + (lane >> 3);
     // local band -> global row
     const uint32_t band = (localRow / BAND_ROWS) * A.world_size + A.rank;
     const uint32_t py = band * BAND_ROWS + (localRow % BAND_ROWS);
@@ -1756,9 +1654,9 @@ void release_hemisphere() {
 }
 
 cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
-    dim3 grid((args.p.width + 15u) / 16u, (args.local_rows + 7u) / 8u);
+    dim3 grid((args.p.width + PRIMARY_TILE_W - 1u) / PRIMARY_TILE_W, (args.local_rows + PRIMARY_TILE_H - 1u) / PRIMARY_TILE_H);
     if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-    primary_kernel<<<grid, 128, 0, stream>>>(args);
+    primary_kernel<<<grid, 32 * RC_PRIMARY_WARPS, 0, stream>>>(args);
     return cudaGetLastError();
 }
 
