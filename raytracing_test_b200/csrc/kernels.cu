@@ -470,6 +470,28 @@ __device__ __forceinline__ F3 gen_sky(float dirX, float dirY, float dirZ, F3 sun
     return out;
 }
 
+// Sky gates (FrameArgs::sky_gate).  A ray at voxel (x, y, z) that steps UP, heading (sxNeg, szNeg) horizontally, is above
+// every occupied voxel of the columns it can still reach when the value returned is > 0 (clear by that much; <= 0: that
+// many steps up, plus one, to go): near blocks as they are, each farther ring less what the ray must have climbed before
+// it can be there.  Climbed per voxel of horizontal (Chebyshev) distance: at least min(absDelta.x, absDelta.z) /
+// absDelta.y steps up per step sideways (events fire in time order), give or take 2 for the phases and 1 for the
+// rounding of the sums; a ring whose nearest block is d blocks away is at least (d - 1) * B voxels away.  merge = false
+// (a NaN deltaPos on y or z -- 0 * inf in buildRay -- makes z fire every time, whatever the times): no climb to count on;
+// fmaxf / fminf also turn a NaN product into 0.  The caller makes sure x and z are on the torus and y + the steps left is.
+__device__ __forceinline__ int sky_gate_distance(const FrameArgs& A, int x, int y, int z, bool sxNeg, bool szNeg, float adx, float adz,
+                                                 float dy, bool merge) {
+    const uint32_t q = (sxNeg ? 1u : 0u) | (szNeg ? 2u : 0u);
+    const uint4 g = __ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)z >> A.sky_shift)) * SKY_GRID + ((uint32_t)x >> A.sky_shift)]);
+    const float slope = merge ? fminf(fmaxf(FMUL(fminf(adx, adz), fabsf(dy)), 0.0f), 16.0f) * (float)(1 << A.sky_shift) : 0.0f;
+    const int y1 = y + 1;
+    int d = y1 - (int)(g.x & 0xFFFFu);
+    d = min(d, y1 + max(__float2int_rd(slope) - 3, 0) - (int)(g.x >> 16));
+    d = min(d, y1 + max(__float2int_rd(slope * 3.0f) - 3, 0) - (int)(g.y & 0xFFFFu));
+    d = min(d, y1 + max(__float2int_rd(slope * 7.0f) - 3, 0) - (int)(g.y >> 16));
+    d = min(d, y1 + max(__float2int_rd(slope * 15.0f) - 3, 0) - (int)g.z);
+    return d;
+}
+
 struct PixelResult {
     F3 color;
     rc_hit hit;
@@ -579,30 +601,13 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         bool freeFlight = false;
         while (act) {
             if (rg.r.mask == 0ull) {
-                // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach
-                // (A.sky_gate: near blocks as they are, farther rings less what the ray must have climbed before it can be
-                // there) has nothing left to hit: the remaining steps only move it, and run after this loop without cells,
-                // countdowns or the tree.  gateDist > 0: clear by that much; <= 0: 1 - gateDist steps up to go.
+                // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach has
+                // nothing left to hit: the remaining steps only move it, and run after this loop without cells, countdowns
+                // or the tree.
                 int gateDist = -0x10000;
                 if (A.sky_gate && ray.sy > 0 && (uint32_t)pos.x <= W.wrap && (uint32_t)pos.z <= W.wrap) {
-                    const uint32_t q = (ray.sx < 0 ? 1u : 0u) | (ray.sz < 0 ? 2u : 0u);
-                    const uint4 g = __ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)pos.z >> A.sky_shift)) * SKY_GRID +
-                                                      ((uint32_t)pos.x >> A.sky_shift)]);
-                    // climbed per voxel of horizontal (Chebyshev) distance: at least min(absDelta.x, absDelta.z) /
-                    // absDelta.y steps up per step sideways, give or take 2 for the phases and 1 for the rounding of
-                    // the sums; a ring whose nearest block is d blocks away is at least (d - 1) * B voxels away
-                    // (a NaN deltaPos on y or z -- 0 * inf in buildRay -- makes z fire every time, whatever the times: no
-                    // climb to count on; fmaxf / fminf also turn a NaN product into 0)
-                    const bool merge = pos.ty == pos.ty && pos.tz == pos.tz;
-                    const float slope = merge ? fminf(fmaxf(FMUL(fminf(ray.adx, ray.adz), fabsf(ray.dy)), 0.0f), 16.0f) *
-                                                    (float)(1 << A.sky_shift)
-                                              : 0.0f;
-                    const int y1 = pos.y + 1;
-                    gateDist = y1 - (int)(g.x & 0xFFFFu);
-                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope) - 3, 0) - (int)(g.x >> 16));
-                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 3.0f) - 3, 0) - (int)(g.y & 0xFFFFu));
-                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 7.0f) - 3, 0) - (int)(g.y >> 16));
-                    gateDist = min(gateDist, y1 + max(__float2int_rd(slope * 15.0f) - 3, 0) - (int)g.z);
+                    gateDist = sky_gate_distance(A, pos.x, pos.y, pos.z, ray.sx < 0, ray.sz < 0, ray.adx, ray.adz, ray.dy,
+                                                 pos.ty == pos.ty && pos.tz == pos.tz);
                     if (gateDist > 0) {
                         freeFlight = true;
                         break;
@@ -899,11 +904,21 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         uint32_t state = 0u;  // block = (-1,-1): "empty"; 1 = LIQUID (the ray goes on), 2 = opaque
         uint32_t ssteps = 0;
         enter_region(W, cur, rg, sp);
+        // the sun is up: a shadow ray that has risen above everything it can still reach (sky gates, as in loop A) stays
+        // unoccluded and runs out of steps -- asked when it enters an empty region and every 8th step inside one
+        const bool gated = A.shadow_gate && sr.sy > 0 && sp.ty == sp.ty && sp.tz == sp.tz;
         while (state != 2u && k-- != 0u) {
             dda_step_bl(sr, sp);
             ssteps++;
-            if (left_region(rg, sp)) enter_region(W, cur, rg, sp);
+            const bool left = left_region(rg, sp);
+            if (left) enter_region(W, cur, rg, sp);
             state = occlusion_state(W, rg.r, sp.x, sp.y, sp.z);
+            if (gated && rg.r.mask == 0ull && (left || (k & 7u) == 0u) && (uint32_t)sp.x <= W.wrap && (uint32_t)sp.z <= W.wrap &&
+                (uint32_t)sp.y + k <= W.wrap &&
+                sky_gate_distance(A, sp.x, sp.y, sp.z, sr.sx < 0, sr.sz < 0, sr.adx, sr.adz, sr.dy, true) > 0) {
+                ssteps += k;  // the steps it would still take, all empty
+                break;
+            }
         }
         const uint32_t sw = state;
         out.hit.shadow_steps = (uint16_t)ssteps;
@@ -957,12 +972,19 @@ __global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) 
     R.aoSeed = false;
     R.hit.kind = RC_KIND_SKY;
     R.hit.steps = 0;
+#ifdef RC_COST_MAP
+    const long long costT0 = clock64();
+#endif
     shade_pixel(A, active, px, py, R);
     if (active) {
         const uint32_t idx = local_index(A, px, localRow);
         // AO pixels get their final colour from the AO kernel
         if (!(R.aoSeed)) store_pixel(A, idx, frame_pixel_of(A, px, localRow), R.color);
         if (A.hits) A.hits[idx] = R.hit;
+#ifdef RC_COST_MAP
+        // developer probe (tools/cost_map.py): cycles this warp spent in shade_pixel, in the alpha channel of the float frame
+        if (A.rgba32f) A.rgba32f[idx].w = (float)(clock64() - costT0);
+#endif
     }
 
     // AO seeds: warp-aggregated append

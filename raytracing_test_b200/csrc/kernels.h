@@ -61,6 +61,7 @@ struct FrameArgs {
     // tree too shallow).
     const uint4* sky_gate;
     int sky_shift;
+    uint32_t shadow_gate;    // the table also covers the shadow rays' reach (shadow_steps <= max_steps, flags allow it)
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
     uchar4* rgba8;           // [local_rows][width]

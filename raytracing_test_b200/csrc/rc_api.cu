@@ -667,6 +667,7 @@ int rc_render_frame(const rc_frame_params* params) {
             if ((rcode = ensureSkyGate(p.max_steps)) != RC_OK) return rcode;
             a.sky_gate = g.dSkyGate;
             a.sky_shift = g.skyShift;
+            a.shadow_gate = p.shadow_steps <= p.max_steps ? 1u : 0u;
         }
     }
     a.local_rows = localRows;
