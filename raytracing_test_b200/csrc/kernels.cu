@@ -499,7 +499,15 @@ struct PixelResult {
     bool shadowRay;
     bool aoSeed;
     float sx_, sy_, sz_;  // un-biased exact at the hit (AO seed)
+#ifdef RC_COST_MAP
+    long long mark[3];    // developer probe: clock64 after loop A / after the replay / before the shadow ray (0: not reached)
+#endif
 };
+#ifdef RC_COST_MAP
+#define RC_MARK(i) out.mark[i] = clock64()
+#else
+#define RC_MARK(i)
+#endif
 
 // One pixel of low_res.frag main() (:256-393).
 // Called by ALL 32 lanes of a warp (valid = the lane has a pixel): the primary loop agrees on its
@@ -676,9 +684,16 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 if (outOfSteps) break;
                 enter_region(W, cur, rg, pos);
             } else {
-                ax = dda_step_bl(ray, pos);
-                steps++;
-                if (left_region(rg, pos)) enter_region(W, cur, rg, pos);
+                // Brick (or uniform solid cell): step until the ray leaves it, enters an occupied voxel or runs out of
+                // steps -- all inside this one pass of the outer loop, so that a lane walking a brick does not make the
+                // rest of the warp (empty-cell lanes wait through every pass) pay a pass per step.
+                bool leftBrick;
+                do {
+                    ax = dda_step_bl(ray, pos);
+                    steps++;
+                    leftBrick = left_region(rg, pos);
+                } while (!leftBrick && !((rg.r.mask >> brick_bit(pos.x, pos.y, pos.z)) & 1ull) && steps < numSteps);
+                if (leftBrick) enter_region(W, cur, rg, pos);
             }
             if (rg.r.mask != 0ull) {
                 const int idx = brick_bit(pos.x, pos.y, pos.z);
@@ -706,6 +721,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         i = word != 0u ? steps : numSteps + 1u;
         if (steps) face = axis_index(ax);
     }
+    RC_MARK(0);
     if (word != 0u || P.render_pos_data == 1) {
         // ratios columns (low_res.frag:75-91) for pos.exact, now that the ray is known to need it
         ray.r0y = FDIV(ray.dy, ray.dx);
@@ -732,6 +748,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     }
     cnt.nx = cnt.ny = cnt.nz = 1;
     cellShift = 0;
+    RC_MARK(1);
     // :317-333  loop B
     while (i++ < numSteps) {
         if (word != 0u) {
@@ -884,6 +901,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     }
     if (!done) out.hit.flags |= RC_HF_FACING_SUN;
 
+    RC_MARK(2);
     // :373-391 shadow ray
     if (!done && (P.flags & RC_F_SHADOWS)) {
         out.shadowRay = true;
@@ -974,6 +992,7 @@ __global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) 
     R.hit.steps = 0;
 #ifdef RC_COST_MAP
     const long long costT0 = clock64();
+    R.mark[0] = R.mark[1] = R.mark[2] = 0;
 #endif
     shade_pixel(A, active, px, py, R);
     if (active) {
@@ -983,7 +1002,12 @@ __global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) 
         if (A.hits) A.hits[idx] = R.hit;
 #ifdef RC_COST_MAP
         // developer probe (tools/cost_map.py): cycles this warp spent in shade_pixel, in the alpha channel of the float frame
-        if (A.rgba32f) A.rgba32f[idx].w = (float)(clock64() - costT0);
+        if (A.rgba32f) {
+            const long long t1 = clock64();
+            const long long m0 = R.mark[0] ? R.mark[0] : t1, m1 = R.mark[1] ? R.mark[1] : m0, m2 = R.mark[2] ? R.mark[2] : t1;
+            // x: to the end of loop A / free flight, y: ratios + replay, z: loop B + shading, w: everything (rest = shadow ray)
+            A.rgba32f[idx] = make_float4((float)(m0 - costT0), (float)(m1 - m0), (float)(m2 - m1), (float)(t1 - costT0));
+        }
 #endif
     }
 

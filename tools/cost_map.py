@@ -18,7 +18,8 @@ w, h = 1920, 1080
 p = rc.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=0, hits=True, rgba32f=True)
 for _ in range(3):
     c.render_frame(p)
-f = c.read_image(fmt=rc.RC_RGBA32F).reshape(h, w, 4)[:, :, 3].astype(np.float64)
+f4 = c.read_image(fmt=rc.RC_RGBA32F).reshape(h, w, 4).astype(np.float64)
+f = f4[:, :, 3]
 hits = c.read_hits().reshape(h, w)
 # one value per warp tile (8 wide, 4 high)
 tile = f.reshape(h // 4, 4, w // 8, 8).max(axis=(1, 3))
@@ -30,6 +31,12 @@ print(f"warps {tile.size}, mean cycles {tile.mean():.0f}, primary {c.stats().pri
 for name, m in (("all sky", sky == 32), ("all terrain", sky == 0), ("mixed", (sky > 0) & (sky < 32))):
     print(f"{name:12s}: {m.mean() * 100:5.1f}% of warps, {tile[m].sum() / tot * 100:5.1f}% of warp-cycles, mean {tile[m].mean():.0f} cycles, "
           f"mean max-steps {steps.max(axis=(1, 3))[m].mean():.0f}")
+# sections: per warp the lane maxima (x: set-up + loop A + free flight, y: ratios + replay, z: loop B + shading, rest: shadow ray)
+sec = f4.reshape(h // 4, 4, w // 8, 8, 4).max(axis=(1, 3))
+for name, m in (("all sky", sky == 32), ("all terrain", sky == 0)):
+    t = sec[m]
+    print(f"{name:12s}: loop A {t[:, 0].mean():.0f}  replay {t[:, 1].mean():.0f}  loop B + shading {t[:, 2].mean():.0f}  "
+          f"shadow + rest {(t[:, 3] - t[:, 0] - t[:, 1] - t[:, 2]).mean():.0f}  total {t[:, 3].mean():.0f} cycles (lane maxima, they overlap)")
 rows = tile.sum(axis=1)
 nb = 10
 for b in range(nb):
