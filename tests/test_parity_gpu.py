@@ -111,6 +111,58 @@ def test_free_flight_changes_nothing(rcmod, caster, defaults):
             assert np.array_equal(g[0], got[2][0])
 
 
+def test_sky_gates_follow_the_world(ob, rcmod, caster, world_desc, defaults):
+    """The free-flight gates are rebuilt from the tree after every world change.  Worlds made for them: empty (every ray that
+    steps up is free at once), a few blocks floating high above bare ground, then edits through rc_update_world that put a
+    block into empty sky and take it away again -- every frame against the oracle (hit records bit-exact, shadows included:
+    shadow rays use the gates too), and identical with free flight off."""
+    from raytracing_test_b200 import voxel_host as vh
+
+    _, _, sun = defaults
+    cams = [((60.5, 40.5, 60.5), camera_dir(45.0, -35.0)), ((60.5, 40.5, 60.5), camera_dir(-100.0, -60.0)),  # pitch < 0: up
+            ((100.5, 130.5, 90.5), camera_dir(200.0, 40.0)), ((20.5, 5.5, 20.5), camera_dir(45.0, -10.0))]
+
+    def check(host, label):
+        nodes, arrays = host.pools()
+        ow = ob.make_world(nodes, arrays, 6)
+        n_hit = 0
+        for i, (o, dd) in enumerate(cams):
+            ref = ob.render(ow, ob.make_frame(480, 270, o, dd, sun, shadows=True))
+            frames = []
+            for ff in (True, False):
+                caster.render_frame(rcmod.frame_params(480, 270, o, dd, sun, shadows=True, hits=True, free_flight=ff))
+                frames.append((caster.read_image().copy(), caster.read_hits().copy()))
+            assert frames[0][1].tobytes() == ref["hits"].tobytes(), (label, i)
+            assert frames[1][1].tobytes() == ref["hits"].tobytes(), (label, i)
+            assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][0], ref["rgba8"])
+            n_hit += int((ref["hits"]["kind"] == 1).sum())
+        return n_hit
+
+    host = vh.World(6)
+    try:
+        caster.upload_world(host.describe())
+        assert check(host, "empty world") == 0
+        for x in range(0, 160, 2):  # bare ground: a strip of 1-voxel columns, so that shadow rays have something to start from
+            for z in range(40, 120, 2):
+                host.put_block(x, 3, z, color=0x3FF00000000, flags=0)
+        host.put_block(90, 100, 90, color=0x1FFFFF, flags=0)
+        host.put_block(64, 120, 64, color=0x7FE00000, flags=0, level=5)   # a 4^3 cell
+        host.put_block(30, 200, 100, color=0x1FFFFF, flags=0)
+        caster.upload_world(host.describe())
+        before = check(host, "floating blocks")
+        assert before > 0
+        host.put_block(78, 58, 78, color=0x1FFFFF, flags=0, level=5)       # into the empty sky, in the middle of the first view
+        info = caster.update_world(host.describe(), None, None)
+        after = check(host, "after put")
+        assert after > before
+        host.put_block(95, 75, 95, color=0x1FFFFF, flags=0)
+        caster.update_world(host.describe(), None, None)
+        check(host, "after second put")
+    finally:
+        host.close()
+        caster.upload_world(world_desc)
+
+
 def test_cuda_frame_equals_the_reference_shader_frame(ob, rcmod, caster, ref_world, defaults):
     """No oracle in between: the CUDA frame against src/shaders/low_res.frag itself, compiled as C++
     (oracle/_ref/libref_shader.so, see tests/test_ref_shader_cpu.py) -- FragColor float for float at config 2's
