@@ -102,6 +102,8 @@ typedef struct rc_frame_params {
 #define RC_F_NO_FREE_FLIGHT 0x10u /* tests / measurements: primary rays that rise above everything they can still reach
                                      keep walking cells instead of finishing their steps in the free-flight loop
                                      (same frame, same hit records either way) */
+#define RC_F_ALWAYS_TAIL 0x40u /* tests / measurements: work out where a free-flight ray ends even when nothing can show it
+                                  (no hit records, no position debug output, looked-at voxel out of its reach) */
 #define RC_F_NO_LEAP   0x20u /* tests / measurements: the free-flight loop walks every step instead of leaping over most of
                                 them in closed form (same frame, same hit records either way) */
 

@@ -601,6 +601,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     // tree is consulted only when the ray leaves the cell.  Inside a brick a step adds a bit test.
     uint32_t i = 0;
     uint32_t steps = 0;
+    bool tailSkipped = false;
     const uint32_t numSteps = P.max_steps;
     {
         StepAxis ax;
@@ -707,13 +708,20 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 const unsigned m = __activemask();
                 if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&A.counters->free_flight_rays, (unsigned)__popc(m));
             }
-            // free_flight.h: most of the remaining steps in closed form, the last few walked; the voxel the ray ends in
-            int nx, ny, nz;
-            free_flight(pos.tx, pos.ty, pos.tz, ray.adx, ray.ady, ray.adz, ray.dx, ray.dy, ray.dz, numSteps - steps,
-                        !(P.flags & RC_F_NO_LEAP), nx, ny, nz, ax.x, ax.y);
-            pos.x += ray.sx * nx;
-            pos.y += ray.sy * ny;
-            pos.z += ray.sz * nz;
+            if (A.sky_tail) {
+                // free_flight.h: most of the remaining steps in closed form, the last few walked; the voxel the ray ends in
+                int nx, ny, nz;
+                free_flight(pos.tx, pos.ty, pos.tz, ray.adx, ray.ady, ray.adz, ray.dx, ray.dy, ray.dz, numSteps - steps,
+                            !(P.flags & RC_F_NO_LEAP), nx, ny, nz, ax.x, ax.y);
+                pos.x += ray.sx * nx;
+                pos.y += ray.sy * ny;
+                pos.z += ray.sz * nz;
+            } else {
+                // Nobody will see where this ray ends: no hit records, no position debug output, and the looked-at voxel is
+                // not max_steps steps from the camera's (every step moves one voxel along one axis, the signs never
+                // change in loop A), so the highlight test below cannot fire.  The pixel is sky either way.
+                tailSkipped = true;
+            }
             steps = numSteps;
         }
         if (!live) return;
@@ -857,7 +865,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     }
 
     // :347-350
-    if (P.looking_at[0] == pos.x && P.looking_at[1] == pos.y && P.looking_at[2] == pos.z) {
+    if (!tailSkipped && P.looking_at[0] == pos.x && P.looking_at[1] == pos.y && P.looking_at[2] == pos.z) {
         const F3 c = decode_color(packedColor);
         out.color = F3{FADD(FMUL(c.x, 2.0f), 0.3f), FADD(FMUL(c.y, 2.0f), 0.3f), FADD(FMUL(c.z, 2.0f), 0.3f)};
         out.hit.kind = RC_KIND_HIGHLIGHT;

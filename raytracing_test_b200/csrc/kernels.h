@@ -61,6 +61,8 @@ struct FrameArgs {
     // tree too shallow).
     const uint4* sky_gate;
     int sky_shift;
+    uint32_t sky_tail;       // 1: a free ray's final voxel / last face are needed (hit records, position debug output, or the
+                             // looked-at voxel lies exactly max_steps steps from the camera's); 0: nobody can see them
     uint32_t shadow_gate;    // the table also covers the shadow rays' reach (shadow_steps <= max_steps, flags allow it)
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;

@@ -668,6 +668,12 @@ int rc_render_frame(const rc_frame_params* params) {
             a.sky_gate = g.dSkyGate;
             a.sky_shift = g.skyShift;
             a.shadow_gate = p.shadow_steps <= p.max_steps ? 1u : 0u;
+            // where a free ray ends matters only to the hit records, to render_pos_data = 2 (pos.round as colour) and to
+            // the highlight test (low_res.frag:347-350) -- which a ray that has taken all max_steps steps can only pass
+            // if the looked-at voxel is exactly that many steps (|dx| + |dy| + |dz|) from the camera's
+            long long manhattan = 0;
+            for (int k = 0; k < 3; k++) manhattan += llabs((long long)p.looking_at[k] - (long long)floorf(p.origin[k]));
+            a.sky_tail = ((p.flags & (RC_F_HITS | RC_F_ALWAYS_TAIL)) || p.render_pos_data != 0 || manhattan == (long long)p.max_steps) ? 1u : 0u;
         }
     }
     a.local_rows = localRows;

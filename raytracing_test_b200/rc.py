@@ -13,7 +13,7 @@ import numpy as np
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RC_LIBRC") or os.path.join(PKG_DIR, "librc.so")  # RC_LIBRC: a variant build (kernel tuning)
 
-RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F, RC_F_NO_FREE_FLIGHT, RC_F_NO_LEAP = 1, 2, 4, 8, 16, 32
+RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F, RC_F_NO_FREE_FLIGHT, RC_F_NO_LEAP, RC_F_ALWAYS_TAIL = 1, 2, 4, 8, 16, 32, 64
 RC_RGBA8, RC_RGBA32F = 0, 1
 RC_IPC_HANDLE_BYTES = 64
 RC_ALL_BLOCKS = 0xFFFFFFFF
@@ -234,7 +234,7 @@ def default_proj_plane(width, height):
 
 def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
                  ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
-                 render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None, free_flight=True, leap=True):
+                 render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None, free_flight=True, leap=True, always_tail=False):
     p = FrameParams()
     p.origin[:] = [float(v) for v in origin]
     p.camera_dir[:] = [float(v) for v in camera_dir]
@@ -253,6 +253,8 @@ def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao
         flags |= RC_F_NO_FREE_FLIGHT
     if not leap:
         flags |= RC_F_NO_LEAP
+    if always_tail:
+        flags |= RC_F_ALWAYS_TAIL
     pp = default_proj_plane(width, height) if proj_plane is None else proj_plane
     p.proj_plane[:] = [float(pp[0]), float(pp[1])]
     p.delta_time, p.ao_strength = delta_time, ao_strength

@@ -94,6 +94,22 @@ def test_free_flight_changes_nothing(rcmod, caster, defaults):
         sky = int((a[2]["kind"] == 0).sum())  # RC_KIND_SKY
         assert a[3].free_flight_rays > 0.5 * sky, (name, a[3].free_flight_rays, sky)
     assert b[3].free_flight_rays == 0
+    # Without hit records (and without the position debug output) nobody can see where a free ray ends, and the tail is not
+    # worked out at all -- unless the looked-at voxel lies exactly max_steps steps from the camera's, the one case in which
+    # the highlight test (low_res.frag:347-350) could fire on a ray that ran out of steps.  Same frame in every case.
+    sky_px = np.flatnonzero(frames["on"][2]["kind"] == 0)
+    end = frames["on"][2][sky_px[len(sky_px) // 2]]           # where some sky ray ends: 300 steps from the camera's voxel
+    for la in ((1 << 30, 1 << 30, 1 << 30), (int(end["x"]), int(end["y"]), int(end["z"])), (int(end["x"]) + 1, int(end["y"]), int(end["z"]))):
+        imgs = []
+        for kw in ({"hits": True}, {}, {"always_tail": True}, {"free_flight": False}):
+            caster.render_frame(rcmod.frame_params(1920, 1080, pos, d, sun, shadows=True, rgba32f=True, looking_at=la, **kw))
+            imgs.append((caster.read_image().copy(), caster.read_image(fmt=rcmod.RC_RGBA32F).copy()))
+        for im in imgs[1:]:
+            assert np.array_equal(im[0], imgs[0][0]) and np.array_equal(im[1].view(np.uint32), imgs[0][1].view(np.uint32)), la
+    # (the middle one really is highlighted)
+    caster.render_frame(rcmod.frame_params(1920, 1080, pos, d, sun, shadows=True, hits=True,
+                                           looking_at=(int(end["x"]), int(end["y"]), int(end["z"]))))
+    assert int((caster.read_hits()["kind"] == 4).sum()) > 0  # RC_KIND_HIGHLIGHT
     # other step budgets (the gate table is rebuilt per budget), cameras looking down / high above the terrain / along an
     # axis (absDelta = inf), all yaw / pitch combinations of the parity cameras
     cams = [(64, pos, d), (1000, pos, d), (1024, pos, d), (300, (100.5, 120.25, 100.5), camera_dir(30.0, -50.0)),
