@@ -463,6 +463,16 @@ def run_b200_arm(args, workload):
         k_ao.append(s.ao_ms)
     kern_ms["primary"] = float(np.mean(k_primary))
     kern_ms["ao"] = float(np.mean(k_ao))
+    # The frames above carry no hit records, so a sky ray in free flight does not work out the voxel it would end in (nothing
+    # can show it: DESIGN section 4).  For the record, the primary kernel with that tail forced (what a parity frame pays):
+    params_tail = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look),
+                                  always_tail=True)
+    k_tail = []
+    for _ in range(min(args.steps, 20)):
+        flush.zero_()
+        sc.render(params_tail)
+        k_tail.append(sc.stats().primary_ms)
+    kern_ms["primary_with_free_flight_tail"] = float(np.mean(k_tail))
 
     # max over ranks (time) / sum over ranks (rays)
     if world_size > 1:
@@ -663,6 +673,9 @@ def run_b200_arm(args, workload):
                    "world_bytes": {"reference_format": int(info.ref_bytes), "packed": int(info.packed_bytes)},
                    "camera": "default (35,50,35) dir normalize(1,0,1)", "rays_per_step": frame_rays,
                    "l2": "flushed between steps (256 MB memset, outside the timed events)",
+                   "outputs": "the RGBA8 frame (what the reference's render() produces); no hit records, so sky rays in free "
+                              "flight do not work out the voxel they would end in -- kernel_ms.primary_with_free_flight_tail "
+                              "is the primary kernel with that forced, as every parity frame runs it",
                    "sharding": f"16-row bands round-robin over {world_size} GPUs, " + (
                        "kernels store into rank 0's frame over NVLink peer memory (CUDA IPC), one-element all-reduce as the "
                        "completion signal" if sc.mode == "direct" else "NCCL gather to rank 0 + compose kernel")
