@@ -1252,9 +1252,14 @@ struct AowRayArgs {
     float a0x, a1x, a0y, a1y, a0z, a1z;    // (pos.exact - pos.round) for a positive / negative step sign
     uint32_t nSteps;
     bool liquid, f2;
+    uint32_t acc1;                         // FORCED: occupancy of the voxel behind the hit face, in the form the ray loop gathers
 };
 
-template <uint32_t NSTEPS, bool BYTES>
+// FORCED: the kernel has proved for every pixel of the warp that the first step of each of its rays is the forced one
+// through the hit face (and no window holds LIQUID): that step is then three additions -- deltaPos[face] gets back the
+// absDelta[face] it was lowered by, the same rounded sum the loop would do -- the ray starts at the voxel behind the face,
+// whose occupancy was read once for the pixel, and nothing has to be looked at before using the window.
+template <uint32_t NSTEPS, bool BYTES, bool FORCED>
 __device__ __forceinline__ uint32_t aow_cast_rays(const DeviceWorld& W, const AoDir* __restrict__ dirs, const AowRayArgs& a) {
     const uint32_t nSteps = a.nSteps;
     uint32_t occluded = 0;
@@ -1282,11 +1287,16 @@ __device__ __forceinline__ uint32_t aow_cast_rays(const DeviceWorld& W, const Ao
             // read straight from the bit pattern.  No early exit on a hit: the warp runs until its last ray is done anyway,
             // a ray that has hit stays inside the window (it covers every position ao_steps steps can reach), and without
             // the branch the load of one step overlaps the compares of the next.
-            float qf = a.q0f;
-            uint32_t acc = 0u;
-            bool window = !a.liquid;
+            float qf = FORCED ? a.q1f : a.q0f;
+            uint32_t acc = FORCED ? a.acc1 : 0u;
+            bool window = FORCED ? true : !a.liquid;
+            if (FORCED) {  // v1.z / v1.w: absDelta[face] for an x / y face, else 0 (v + 0 = v)
+                px = FADD(px, v1.z);
+                py = FADD(py, v1.w);
+                if (a.f2) pz = FADD(pz, adz);
+            }
 #pragma unroll
-            for (uint32_t i = 0; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
+            for (uint32_t i = FORCED ? 1u : 0u; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
                 if (NSTEPS == 0 && i >= nSteps) break;
                 const bool bx = px < py && px < pz;
                 const bool by = !bx && py < pz;
@@ -1437,8 +1447,34 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     // the index after the forced first step (through the hit face): q0 + sign(normal) * stride(face)
     const float q1f = q0f + __uint_as_float((negNormal ? 0x80000000u : 0u) | (uint32_t)(f0 ? 1 : (f1 ? strideY : strideZ)));
 
-    const AowRayArgs ra{s.x, s.y, s.z, q0f, q1f, a0x, a1x, a0y, a1y, a0z, a1z, nSteps, liquid, f2};
-    const uint32_t occluded = byteMode ? aow_cast_rays<NSTEPS, true>(W, dirs, ra) : aow_cast_rays<NSTEPS, false>(W, dirs, ra);
+    // With pos.exact exactly on the hit face (its face coordinate = the voxel's, + 1 for a positive normal) and inside the
+    // voxel along both tangents, every sample's first step IS the forced one: deltaPos[face] = (absDelta - 1 * absDelta) -
+    // absDelta = -absDelta < 0 exactly, and a tangent deltaPos = absDelta - (0..1) * absDelta >= 0 (one rounded product,
+    // never above absDelta).  If that holds for the whole warp (and no window holds LIQUID) the rays skip that step's
+    // compares and the look-before-you-leap; pixels that fail it (rounding of pos.exact along the primary ray) keep the
+    // general loop for their warp.
+    const float aF = f0 ? a0x : (f1 ? a0y : a0z);
+    const bool forcedPixel = !liquid && aF == (negNormal ? 0.0f : 1.0f) && a0x >= 0.0f && a0x <= 1.0f && a0y >= 0.0f &&
+                             a0y <= 1.0f && a0z >= 0.0f && a0z <= 1.0f;
+    const bool forced = NSTEPS == AOW_MAX_STEPS && __all_sync(__activemask(), forcedPixel);
+    uint32_t acc1 = 0u;
+    if (forced) {
+        const uint32_t q1 = __float_as_uint(q1f);
+        uint32_t byte;
+        if (byteMode) {
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q1) : "memory");
+            acc1 = byte;
+        } else {
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q1 >> 3) : "memory");
+            acc1 = (byte * 0x01010101u) << (q1 & 31u);
+        }
+    }
+    const AowRayArgs ra{s.x, s.y, s.z, q0f, q1f, a0x, a1x, a0y, a1y, a0z, a1z, nSteps, liquid, f2, acc1};
+    uint32_t occluded;
+    if (forced)
+        occluded = byteMode ? aow_cast_rays<NSTEPS, true, true>(W, dirs, ra) : aow_cast_rays<NSTEPS, false, true>(W, dirs, ra);
+    else
+        occluded = byteMode ? aow_cast_rays<NSTEPS, true, false>(W, dirs, ra) : aow_cast_rays<NSTEPS, false, false>(W, dirs, ra);
     const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
     store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
     if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
