@@ -179,6 +179,61 @@ def test_sky_gates_follow_the_world(ob, rcmod, caster, world_desc, defaults):
         caster.upload_world(world_desc)
 
 
+def _spike_world(vh):
+    """Bare ground with a forest of one-voxel-wide towers of pseudo-random heights: rays that rise between them graze
+    tower tops at every distance and slope -- what the sky gates' slope / ring arithmetic has to get right."""
+    host = vh.World(6)
+    for x in range(0, 400, 3):
+        for z in range(0, 400, 3):
+            host.put_block(x, 2, z, color=0x3FF00000000, flags=0)
+    state = 12345
+    for x in range(4, 400, 7):
+        for z in range(5, 400, 7):
+            state = (state * 1103515245 + 12345) & 0x7FFFFFFF
+            top = 4 + (state >> 8) % 140
+            if (state >> 3) % 5 == 0:
+                top = 4 + (state >> 12) % 20      # many low ones, so that the gates near the camera stay low
+            for y in range(max(3, top - 2), top + 1):   # the top three voxels are enough for rays from below / the side
+                host.put_block(x, y, z, color=0x1FFFFF, flags=0)
+            for y in range(3, top - 2, 5):              # and a sparse stem
+                host.put_block(x, y, z, color=0x7FE00000, flags=0)
+    return host
+
+
+def test_sky_gates_on_a_forest_of_towers(ob, rcmod, caster, world_desc, defaults):
+    """Adversarial world for free flight (primary and shadow rays): hit records bit-exact against the oracle and identical
+    with free flight off, from cameras low between the towers looking up at many pitches, and with a low sun."""
+    from raytracing_test_b200 import voxel_host as vh
+
+    host = _spike_world(vh)
+    try:
+        caster.upload_world(host.describe())
+        nodes, arrays = host.pools()
+        ow = ob.make_world(nodes, arrays, 6)
+        f = np.float32
+        suns = [defaults[2], tuple(float(v) for v in (np.array([3.0, 0.35, 1.0], dtype=f) / f(np.sqrt(f(10.1225)))))]
+        cams = [((150.5, 6.5, 150.5), camera_dir(45.0, -8.0)), ((150.5, 6.5, 150.5), camera_dir(20.0, -25.0)),
+                ((201.5, 30.5, 180.5), camera_dir(-60.0, -3.0)), ((120.5, 12.5, 260.5), camera_dir(135.0, -15.0)),
+                ((180.5, 60.5, 170.5), camera_dir(80.0, -45.0)), ((160.5, 4.5, 140.5), camera_dir(5.0, -1.5))]
+        free = 0
+        for i, (o, dd) in enumerate(cams):
+            sun = suns[i % 2]
+            ref = ob.render(ow, ob.make_frame(480, 270, o, dd, sun, shadows=True))
+            frames = []
+            for ff in (True, False):
+                caster.render_frame(rcmod.frame_params(480, 270, o, dd, sun, shadows=True, hits=True, free_flight=ff))
+                frames.append((caster.read_image().copy(), caster.read_hits().copy()))
+                if ff:
+                    free += caster.stats().free_flight_rays
+            assert frames[0][1].tobytes() == ref["hits"].tobytes(), i
+            assert frames[1][1].tobytes() == ref["hits"].tobytes(), i
+            assert np.array_equal(frames[0][0], ref["rgba8"]) and np.array_equal(frames[1][0], ref["rgba8"])
+        assert free > 0
+    finally:
+        host.close()
+        caster.upload_world(world_desc)
+
+
 def test_cuda_frame_equals_the_reference_shader_frame(ob, rcmod, caster, ref_world, defaults):
     """No oracle in between: the CUDA frame against src/shaders/low_res.frag itself, compiled as C++
     (oracle/_ref/libref_shader.so, see tests/test_ref_shader_cpu.py) -- FragColor float for float at config 2's
