@@ -229,6 +229,13 @@ def test_sky_gates_on_a_forest_of_towers(ob, rcmod, caster, world_desc, defaults
             assert frames[1][1].tobytes() == ref["hits"].tobytes(), i
             assert np.array_equal(frames[0][0], ref["rgba8"]) and np.array_equal(frames[1][0], ref["rgba8"])
         assert free > 0
+        # other step budgets: the gate tables (reach in blocks, rings) are rebuilt for each
+        for steps in (40, 120, 700, 1024):
+            for o, dd in (cams[0], cams[3], cams[5]):
+                ref = ob.render(ow, ob.make_frame(320, 180, o, dd, suns[1], shadows=True, max_steps=steps, shadow_steps=min(steps, 75)))
+                caster.render_frame(rcmod.frame_params(320, 180, o, dd, suns[1], shadows=True, hits=True, max_steps=steps,
+                                                       shadow_steps=min(steps, 75)))
+                assert caster.read_hits().tobytes() == ref["hits"].tobytes(), (steps, o)
     finally:
         host.close()
         caster.upload_world(world_desc)
