@@ -179,13 +179,13 @@ def test_sky_gates_follow_the_world(ob, rcmod, caster, world_desc, defaults):
         caster.upload_world(world_desc)
 
 
-def _spike_world(vh):
+def _spike_world(vh, depth=6, off=0):
     """Bare ground with a forest of one-voxel-wide towers of pseudo-random heights: rays that rise between them graze
     tower tops at every distance and slope -- what the sky gates' slope / ring arithmetic has to get right."""
-    host = vh.World(6)
+    host = vh.World(depth)
     for x in range(0, 400, 3):
         for z in range(0, 400, 3):
-            host.put_block(x, 2, z, color=0x3FF00000000, flags=0)
+            host.put_block(off + x, 2, off + z, color=0x3FF00000000, flags=0)
     state = 12345
     for x in range(4, 400, 7):
         for z in range(5, 400, 7):
@@ -194,9 +194,9 @@ def _spike_world(vh):
             if (state >> 3) % 5 == 0:
                 top = 4 + (state >> 12) % 20      # many low ones, so that the gates near the camera stay low
             for y in range(max(3, top - 2), top + 1):   # the top three voxels are enough for rays from below / the side
-                host.put_block(x, y, z, color=0x1FFFFF, flags=0)
+                host.put_block(off + x, y, off + z, color=0x1FFFFF, flags=0)
             for y in range(3, top - 2, 5):              # and a sparse stem
-                host.put_block(x, y, z, color=0x7FE00000, flags=0)
+                host.put_block(off + x, y, off + z, color=0x7FE00000, flags=0)
     return host
 
 
@@ -236,6 +236,28 @@ def test_sky_gates_on_a_forest_of_towers(ob, rcmod, caster, world_desc, defaults
                 caster.render_frame(rcmod.frame_params(320, 180, o, dd, suns[1], shadows=True, hits=True, max_steps=steps,
                                                        shadow_steps=min(steps, 75)))
                 assert caster.read_hits().tobytes() == ref["hits"].tobytes(), (steps, o)
+    finally:
+        host.close()
+        caster.upload_world(world_desc)
+
+
+def test_sky_gates_on_a_forest_of_towers_depth7(ob, rcmod, caster, world_desc, defaults):
+    """The same forest in a depth-7 tree (4096^3 torus, column blocks of 64 x 64), planted beyond x, z = 1024."""
+    from raytracing_test_b200 import voxel_host as vh
+
+    host = _spike_world(vh, 7, 1100)
+    try:
+        caster.upload_world(host.describe())
+        nodes, arrays = host.pools()
+        ow = ob.make_world(nodes, arrays, 7)
+        sun = defaults[2]
+        for o, dd in (((1250.5, 6.5, 1250.5), camera_dir(45.0, -8.0)), ((1301.5, 30.5, 1280.5), camera_dir(-60.0, -3.0)),
+                      ((1280.5, 60.5, 1270.5), camera_dir(80.0, -45.0)), ((1260.5, 4.5, 1240.5), camera_dir(5.0, -1.5))):
+            ref = ob.render(ow, ob.make_frame(480, 270, o, dd, sun, shadows=True))
+            for ff in (True, False):
+                caster.render_frame(rcmod.frame_params(480, 270, o, dd, sun, shadows=True, hits=True, free_flight=ff))
+                assert caster.read_hits().tobytes() == ref["hits"].tobytes(), (o, ff)
+                assert np.array_equal(caster.read_image(), ref["rgba8"])
     finally:
         host.close()
         caster.upload_world(world_desc)
