@@ -229,6 +229,14 @@ def test_sky_gates_on_a_forest_of_towers(ob, rcmod, caster, world_desc, defaults
             assert frames[1][1].tobytes() == ref["hits"].tobytes(), i
             assert np.array_equal(frames[0][0], ref["rgba8"]) and np.array_equal(frames[1][0], ref["rgba8"])
         assert free > 0
+        # AO on tower faces (thin columns: every window holds several faces' worth of edges), both sample counts
+        for ao, (o, dd) in ((64, cams[1]), (20, cams[4]), (64, cams[5])):
+            tab = caster.hemisphere_table(ao)
+            ob.oracle_lib().oracle_set_hemisphere(ao, tab.ctypes.data)
+            ref = ob.render(ow, ob.make_frame(320, 180, o, dd, suns[0], shadows=True, ao_samples=ao))
+            caster.render_frame(rcmod.frame_params(320, 180, o, dd, suns[0], shadows=True, ao_samples=ao, hits=True))
+            assert caster.read_hits().tobytes() == ref["hits"].tobytes(), (ao, o)
+            assert np.array_equal(caster.read_image(), ref["rgba8"])
         # other step budgets: the gate tables (reach in blocks, rings) are rebuilt for each
         for steps in (40, 120, 700, 1024):
             for o, dd in (cams[0], cams[3], cams[5]):
