@@ -31,8 +31,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "Mrays/s (primary+AO) at 1920x1080 per B200"
 UNIT = "Mrays/s"
+
+
+def metric_name(workload, n_gpus):
+    """BASELINE.json metric: "Mrays/s (primary+AO) at 1920x1080 per B200; frame ms at 1/2/4/8 GPUs vs CPU" -- the first half
+    names the N = 1 line, the second the sharded ones (ms_per_step is the frame ms); the resolution is the line's own."""
+    w, h = WORKLOADS[workload][0], WORKLOADS[workload][1]
+    if n_gpus == 1:
+        return f"Mrays/s (primary+AO) at {w}x{h} per B200"
+    return f"Mrays/s (primary+AO), {w}x{h} frame sharded over {n_gpus} B200 (frame ms = ms_per_step)"
+
 
 WORKLOADS = {
     # name: (width, height, shadows, ao_samples, golden case holding the oracle's algorithmic byte counts)
@@ -53,6 +62,11 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--cpu-baseline-only", action="store_true",
+                    help="internal: print the cpu_baseline object of --workload as JSON and exit (the default arm runs this leg in a "
+                         "subprocess, so that the process that drives the GPU never maps an oracle library)")
+    ap.add_argument("--schedule", default=None, choices=["two_kernels", "ao_persistent", "fused", "persistent", "persistent_staged"],
+                    help="A/B runs: how librc schedules a frame on the device (default: the library's default)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
     ap.add_argument("--frame-path", choices=["direct", "gather"], default="direct",
                     help="N>1: how the bands become one frame on rank 0 (direct = peer stores from the kernels over NVLink; "
@@ -72,35 +86,49 @@ def hbm_peak():
 def golden_counters(case):
     """Algorithmic bytes of the reference algorithm for exactly this frame, counted by the oracle when
     tests/golden was generated (tools/make_golden.py): 16 B per nodes[] read + 4 B per child-index read."""
-    for name in ("frames.json", "frames_big.json"):  # configs 1-3 / configs 4-5 (tools/make_golden_big.py)
+    g = golden_case(case)
+    return g["counters"] if g else None
+
+
+def golden_case(case):
+    """The oracle's record of exactly the frame bench.py renders for a workload (same world, camera and lookingAtBlock):
+    configs 1-3 tests/golden/frames_bench.json (tools/make_golden_bench.py), configs 4-5 frames_big.json."""
+    for name in ("frames_bench.json", "frames_big.json"):
         try:
             with open(os.path.join(ROOT, "tests", "golden", name)) as f:
                 cases = json.load(f)["cases"]
             if case in cases:
-                return cases[case]["counters"]
+                return dict(cases[case], file=f"tests/golden/{name}")
         except Exception:
             pass
     return None
 
 
-def measured_instructions(workload, kernel):
-    """smsp__inst_executed.sum (warp instructions) of one launch of `kernel` from the same ncu capture; the count is
-    a property of the frame (same rays, same steps), not of the run."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f)[workload][kernel].get("warp_instructions_per_launch")
-    except Exception:
-        return None
+def sha256_of(array):
+    import hashlib
+
+    return hashlib.sha256(np.ascontiguousarray(array).tobytes()).hexdigest()
 
 
-def measured_traffic(workload, kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full`
-    capture of this workload (profiles/traffic.json, written by tools/ncu_traffic.py); None if not captured."""
+def kernel_sources_sha256():
+    """Same digest csrc/Makefile bakes into librc.so (rc_build_id) and tools/ncu_traffic.py records with a capture."""
+    import hashlib
+
+    h = hashlib.sha256()
+    for name in ("kernels.cu", "kernels.h", "free_flight.h"):
+        with open(os.path.join(ROOT, "raytracing_test_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def capture_record(workload):
+    """(per-kernel records, kernel-source digest) of the committed ncu capture of this workload, or ({}, None)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f)[workload][kernel]["dram_bytes_per_launch"]
+            j = json.load(f)
+        return j.get(workload, {}), j.get("_kernel_sources_sha256", {}).get(workload)
     except Exception:
-        return None
+        return {}, None
 
 
 class ClockSampler:
@@ -160,9 +188,19 @@ def build_host_world(workload):
     return vh.World.default(), 6
 
 
-def cpu_render_sample(workload, stride, threads=0, world_cache={}):
+def host_threads():
+    """Threads the CPU arm asks for: every core this process may run on.  Passed EXPLICITLY to the oracle (num_threads
+    clause): launchers such as torchrun export OMP_NUM_THREADS=1 for nproc > 1, which a default-sized OpenMP team obeys."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_render_sample(workload, stride, threads=None, world_cache={}):
     """One bounded sample of the workload on the host cores: every stride-th 16-row band of the frame,
-    all passes. Returns (rays, seconds, algorithmic bytes by phase)."""
+    all passes. Returns (rays, seconds, algorithmic bytes by phase); cpu_render_sample.last_threads = the OpenMP team
+    the run really got."""
     from oracle import bindings as ob  # the checker, timed here as the CPU baseline only
     from raytracing_test_b200 import voxel_host as vh
 
@@ -177,11 +215,12 @@ def cpu_render_sample(workload, stride, threads=0, world_cache={}):
             ob.oracle_lib().oracle_set_hemisphere(ao, tab.ctypes.data)
     ow = world_cache[workload][0]
     pos, d, sun = vh.default_camera()
-    frame = ob.make_frame(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, threads=threads,
+    frame = ob.make_frame(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, threads=threads if threads else host_threads(),
                           bands=(16, stride, 0) if stride > 1 else None)
     t = time.perf_counter()
     r = ob.render(ow, frame, want_hits=False, want_rgba8=True)
     dt = time.perf_counter() - t
+    cpu_render_sample.last_threads = int(ob.oracle_lib().oracle_last_threads())
     c = r["counters"]
     return int(sum(c.rays)), dt, c.as_dict()["algorithmic_bytes"]
 
@@ -191,7 +230,6 @@ def run_reference_arm(args, workload):
     if rank != 0:
         return
     w, h, shadows, ao, _ = WORKLOADS[workload]
-    cores = os.cpu_count() or 1
     if shadows and not ao and reference_shader_sample(workload, reps=1) is not None:
         return run_reference_shader_arm(args, workload)  # config 2 = the live shader: time the reference's own source
     stride = max(1, (w * h) // (1920 * 1080) * 8)
@@ -208,9 +246,10 @@ def run_reference_arm(args, workload):
         total_rays += rays
         total_s += dt
     value = total_rays / total_s / 1e6
+    cores = cpu_render_sample.last_threads  # the OpenMP team the timed runs really had
     sample = f"every {stride}th 16-row band of the {w}x{h} frame per step ({rays} rays/step), all passes, OpenMP x{cores}"
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+        "metric": metric_name(workload, args.gpus), "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao,
@@ -241,7 +280,7 @@ def run_reference_shader_arm(args, workload):
         total_s += last["seconds"]
     value = total_rays / total_s / 1e6
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+        "metric": metric_name(workload, args.gpus), "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao,
@@ -299,7 +338,7 @@ def reference_ray_caster_sample(workload, target_rays=40000):
             "hits": int((out[:, 6] > 0).sum())}
 
 
-def reference_shader_sample(workload, threads=0, reps=3, state={}):
+def reference_shader_sample(workload, threads=None, reps=3, state={}):
     """The reference's OWN renderer on the host cores: src/shaders/low_res.frag compiled as C++ (oracle/ref_shader.cpp ->
     oracle/_ref/libref_shader.so; GLSL itself cannot run on this box), one instance per pixel, OpenMP over rows, over the
     world the reference's unmodified putBlock / genWorld built.  It is the live shader as it stands: primary + sun-shadow
@@ -334,10 +373,10 @@ def reference_shader_sample(workload, threads=0, reps=3, state={}):
     best = None
     for _ in range(reps):
         t = time.perf_counter()
-        n = shader.render(w, h, pos, d, sun, row_stride=row_stride, threads=threads, want_state=False)["fragments"]
+        out = shader.render(w, h, pos, d, sun, row_stride=row_stride, threads=threads if threads else host_threads(), want_state=False)
         dt = time.perf_counter() - t
         best = dt if best is None else min(best, dt)
-    cores = threads if threads > 0 else (os.cpu_count() or 1)
+    n, cores = out["fragments"], out["threads"]  # the OpenMP team the run really had
     what = "whole" if row_stride == 1 else f"every {row_stride}th row of the"
     return {"value": rays / best / 1e6, "unit": "Mrays/s (primary + shadow rays: the live shader)", "cores": cores,
             "kind": "reference", "rays": rays, "seconds": best, "fragments": n,
@@ -348,7 +387,6 @@ def reference_shader_sample(workload, threads=0, reps=3, state={}):
 def cpu_baseline_leg(workload):
     """cpu_baseline object of the default arm: about 10-30 s of CPU work on rank 0."""
     w, h, shadows, ao, _ = WORKLOADS[workload]
-    cores = os.cpu_count() or 1
     stride = max(1, (w * h) // (1920 * 1080))
     cpu_render_sample(workload, 64)  # builds the world, warms the caches
     best, spent, reps, rays = None, 0.0, 0, 0
@@ -357,6 +395,7 @@ def cpu_baseline_leg(workload):
         best = dt if best is None else min(best, dt)
         spent += dt
         reps += 1
+    cores = cpu_render_sample.last_threads
     one_rays, one_dt, _ = cpu_render_sample(workload, max(stride, 4), threads=1)
     port = {
         "value": rays / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
@@ -388,6 +427,19 @@ def cpu_baseline_leg(workload):
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
+def cpu_baseline_subprocess(workload):
+    """The cpu_baseline leg in a process of its own: the process that drives the GPU never maps an oracle library."""
+    try:
+        out = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-baseline-only", "--workload", workload],
+                             capture_output=True, text=True, timeout=900)
+        for line in reversed(out.stdout.strip().splitlines()):
+            if line.startswith("{"):
+                return json.loads(line)
+        return {"unavailable": (out.stderr or out.stdout)[-300:]}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)}
+
+
 def run_b200_arm(args, workload):
     import torch
     import torch.distributed as dist
@@ -408,22 +460,66 @@ def run_b200_arm(args, workload):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    w, h, shadows, ao, golden_case = WORKLOADS[workload]
+    w, h, shadows, ao, case = WORKLOADS[workload]
+    golden = golden_case(case)
     host, depth = build_host_world(workload)
     pos, d, sun = vh.default_camera()
-    look, _, _ = host.pick(pos, d, 30)  # src/main.cpp:81: the host's picking ray feeds lookingAtBlock
+    look = tuple(int(v) for v in host.pick(pos, d, 30)[0])  # src/main.cpp:81: the host's picking ray feeds lookingAtBlock
 
     sc = fg.ShardedRayCaster(local_rank, rank, world_size, mode=args.frame_path)
+    if args.schedule:
+        sc.caster.set_option("schedule", args.schedule)
     info = sc.upload_world(host.describe())
-    params = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look))
+    kw = dict(shadows=shadows, ao_samples=ao, looking_at=look)
+    params = rc.frame_params(w, h, pos, d, sun, **kw)                 # the timed frame: what the reference's render() produces
+    params_hits = rc.frame_params(w, h, pos, d, sun, hits=True, **kw)  # + parity records (free-flight rays work out where they end)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = sc.stream  # librc's kernels, the NCCL gather, the flush and the timing events all go on this stream
     torch.cuda.set_stream(stream)
+    n_side = min(args.steps, 20)  # frames of each side measurement (outside the timed K steps)
+    checked = []  # (what, sha256) of every frame hashed against the golden
 
     def barrier():
         if world_size > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
+
+    def max_over_ranks(x):
+        if world_size == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def device_ms(render, n):
+        """Mean device time of n frames (CUDA events on the launching stream, L2 flushed before each, outside the events)."""
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        for i in range(n):
+            flush.zero_()
+            ev[i][0].record()
+            render()
+            ev[i][1].record()
+        torch.cuda.synchronize(dev)
+        return float(sum(a.elapsed_time(b) for a, b in ev)) / n
+
+    # ---- N > 1: the SAME frame on ONE GPU first (rank 0, unsharded), so that the line carries a same-workload, same-box,
+    # same-run strong-scaling figure; the other ranks wait.  Also the first parity check: that frame against the golden.
+    strong = None
+    if world_size > 1:
+        t1 = t1_hits = 0.0
+        if rank == 0:
+            sc.caster.set_shard(0, 1)
+            for _ in range(3):
+                sc.caster.render_frame(params)
+            t1 = device_ms(lambda: sc.caster.render_frame(params), n_side)
+            checked.append(("one GPU, unsharded", sha256_of(sc.caster.read_image())))
+            t1_hits = device_ms(lambda: sc.caster.render_frame(params_hits), min(n_side, 5))
+            if golden:
+                checked.append(("one GPU, unsharded, hit records", sha256_of(sc.caster.read_hits()), "hits_sha256"))
+            sc.caster.set_shard(rank, world_size)
+        barrier()
+        strong = {"workload": workload, "t1_ms": t1, "t1_ms_with_hits": t1_hits,
+                  "how": f"rank 0 rendered the unsharded frame alone ({n_side} frames, CUDA events, L2 flushed) before the sharded run"}
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -436,11 +532,11 @@ def run_b200_arm(args, workload):
     barrier()
     st = sc.stats()
     local_rays = int(st.primary_rays + st.shadow_rays + st.ao_rays)
+    schedule_used = int(st.schedule)
     launches_per_step = int(st.kernel_launches) + (1 if (world_size > 1 and rank == 0 and sc.mode == "gather") else 0)
 
     # ---- timed: K steps, device time by CUDA events on the launching stream, L2 flushed between steps ----
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kern_ms = {"primary": 0.0, "ao": 0.0}
     barrier()
     t_begin = time.time()
     for i in range(args.steps):
@@ -450,35 +546,8 @@ def run_b200_arm(args, workload):
         ev[i][1].record()
     barrier()
     t_end = time.time()
-    step_ms = [a.elapsed_time(b) for a, b in ev]
-    total_ms = float(sum(step_ms))
-
-    # per-kernel device times (librc's events around each kernel), measured on separate frames after the timed loop
-    k_primary, k_ao = [], []
-    for _ in range(min(args.steps, 20)):
-        flush.zero_()
-        sc.render(params)
-        s = sc.stats()  # synchronises
-        k_primary.append(s.primary_ms)
-        k_ao.append(s.ao_ms)
-    kern_ms["primary"] = float(np.mean(k_primary))
-    kern_ms["ao"] = float(np.mean(k_ao))
-    # The frames above carry no hit records, so a sky ray in free flight does not work out the voxel it would end in (nothing
-    # can show it: DESIGN section 4).  For the record, the primary kernel with that tail forced (what a parity frame pays):
-    params_tail = rc.frame_params(w, h, pos, d, sun, shadows=shadows, ao_samples=ao, looking_at=tuple(int(v) for v in look),
-                                  always_tail=True)
-    k_tail = []
-    for _ in range(min(args.steps, 20)):
-        flush.zero_()
-        sc.render(params_tail)
-        k_tail.append(sc.stats().primary_ms)
-    kern_ms["primary_with_free_flight_tail"] = float(np.mean(k_tail))
-
-    # max over ranks (time) / sum over ranks (rays)
+    total_ms = max_over_ranks(float(sum(a.elapsed_time(b) for a, b in ev)))
     if world_size > 1:
-        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
         r = torch.tensor([local_rays], dtype=torch.int64, device=dev)
         dist.all_reduce(r, op=dist.ReduceOp.SUM)
         frame_rays = int(r.item())
@@ -486,6 +555,44 @@ def run_b200_arm(args, workload):
         frame_rays = local_rays
     ms_per_step = total_ms / args.steps
     value = frame_rays / (ms_per_step * 1e-3) / 1e6
+
+    # ---- side measurements, outside the timed steps -------------------------------------------------------------------
+    # (a) the same frame WITH hit records: free-flight sky rays then work out the voxel they end in
+    barrier()
+    ms_hits = max_over_ranks(device_ms(lambda: sc.render(params_hits), n_side))
+    if world_size == 1 and golden:
+        checked.append(("hit records of the timed frame", sha256_of(sc.caster.read_hits()), "hits_sha256"))
+    # (b) per-kernel device times: librc's own events around each kernel (RC_F_KERNEL_TIMES) under the two-kernel schedule;
+    # the default schedule is ONE fused kernel, whose time is the frame's
+    kern_ms = {}
+    names = {v: k for k, v in rc.SCHEDULES.items()}
+    tot = []
+    for _ in range(n_side):
+        flush.zero_()
+        sc.render(params)
+        tot.append(sc.stats().total_ms)  # synchronises
+    kern_ms[names[schedule_used]] = float(np.mean(tot))
+    if not args.schedule:
+        p_kt = rc.frame_params(w, h, pos, d, sun, kernel_times=True, **kw)
+        p_kt_tail = rc.frame_params(w, h, pos, d, sun, kernel_times=True, always_tail=True, **kw)
+        sc.caster.set_option("schedule", "two_kernels")
+        k_primary, k_ao, k_tail = [], [], []
+        for _ in range(n_side):
+            flush.zero_()
+            sc.render(p_kt)
+            s_ = sc.stats()
+            k_primary.append(s_.primary_ms)
+            k_ao.append(s_.ao_ms)
+        for _ in range(n_side):
+            flush.zero_()
+            sc.render(p_kt_tail)
+            k_tail.append(sc.stats().primary_ms)
+        kern_ms["two_kernels_primary"] = float(np.mean(k_primary))
+        kern_ms["two_kernels_ao"] = float(np.mean(k_ao))
+        kern_ms["two_kernels_primary_with_free_flight_tail"] = float(np.mean(k_tail))
+        sc.caster.set_option("schedule", schedule_used)
+        sc.render(params)
+    barrier()
 
     # ---- e2e: through the C-ABI with HOST buffers: params in, RGBA8 frame out into pinned memory, every step ----
     e2e = None
@@ -510,12 +617,7 @@ def run_b200_arm(args, workload):
             t0 = time.perf_counter()
             run()
             barrier()
-            dt = time.perf_counter() - t0
-            if world_size > 1:
-                t = torch.tensor([dt], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                dt = float(t.item())
-            return dt
+            return max_over_ranks(time.perf_counter() - t0)
 
         def run_sync():
             for _ in range(args.steps):
@@ -535,7 +637,7 @@ def run_b200_arm(args, workload):
 
         def run_pipelined_sharded():
             # N>1, direct frame: rank 0 copies frame i out of one frame slot while every rank traces frame i+1
-            # into the other; the peers are held back by the per-frame all-reduce
+            # into the other; the peers are held back by the per-frame completion signal
             prev = None
             for i in range(args.steps):
                 sc.render(params)
@@ -576,7 +678,11 @@ def run_b200_arm(args, workload):
 
         for _ in range(3):
             sync_step()
+        if rank == 0:
+            checked.append(("rc_read_image, synchronous" if world_size == 1 else "rank 0's frame written by every rank's kernels (peer stores)"
+                            if sc.mode == "direct" else "rank 0's frame after the NCCL gather + compose", sha256_of(host_img)))
         sync_s = timed(run_sync)
+        rank0_s = None
         e2e_s, how = sync_s, "rc_render_frame(host params) + rc_read_image into pinned host memory, synchronous, every step"
         if world_size == 1:
             host_imgs[1][:] = 0
@@ -584,12 +690,14 @@ def run_b200_arm(args, workload):
             e2e_s = timed(run_pipelined)
             how = ("rc_render_frame(host params) + rc_read_image_async into one of two pinned host frames + rc_wait_image, "
                    "every step; frame N+1 is traced while frame N is copied (double-buffered like the reference's swap chain)")
-            assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
+            checked.append(("rc_read_image_async, host frame 0", sha256_of(host_imgs[0])))
+            checked.append(("rc_read_image_async, host frame 1", sha256_of(host_imgs[1])))
         elif sc.mode == "direct":
             run_pipelined_sharded()
             rank0_s = timed(run_pipelined_sharded)
             if rank == 0:
-                assert np.array_equal(host_imgs[0], host_imgs[1]), "pipelined frames differ from each other"
+                checked.append(("peer-store frame, pipelined read-back, host frame 0", sha256_of(host_imgs[0])))
+                checked.append(("peer-store frame, pipelined read-back, host frame 1", sha256_of(host_imgs[1])))
             try:
                 sink["frames"] = fg.SharedHostFrames(w, h, rank, world_size, slots=2, pin=sc.caster)
             except RuntimeError as e:  # raised on every rank together (no room in /dev/shm)
@@ -602,8 +710,8 @@ def run_b200_arm(args, workload):
                 run_host_direct()
                 e2e_s = timed(run_host_direct)
                 if rank == 0:
-                    for f in sink["frames"].frames:
-                        assert np.array_equal(f, host_imgs[0]), "frame assembled in shared host memory differs from rank 0's frame"
+                    for i, f in enumerate(sink["frames"].frames):
+                        checked.append((f"frame assembled in shared host memory by every rank's own read-back, slot {i}", sha256_of(f)))
                 sink["frames"].close()
                 how = ("every rank: rc_render_frame(host params) + rc_read_image_async of ITS bands into one shared page-locked "
                        "host frame (POSIX shared memory, two frame slots), every step; rank 0 consumes each complete frame; no "
@@ -612,88 +720,148 @@ def run_b200_arm(args, workload):
                "h2d_bytes_per_step": 104, "d2h_bytes_per_step": w * h * 4,
                "ms_per_step": e2e_s / args.steps * 1e3,
                "sync_ms_per_step": sync_s / args.steps * 1e3,
-               **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if world_size > 1 and sc.mode == "direct" else {}),
+               **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if rank0_s is not None else {}),
                "sync_value": frame_rays * args.steps / sync_s / 1e6,
                "what": how + ("; includes the NCCL band gather + compose on rank 0"
                               if world_size > 1 and sc.mode == "gather" else "")}
         if rank == 0:
             assert host_img.any(), "e2e frame is empty"
+    elif rank == 0:
+        if world_size == 1:
+            sc.caster.render_frame(params)
+            checked.append(("rc_read_image, synchronous", sha256_of(sc.caster.read_image())))
+        else:
+            sc.render(params)
+            torch.cuda.synchronize(dev)
+            checked.append(("rank 0's composed frame", sha256_of(sc.frame().cpu().numpy())))
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
+    build_id = sc.caster.build_id()
     if rank != 0:
         sc.close()
         if world_size > 1:
             dist.destroy_process_group()
         return
 
+    # ---- parity of exactly the frames that were timed / delivered, against the oracle's golden for this workload --------
+    parity = None
+    if golden:
+        bad = [c[0] for c in checked if c[1] != golden[c[2] if len(c) > 2 else "rgba8_sha256"]]
+        parity = {"golden": case, "file": golden["file"], "rgba8_sha256_match": not any(len(c) == 2 and c[0] in bad for c in checked),
+                  "hits_sha256_match": not any(len(c) > 2 and c[0] in bad for c in checked) if any(len(c) > 2 for c in checked) else None,
+                  "frames_checked": len(checked), "checked": [c[0] for c in checked], "mismatched": bad,
+                  "what": "sha256 of each frame (and of one frame's hit records) this run rendered with the timed parameters, "
+                          "against the oracle's frame for the same parameters; outside every timed region"}
+
     # ---- roofline of the dominant kernel ----
     peak, peak_src = hbm_peak()
-    counters = golden_counters(golden_case)
+    counters = golden["counters"] if golden else None
     roof, roof_all = None, {}
+    records, capture_id = capture_record(workload)
+    src_id = kernel_sources_sha256()
+    # a capture belongs to the kernels that ran iff its digest of kernels.cu / kernels.h / free_flight.h is the one baked into
+    # the librc.so this process loaded (rc_build_id)
+    stale = (capture_id is None) or (capture_id != build_id)
     if counters:
         # one launch per rank renders 1/world_size of the frame's bands (round-robin: the shares are equal
         # to within a band), timed on rank 0
         ab = [b / world_size for b in counters["algorithmic_bytes"]]  # [primary, shadow, ao]
-        ao_name = "ao_window_kernel"  # ao_steps = 5 (<= 5: dense-window kernel; above: ao_cached_kernel)
-        per_kernel = {"primary_kernel": ((ab[0] + ab[1]), kern_ms["primary"]), ao_name: (ab[2], kern_ms["ao"])}
-        for name, (bytes_, ms) in per_kernel.items():
+        fused = schedule_used >= rc.SCHED_FUSED
+        per_kernel = {}
+        if fused:
+            per_kernel["primary_kernel"] = (sum(ab), kern_ms[names[schedule_used]],
+                                            "one fused launch: primary + shadow + AO rays (schedule %s)" % names[schedule_used])
+        if "two_kernels_primary" in kern_ms:
+            per_kernel["two_kernels/primary_kernel"] = (ab[0] + ab[1], kern_ms["two_kernels_primary"], "A/B schedule: primary + shadow rays")
+            per_kernel["two_kernels/ao_window_kernel"] = (ab[2], kern_ms["two_kernels_ao"], "A/B schedule: AO rays over the seed list")
+        for name, (bytes_, ms, what) in per_kernel.items():
             if ms > 0:
                 ach = bytes_ / (ms * 1e-3) / 1e9
-                roof_all[name] = {"algorithmic_bytes_per_launch": bytes_, "ms": ms, "achieved": ach, "frac": ach / peak}
+                roof_all[name] = {"what": what, "algorithmic_bytes_per_launch": bytes_, "ms": ms, "achieved": ach, "frac": ach / peak}
         # what really bounds these kernels (profiles/*_ncu_full_summary.txt): instruction issue.  Issue-slot use of the
         # launches timed here = warp instructions of the launch (ncu capture) / (launch time x 4 schedulers x SMs x clock)
         sm_clock = (clocks or {}).get("sm_mhz")
         if sm_clock:
             slots_per_s = 4 * torch.cuda.get_device_properties(dev).multi_processor_count * sm_clock * 1e6
             for name, r in roof_all.items():
-                inst = measured_instructions(workload, name)
-                if inst:
-                    inst /= world_size
-                    r["issue_slots"] = {"warp_instructions_per_launch": inst, "peak_per_s": slots_per_s,
-                                        "frac": inst / (r["ms"] * 1e-3) / slots_per_s}
-        dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
+                rec = records.get(name)
+                if rec and rec.get("warp_instructions_per_launch"):
+                    inst = rec["warp_instructions_per_launch"] / world_size
+                    r["issue_slots"] = {"warp_instructions_per_launch": inst, "peak_per_s": slots_per_s, "stale": stale,
+                                        "capture": rec.get("source"), "ncu_issue_active_pct": rec.get("ncu_issue_active_pct")}
+                    if not stale:
+                        r["issue_slots"]["frac"] = inst / (r["ms"] * 1e-3) / slots_per_s
+        dom = "primary_kernel" if "primary_kernel" in roof_all else (max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None)
         if dom:
-            roof = {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak, "unit": "GB/s",
-                    "frac": roof_all[dom]["frac"],
+            rec = records.get(dom, {})
+            traffic = rec.get("dram_bytes_per_launch")
+            # what the launch cannot avoid moving: the packed world once (upper bound on the part of it the rays touch), the
+            # RGBA8 frame out, and -- two-kernel schedules only -- the AO seed list written and read back (48 B per hit pixel)
+            seeds = 0 if fused else 2 * 48 * int(st.hit_pixels)
+            compulsory = (int(info.packed_bytes) + w * h * 4 // world_size + seeds)
+            roof = {"bound": "hbm", "kernel": dom, "schedule": names[schedule_used], "achieved": roof_all[dom]["achieved"], "peak": peak,
+                    "unit": "GB/s", "frac": roof_all[dom]["frac"],
                     # the capture is of one GPU rendering the whole frame; a rank of N renders 1/N of its bands
-                    "traffic": (measured_traffic(workload, dom) or 0) / world_size or None, "peak_source": peak_src,
+                    "traffic": (traffic / world_size) if (traffic and not stale) else None, "traffic_stale": stale,
+                    "compulsory_bytes": compulsory, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": roof_all[dom]["algorithmic_bytes_per_launch"],
                     "launch_ms": roof_all[dom]["ms"],
+                    "issue_slots": roof_all[dom].get("issue_slots"),
+                    "binding_resource": "instruction issue (issue_slots), not memory: the world is L1/L2 resident",
                     "note": "algorithmic bytes = what the REFERENCE algorithm fetches for this frame (16 B per nodes[] read + "
-                            "4 B per child index, counted by the oracle); the kernel's cell caching avoids most of them, so "
-                            "frac can exceed 1; traffic = DRAM bytes of one launch from the ncu capture in profiles/"}
+                            "4 B per child index, counted by the oracle); the kernel's region caching avoids most of them, so "
+                            "frac exceeds 1 and says how far the design is from the reference's traffic, not how close to the "
+                            "HBM limit; traffic = DRAM bytes of one launch from the ncu capture in profiles/ (null when that "
+                            "capture is of other kernel sources than the librc.so that ran); compulsory_bytes = packed world + "
+                            "this rank's share of the frame (+ seed list)"}
+    if strong is not None:
+        strong["tN_ms"] = ms_per_step
+        strong["n_gpus"] = world_size
+        strong["efficiency"] = strong["t1_ms"] / (world_size * ms_per_step) if ms_per_step > 0 else None
+        strong["tN_ms_with_hits"] = ms_hits
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": metric_name(workload, world_size), "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps,
+        "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world_size > 1 else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "value_with_hits": frame_rays / (ms_hits * 1e-3) / 1e6, "ms_per_step_with_hits": ms_hits,
         "config": {"workload": workload, "resolution": [w, h], "shadows": shadows, "ao_samples": ao, "ao_steps": 5,
                    "max_steps": 300, "shadow_steps": 75,
                    "world": "default generated world (initTetraHexaTree + genWorld, seeds 42/64/100, 200x200 columns)"
                             if depth == 6 else "generated world 2048x2048 columns, tree depth 7 (extension)",
                    "world_bytes": {"reference_format": int(info.ref_bytes), "packed": int(info.packed_bytes)},
                    "camera": "default (35,50,35) dir normalize(1,0,1)", "rays_per_step": frame_rays,
+                   "schedule": names[schedule_used],
                    "l2": "flushed between steps (256 MB memset, outside the timed events)",
                    "outputs": "the RGBA8 frame (what the reference's render() produces); no hit records, so sky rays in free "
-                              "flight do not work out the voxel they would end in -- kernel_ms.primary_with_free_flight_tail "
-                              "is the primary kernel with that forced, as every parity frame runs it",
+                              "flight do not work out the voxel they would end in -- value_with_hits / ms_per_step_with_hits "
+                              "are the same frame with the parity records written, as every parity test runs it",
                    "sharding": f"16-row bands round-robin over {world_size} GPUs, " + (
-                       "kernels store into rank 0's frame over NVLink peer memory (CUDA IPC), one-element all-reduce as the "
-                       "completion signal" if sc.mode == "direct" else "NCCL gather to rank 0 + compose kernel")
+                       "kernels store into rank 0's frame over NVLink peer memory (CUDA IPC), " + sc.completion_signal
+                       if sc.mode == "direct" else "NCCL gather to rank 0 + compose kernel")
                                if world_size > 1 else "none"},
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "kernel_ms": kern_ms,
-        "roofline": roof, "roofline_kernels": roof_all, "clocks": clocks,
+        "parity_check": parity, "roofline": roof, "roofline_kernels": roof_all, "clocks": clocks,
+        "librc_build_id": build_id, "kernel_sources_sha256": src_id,
     }
-    if world_size == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline_leg(workload)
+    if strong is not None:
+        line["strong_scaling"] = strong
     sc.close()
     if world_size > 1:
         dist.destroy_process_group()
+    if world_size == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_subprocess(workload)
     print(json.dumps(line), flush=True)
+    if parity and parity["mismatched"]:
+        raise SystemExit(f"bench.py: parity_check failed: {parity['mismatched']}")
 
 
 def main():
     args = parse_args()
     workload = args.workload or ("config3_1080p_ao64" if args.gpus == 1 else "config5_8k_ao64")
+    if args.cpu_baseline_only:
+        print(json.dumps(cpu_baseline_leg(workload)), flush=True)
+        return
     if args.impl == "reference":
         run_reference_arm(args, workload)
     else:

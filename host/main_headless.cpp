@@ -6,7 +6,13 @@
 // (include/voxel_host.h), a from-scratch stand-in that the tests hold to the reference's own code voxel for
 // voxel.  INTEGRATION.md shows the same loop as a patch to the real src/main.cpp.
 //
-//   rc_headless [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D]
+//   rc_headless [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D] [--gpus N]
+//               [--still] [--dump-last FILE]
+//
+// --gpus N: rc_init_multi over devices D .. D+N-1 -- the same loop, one process, one thread; the library deals the bands of
+// every frame to its devices and rc_read_image lands each device's bands in the (page-locked) host frame.
+// --still keeps the default camera and draws no crosshair (the frame of BASELINE configs 3 / 5); --dump-last FILE writes the last frame raw
+// (RGBA8, bottom row first) for byte comparisons.
 //
 // Per frame: camera yaw advances as rotateCamera() would (src/input.cpp:19-30), the picking ray feeds
 // lookingAtBlock (src/main.cpp:81,89), --edit clicks once per 8 frames (src/input.cpp:141-160: delete the picked
@@ -45,9 +51,9 @@ static void cameraDirFor(double rotationX, double rotationY, float out[3]) {
 }
 
 int main(int argc, char** argv) {
-    int frames = 16, width = 1920, height = 1080, ao = 64, device = 0;
-    bool edit = false, gpuPick = false, genDevice = false;
-    std::string out;
+    int frames = 16, width = 1920, height = 1080, ao = 64, device = 0, gpus = 1;
+    bool edit = false, gpuPick = false, genDevice = false, still = false;
+    std::string out, dumpLast;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() { return i + 1 < argc ? argv[++i] : ""; };
@@ -56,16 +62,26 @@ int main(int argc, char** argv) {
         else if (a == "--ao") ao = atoi(next());
         else if (a == "--out") out = next();
         else if (a == "--device") device = atoi(next());
+        else if (a == "--gpus") gpus = atoi(next());
+        else if (a == "--still") still = true;
+        else if (a == "--dump-last") dumpLast = next();
         else if (a == "--edit") edit = true;
         else if (a == "--gpu-pick") gpuPick = true;
         else if (a == "--gen-device") genDevice = gpuPick = true;  // no host tree: the picking ray runs on the device too
         else {
-            fprintf(stderr, "usage: %s [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D]\n", argv[0]);
+            fprintf(stderr, "usage: %s [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D] "
+                            "[--gpus N] [--still] [--dump-last file]\n", argv[0]);
             return 2;
         }
     }
 
-    check(rc_init(device), "rc_init");  // createWindow(); setupOpenGl();            src/main.cpp:176-179
+    if (gpus > 1) {  // createWindow(); setupOpenGl();                                src/main.cpp:176-179
+        std::vector<int> devices;
+        for (int i = 0; i < gpus; i++) devices.push_back(device + i);
+        check(rc_init_multi(gpus, devices.data()), "rc_init_multi");
+    } else {
+        check(rc_init(device), "rc_init");
+    }
     vh_world* world = vh_create(6);     // initTetraHexaTree();                      :181
     const int64_t seeds[3] = {42, 64, 100};
     bool hostTree = !genDevice;
@@ -100,7 +116,9 @@ int main(int argc, char** argv) {
     printf("world: %llu reference nodes (%.1f MB) -> %.2f MB packed, %s %.1f ms, upload %.2f ms\n", (unsigned long long)wi.ref_nodes,
            wi.ref_bytes / 1e6, wi.packed_bytes / 1e6, hostTree ? "flatten" : "generate", wi.flatten_ms, wi.upload_ms);
 
+    // the frame in host memory, page-locked so that every device's read-back runs as an asynchronous copy of its own
     std::vector<uint8_t> frame((size_t)width * height * 4);
+    check(rc_host_register(frame.data(), frame.size()), "rc_host_register");
     double rotationX = 45.0, rotationY = 0.0, sumMs = 0.0;  // cameraDir (1,0,1) = 45 degrees of yaw
     const vh_block placed = {vh_rgb(255, 40, 40), 0u, 0.0f};
     for (int f = 0; f < frames; f++) {
@@ -129,14 +147,14 @@ int main(int argc, char** argv) {
         memcpy(p.origin, cameraPos, 12);
         memcpy(p.camera_dir, cameraDir, 12);
         memcpy(p.sun_dir, sun, 12);
-        p.mouse_pos[0] = width * 0.5f, p.mouse_pos[1] = height * 0.5f;
+        p.mouse_pos[0] = width * 0.5f, p.mouse_pos[1] = height * 0.5f;  // (--still: no crosshair, the frame of the BASELINE configs)
         memcpy(p.looking_at, pick.pos, 12);
         p.delta_time = (float)(f / 60.0);
         p.width = (uint32_t)width, p.height = (uint32_t)height;
         p.proj_plane[0] = (float)tan(45.0 * 0.017453292519943295);
         p.proj_plane[1] = (float)(tan(45.0 * 0.017453292519943295) * ((float)height) / width);
         p.max_steps = 300, p.shadow_steps = 75, p.ao_samples = (uint32_t)ao, p.ao_steps = 5, p.ao_strength = 1.0f;
-        p.flags = RC_F_CROSSHAIR | RC_F_SHADOWS;
+        p.flags = (still ? 0u : RC_F_CROSSHAIR) | RC_F_SHADOWS;
         check(rc_render_frame(&p), "rc_render_frame");                           // glDrawArrays :105-107
         check(rc_read_image(frame.data(), frame.size(), RC_RGBA8), "rc_read_image");  // glfwSwapBuffers :216
         const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - start).count();
@@ -151,13 +169,23 @@ int main(int argc, char** argv) {
         printf("\rframe %d: %.2f ms host wall (%.3f ms on the device: primary %.3f + ao %.3f), %.1f Mrays", f, ms, st.total_ms,
                st.primary_ms, st.ao_ms, (st.primary_rays + st.shadow_rays + st.ao_rays) / 1e6);
         fflush(stdout);
+        if (still) continue;
         rotationX += 25 * (1.0 / 60.0) * 0.5 * 8;  // the right-arrow key held for 8 ticks (src/input.cpp:40,53)
         if (rotationX > 180) rotationX -= 360;
         rotationY = 35.0;  // and the down-arrow until the crosshair is on the ground (the picking ray reaches 30 voxels)
         cameraDirFor(rotationX, rotationY, cameraDir);
     }
-    if (frames > 1) printf("\nrender time: %.2f ms (%d fps) over %d frames at %dx%d, ao %d\n", sumMs / (frames - 1),
-                           (int)(1000.0 / (sumMs / (frames - 1))), frames - 1, width, height, ao);
+    if (!dumpLast.empty()) {
+        FILE* fp = fopen(dumpLast.c_str(), "wb");
+        if (!fp || fwrite(frame.data(), 1, frame.size(), fp) != frame.size()) {
+            fprintf(stderr, "cannot write %s\n", dumpLast.c_str());
+            return 1;
+        }
+        fclose(fp);
+    }
+    check(rc_host_unregister(frame.data()), "rc_host_unregister");
+    if (frames > 1) printf("\nrender time: %.2f ms (%d fps) over %d frames at %dx%d, ao %d, %d GPU%s\n", sumMs / (frames - 1),
+                           (int)(1000.0 / (sumMs / (frames - 1))), frames - 1, width, height, ao, gpus, gpus > 1 ? "s" : "");
     vh_destroy(world);
     rc_shutdown();  // glfwDestroyWindow / glfwTerminate                              :229-230
     return 0;

@@ -88,8 +88,10 @@ typedef struct rc_frame_params {
     int32_t looking_at[3];   /* lookingAtBlock <- castRayFromCam(30).pos  main.cpp:81,89 */
     int32_t render_pos_data; /* renderPosData  <- sendDebugFrame       main.cpp:87 */
     uint32_t width, height;  /* resolution                             main.cpp:93 */
-    uint32_t max_steps;      /* numSteps = 300                         low_res.frag:310 */
-    uint32_t shadow_steps;   /* 75                                     low_res.frag:382 */
+    uint32_t max_steps;      /* numSteps = 300                         low_res.frag:310; <= 65535 (rc_hit.steps is 16 bits).
+                                Above 1024 free flight is off (step counts are recovered from fp32 sums, exact up to there):
+                                same frames, sky rays walk every step */
+    uint32_t shadow_steps;   /* 75                                     low_res.frag:382; <= 65535 */
     uint32_t ao_samples;     /* 0 = AO off; 64 for BASELINE configs 3-5 (<= RC_MAX_AO_SAMPLES) */
     uint32_t ao_steps;       /* 5                                      light_scattering.frag:231 */
     uint32_t flags;          /* RC_F_* */
@@ -106,6 +108,11 @@ typedef struct rc_frame_params {
                                   (no hit records, no position debug output, looked-at voxel out of its reach) */
 #define RC_F_NO_LEAP   0x20u /* tests / measurements: the free-flight loop walks every step instead of leaping over most of
                                 them in closed form (same frame, same hit records either way) */
+
+#define RC_F_KERNEL_TIMES 0x80u /* measurements: also time the primary and the AO kernel separately (rc_frame_stats.primary_ms /
+                                   ao_ms).  The event between the two launches keeps the AO grid from becoming resident while
+                                   the primary grid drains, and a fused frame (one kernel) has no such split: without this flag
+                                   only total_ms is filled in */
 
 #define RC_MAX_AO_SAMPLES 256u
 
@@ -150,10 +157,12 @@ typedef struct rc_frame_stats {
     uint64_t primary_steps;  /* DDA steps, summed (0 unless RC_F_HITS) */
     uint32_t kernel_launches;/* kernels launched by the last rc_render_frame */
     uint32_t free_flight_rays; /* primary rays that finished their step budget in free flight (kernels.cu, loop A) */
-    float primary_ms;        /* device time of each kernel of the last frame (CUDA events */
-    float ao_ms;             /*   on the library's stream); valid after rc_sync/rc_read_* */
-    float total_ms;
-    float reserved2;
+    float primary_ms;        /* RC_F_KERNEL_TIMES and a two-kernel schedule: device time of each kernel (CUDA events on the */
+    float ao_ms;             /*   library's stream), else 0 */
+    float total_ms;          /* device time of the whole frame; valid after rc_sync / rc_read_* */
+    uint32_t schedule;       /* how the frame was scheduled: 0 primary kernel + AO kernel, 1 the same with a persistent AO grid
+                                (programmatic dependent launch), 2 one fused kernel, 3 / 4 persistent fused kernel (global
+                                atomic tile queue; 4: top tree levels staged in shared memory) */
 } rc_frame_stats;
 
 /* ---- lifetime -----------------------------------------------------------------
@@ -162,16 +171,33 @@ typedef struct rc_frame_stats {
  * rc_shutdown replaces glfwDestroyWindow/glfwTerminate (src/main.cpp:229-230). */
 int rc_init(int device);
 void rc_shutdown(void);
+
+/* Several GPUs of one box behind the same calls, from the same single host thread (the reference's host is one process with
+ * one render loop, src/main.cpp:173-232): rc_init_multi(n, devices) instead of rc_init.  Every device holds the
+ * whole world (rc_upload_world flattens once and copies to each; rc_update_world diffs once and patches each;
+ * rc_generate_world runs on each); rc_render_frame deals the 16-row bands of the frame to the devices (band % n == i) and
+ * queues every device's kernels on its own stream before any is waited for; rc_read_image / rc_read_image_async /
+ * rc_read_hits copy each device's bands to their place in the caller's frame, every device over its own PCIe link (pass
+ * page-locked memory, rc_host_register, for the copies to overlap) -- there is no device-side gather.  rc_frame_stats_get
+ * sums the rays and reports the slowest device's times.  With rc_frame_target_create the devices' kernels ALSO store every
+ * pixel into one frame on devices[0] through NVLink peer access (rc_frame_target_device; complete in that device's stream
+ * order after rc_render_frame).  rc_set_stream, rc_set_shard and rc_frame_target_open belong to the one-process-per-GPU
+ * deployment (rc_init) and are refused.  rc_pick, rc_device_image, rc_device_hits, rc_compose_frame act on devices[0]. */
+int rc_init_multi(int n_devices, const int* devices);
+int rc_device_count(void); /* devices the library drives (0 before rc_init) */
 const char* rc_last_error(void);
 int rc_abi_version(void);
+/* sha256 (hex) of the kernel sources this library was compiled from; profiles/traffic.json records the digest of the
+ * sources a profiler capture was taken with, so a reader can tell whether the two belong together. */
+const char* rc_build_id(void);
 
 /* Launch on a caller-owned cudaStream_t (e.g. torch's current stream) instead of
  * the library's own; NULL restores the internal stream. */
 int rc_set_stream(void* cuda_stream);
 
-/* Image-tile sharding for one-process-per-GPU rendering: this
- * process renders the 32x32 tiles with tile_id % world_size == rank and leaves
- * the others untouched.  (0,1) = whole frame. */
+/* Image sharding for one-process-per-GPU rendering: this process renders the bands of
+ * 16 rows with band % world_size == rank (band b = rows 16 b .. 16 b + 15, counted from the bottom
+ * row) and leaves the others untouched.  (0,1) = whole frame. */
 int rc_set_shard(uint32_t rank, uint32_t world_size);
 
 /* Layout of a sharded frame: how many rows this rank renders (local_rows, bands of 16 rows dealt

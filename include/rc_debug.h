@@ -46,6 +46,13 @@ int rc_debug_update_host(const rc_world_desc* desc, const uint32_t* dirty_node_b
 int rc_debug_save_host(const char* path);
 int rc_debug_load_host(const char* path, rc_world_info* info);
 
+/* Scheduling / specialisation switches for A/B measurements and parity tests; every setting renders the same pixels.
+ *   "schedule": 0 primary kernel + AO kernel, 1 primary kernel + persistent AO grid (atomic chunk cursor, programmatic
+ *               dependent launch), 2 one fused kernel (default), 3 persistent fused kernel over a global atomic queue of
+ *               Morton-ordered 8x4 tiles, 4 the same with the top tree levels staged in shared memory
+ *   "ao_opts" : bit 0 empty sample octants skipped (default 1) */
+int rc_debug_set_option(const char* name, int value);
+
 /* sizeof of the ABI structs as the library was compiled: rc_world_desc, rc_world_info,
  * rc_frame_params, rc_hit, rc_frame_stats (bindings check their layouts against it). */
 int rc_debug_struct_sizes(uint32_t out[5]);

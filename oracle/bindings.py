@@ -110,6 +110,7 @@ def oracle_lib():
         L.oracle_expf.argtypes = [ctypes.c_float]
         L.oracle_hemisphere.argtypes = [ctypes.c_uint32, ctypes.c_void_p]
         L.oracle_set_hemisphere.argtypes = [ctypes.c_uint32, ctypes.c_void_p]
+        L.oracle_last_threads.restype = ctypes.c_int
         _oracle = L
     return _oracle
 
@@ -318,6 +319,7 @@ def ref_shader_lib():
         L.refshader_set_math.argtypes = [ctypes.c_void_p] * 3
         L.refshader_render.restype = ctypes.c_longlong
         L.refshader_render.argtypes = [ctypes.c_void_p] * 3
+        L.refshader_last_threads.restype = ctypes.c_int
         assert L.refshader_sizeof_frame() == ctypes.sizeof(RefShaderFrame)
         assert L.refshader_sizeof_state() == REF_SHADER_STATE.itemsize
         _ref_shader = L
@@ -366,4 +368,4 @@ class RefShader:
                                       state.ctypes.data if state is not None else None)
         if n < 0:
             raise RuntimeError("refshader_render failed")
-        return {"rgba32f": rgba, "state": state, "fragments": int(n)}
+        return {"rgba32f": rgba, "state": state, "fragments": int(n), "threads": int(self.lib.refshader_last_threads())}

@@ -612,6 +612,8 @@ PixelOut shadePixel(Pixel& P, u32 px, u32 py) {
 
 }  // namespace
 
+static int g_lastThreads = 1;
+
 extern "C" {
 
 int oracle_render(const OracleWorld* world, const OracleFrame* frame, OracleHit* hits, uint8_t* rgba8, float* rgba32f,
@@ -637,6 +639,7 @@ int oracle_render(const OracleWorld* world, const OracleFrame* frame, OracleHit*
         OracleCounters local;
         memset(&local, 0, sizeof(local));
 #ifdef _OPENMP
+        if (omp_get_thread_num() == 0) g_lastThreads = omp_get_num_threads();  // what the run really got (bench.py reports it)
 #pragma omp for schedule(dynamic, 2)
 #endif
         for (int64_t py = (int64_t)y0; py < (int64_t)y1; py++) {
@@ -776,6 +779,10 @@ float oracle_sinf(float x) { return detSin(x); }
 float oracle_expf(float x) { return detExp(x); }
 
 void oracle_hemisphere(uint32_t n, float* out) { buildHemisphere(n, out); }
+
+/* OpenMP threads the last oracle_render really ran on (OMP_NUM_THREADS, cgroup limits and nested launchers such as
+ * torchrun can give fewer than asked for). */
+int oracle_last_threads(void) { return g_lastThreads; }
 
 void oracle_set_hemisphere(uint32_t n, const float* dirs) { g_hemi.assign(dirs, dirs + 3 * (size_t)n); }
 

@@ -135,6 +135,10 @@ float oracle_expf(float x);
  * double and rounded to fp32; out holds 3*n floats in tangent space (x, y, up). */
 void oracle_hemisphere(uint32_t n, float* out);
 
+/* OpenMP threads the last oracle_render really ran on (OMP_NUM_THREADS or a launcher such as torchrun can give fewer
+ * than asked for); bench.py reports this as cpu_baseline.cores. */
+int oracle_last_threads(void);
+
 /* Lets tests feed the exact table the product uses instead of the libm-computed one. */
 void oracle_set_hemisphere(uint32_t n, const float* dirs);
 

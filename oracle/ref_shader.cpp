@@ -59,6 +59,8 @@ const uint32_t* g_arrays = nullptr;
 
 }  // namespace
 
+static int g_lastThreads = 1;
+
 extern "C" {
 
 // Byte layout shared with oracle/bindings.py (RefShaderFrame).
@@ -123,6 +125,8 @@ long long refshader_render(const RefShaderFrame* f, float* rgba, RefShaderState*
     const uint32_t cs = f->col_stride ? f->col_stride : 1, rs = f->row_stride ? f->row_stride : 1;
     const int threads = f->threads > 0 ? f->threads : omp_get_max_threads();
     long long shaded = 0;
+#pragma omp parallel num_threads(threads)
+    if (omp_get_thread_num() == 0) g_lastThreads = omp_get_num_threads();  // what the run really gets (bench.py reports it)
 #pragma omp parallel for schedule(dynamic, 1) num_threads(threads) reduction(+ : shaded)
     for (uint32_t y = r0; y < r1; y += rs) {
         for (uint32_t x = 0; x < f->width; x += cs) {
@@ -153,6 +157,9 @@ long long refshader_render(const RefShaderFrame* f, float* rgba, RefShaderState*
     }
     return shaded;
 }
+
+/* OpenMP threads the last refshader_render really ran on. */
+int refshader_last_threads(void) { return g_lastThreads; }
 
 uint32_t refshader_sizeof_frame(void) { return (uint32_t)sizeof(RefShaderFrame); }
 uint32_t refshader_sizeof_state(void) { return (uint32_t)sizeof(RefShaderState); }

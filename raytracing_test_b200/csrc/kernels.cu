@@ -122,10 +122,21 @@ struct Cursor {
     uint32_t kind;
     int shift;       // cell shift of the cached node's children
     int lx, ly, lz;  // wrapped coordinates of a voxel inside the cached node
+    // SCHED_PERSISTENT_STAGED: the first ntop nodes (breadth-first prefix = the top tree levels) are also in shared memory.
+    // Everywhere else ntop is the constant 0 and the test below folds away.
+    const uint4* top;
+    uint32_t ntop;
 };
 
-__device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c) {
-    uint4 n = __ldg(&W.nodes[0]);
+__device__ __forceinline__ uint4 load_node(const DeviceWorld& W, const Cursor& c, uint32_t idx) {
+    if (idx < c.ntop) return c.top[idx];
+    return __ldg(&W.nodes[idx]);
+}
+
+__device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c, const uint4* top = nullptr, uint32_t ntop = 0u) {
+    c.top = top;
+    c.ntop = ntop;
+    uint4 n = load_node(W, c, 0u);
     c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
     c.base = n.z;
     c.kind = n.w;
@@ -148,7 +159,7 @@ __device__ __forceinline__ int wrap_coord(const DeviceWorld& W, int v) {
 __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int x, int y, int z, int& cellShift) {
     const int wx = wrap_coord(W, x), wy = wrap_coord(W, y), wz = wrap_coord(W, z);
     if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
-        uint4 n = __ldg(&W.nodes[0]);
+        uint4 n = load_node(W, c, 0u);
         c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
         c.base = n.z;
         c.kind = n.w;
@@ -168,7 +179,7 @@ __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int 
             cellShift = 0;
             return __ldg(&W.voxels[c.base + rank]);
         }
-        const uint4 n = __ldg(&W.nodes[c.base + rank]);
+        const uint4 n = load_node(W, c, c.base + rank);
         if ((n.w & PK_KIND_MASK) == PK_LEAF) {
             cellShift = c.shift;
             return n.z;
@@ -201,7 +212,7 @@ struct Region {
 // Region around wrapped voxel (wx,wy,wz); descends from the deepest cached node that contains it.
 __device__ __forceinline__ void fetch_region(const DeviceWorld& W, Cursor& c, int wx, int wy, int wz, Region& r) {
     if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
-        uint4 n = __ldg(&W.nodes[0]);
+        uint4 n = load_node(W, c, 0u);
         c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
         c.base = n.z;
         c.kind = n.w;
@@ -227,7 +238,7 @@ __device__ __forceinline__ void fetch_region(const DeviceWorld& W, Cursor& c, in
             return;
         }
         const uint32_t rank = (uint32_t)__popcll(c.mask & ((1ull << idx) - 1ull));
-        const uint4 n = __ldg(&W.nodes[c.base + rank]);
+        const uint4 n = load_node(W, c, c.base + rank);
         if ((n.w & PK_KIND_MASK) == PK_LEAF) {
             r.mask = ~0ull;
             r.base = n.z;
@@ -512,7 +523,8 @@ struct PixelResult {
 // One pixel of low_res.frag main() (:256-393).
 // Called by ALL 32 lanes of a warp (valid = the lane has a pixel): the primary loop agrees on its
 // batch length with warp votes.
-__device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint32_t px, uint32_t py, PixelResult& out) {
+__device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint32_t px, uint32_t py, PixelResult& out,
+                                            const uint4* top = nullptr, uint32_t ntop = 0u) {
     const rc_frame_params& P = A.p;
     const DeviceWorld& W = A.world;
     out.color = F3{0.0f, 0.0f, 0.0f};
@@ -564,7 +576,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     init_delta_pos(ray, pos);
 
     Cursor cur;
-    cursor_reset(W, cur);
+    cursor_reset(W, cur, top, ntop);
     CellCount cnt;
     int cellShift;
     int face = 0;
@@ -913,8 +925,11 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     // :373-391 shadow ray
     if (!done && (P.flags & RC_F_SHADOWS)) {
         out.shadowRay = true;
-        Ray sr;
-        build_ray(sr, sun.x, sun.y, sun.z, false);
+        Ray sr;  // buildRay(sunDir): the same for every pixel, its three divisions are done once on the host (FrameArgs::sun_inv)
+        sr.dx = sun.x; sr.dy = sun.y; sr.dz = sun.z;
+        sr.sx = sun.x < 0.0f ? -1 : 1; sr.sy = sun.y < 0.0f ? -1 : 1; sr.sz = sun.z < 0.0f ? -1 : 1;
+        sr.ddx = A.sun_inv[0]; sr.ddy = A.sun_inv[1]; sr.ddz = A.sun_inv[2];
+        sr.adx = fabsf(sr.ddx); sr.ady = fabsf(sr.ddy); sr.adz = fabsf(sr.ddz);
         Pos sp;
         sp.x = pos.x;
         sp.y = pos.y;
@@ -972,94 +987,6 @@ __device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, ui
     A.rgba8[idx] = v;
     if (A.frame_target) A.frame_target[framePixel] = v;
     if (A.rgba32f) A.rgba32f[idx] = make_float4(c.x, c.y, c.z, 0.0f);
-}
-
-// grid.x = ceil(width/16), grid.y = local_rows/8 ; block = 128 threads = 4 warps,
-// each warp an 8x4 pixel tile, the block a 16x8 tile.
-#ifndef RC_PRIMARY_WARPS
-#define RC_PRIMARY_WARPS 4  // warps per CTA: 4 = a 16x8 pixel tile, 2 = 16x4, 1 = 8x4
-#endif
-#ifndef RC_PRIMARY_MIN_BLOCKS
-#define RC_PRIMARY_MIN_BLOCKS (32 / RC_PRIMARY_WARPS)  // 64 registers: 32 warps per SM
-#endif
-constexpr uint32_t PRIMARY_TILE_W = RC_PRIMARY_WARPS >= 2 ? 16u : 8u, PRIMARY_TILE_H = RC_PRIMARY_WARPS >= 4 ? 8u : 4u;
-__global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) primary_kernel(const __grid_constant__ FrameArgs A) {
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t px = blockIdx.x * PRIMARY_TILE_W + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t localRow = blockIdx.y * PRIMARY_TILE_H + (warp >> 1) * 4u + (lane >> 3);
-    // local band -> global row
-    const uint32_t band = (localRow / BAND_ROWS) * A.world_size + A.rank;
-    const uint32_t py = band * BAND_ROWS + (localRow % BAND_ROWS);
-    const bool active = px < A.p.width && py < A.p.height && localRow < A.local_rows;
-
-    PixelResult R;
-    R.traced = false;
-    R.shadowRay = false;
-    R.aoSeed = false;
-    R.hit.kind = RC_KIND_SKY;
-    R.hit.steps = 0;
-#ifdef RC_COST_MAP
-    const long long costT0 = clock64();
-    R.mark[0] = R.mark[1] = R.mark[2] = 0;
-#endif
-    shade_pixel(A, active, px, py, R);
-    if (active) {
-        const uint32_t idx = local_index(A, px, localRow);
-        // AO pixels get their final colour from the AO kernel
-        if (!(R.aoSeed)) store_pixel(A, idx, frame_pixel_of(A, px, localRow), R.color);
-        if (A.hits) A.hits[idx] = R.hit;
-#ifdef RC_COST_MAP
-        // developer probe (tools/cost_map.py): cycles this warp spent in shade_pixel, in the alpha channel of the float frame
-        if (A.rgba32f) {
-            const long long t1 = clock64();
-            const long long m0 = R.mark[0] ? R.mark[0] : t1, m1 = R.mark[1] ? R.mark[1] : m0, m2 = R.mark[2] ? R.mark[2] : t1;
-            // x: to the end of loop A / free flight, y: ratios + replay, z: loop B + shading, w: everything (rest = shadow ray)
-            A.rgba32f[idx] = make_float4((float)(m0 - costT0), (float)(m1 - m0), (float)(m2 - m1), (float)(t1 - costT0));
-        }
-#endif
-    }
-
-    // AO seeds: warp-aggregated append
-    const bool seed = active && R.aoSeed;
-    const unsigned seedMask = __ballot_sync(0xffffffffu, seed);
-    if (seedMask) {
-        unsigned base = 0;
-        const int leader = __ffs(seedMask) - 1;
-        if ((int)lane == leader) base = atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (seed) {
-            AoSeed s;
-            s.ex = R.sx_;
-            s.ey = R.sy_;
-            s.ez = R.sz_;
-            s.x = R.hit.x;
-            s.y = R.hit.y;
-            s.z = R.hit.z;
-            s.r = R.color.x;
-            s.g = R.color.y;
-            s.b = R.color.z;
-            s.pixel = local_index(A, px, localRow);
-            const uint32_t sneg = R.hit.face == 0 ? (R.hit.flags & RC_HF_STEPX_NEG)
-                                                  : (R.hit.face == 1 ? (R.hit.flags & RC_HF_STEPY_NEG) : (R.hit.flags & RC_HF_STEPZ_NEG));
-            // normal sign = -step[face]: negative normal iff the step was positive
-            s.face_sign = (uint32_t)R.hit.face | (sneg ? 0u : 4u);
-            s.frame_pixel = frame_pixel_of(A, px, localRow);
-            A.ao_seeds[base + __popc(seedMask & ((1u << lane) - 1u))] = s;
-        }
-    }
-
-    // frame statistics: one atomic per warp per counter
-    const unsigned tracedMask = __ballot_sync(0xffffffffu, active && R.traced);
-    const unsigned shadowMask = __ballot_sync(0xffffffffu, active && R.shadowRay);
-    const unsigned hitMask = __ballot_sync(0xffffffffu, active && R.hit.kind == RC_KIND_HIT);
-    unsigned stepSum = active ? (unsigned)R.hit.steps : 0u;
-    for (int o = 16; o > 0; o >>= 1) stepSum += __shfl_xor_sync(0xffffffffu, stepSum, o);
-    if (lane == 0) {
-        if (tracedMask) atomicAdd(&A.counters->primary_rays, (unsigned long long)__popc(tracedMask));
-        if (shadowMask) atomicAdd(&A.counters->shadow_rays, (unsigned long long)__popc(shadowMask));
-        if (hitMask) atomicAdd(&A.counters->hit_pixels, (unsigned long long)__popc(hitMask));
-        if (stepSum) atomicAdd(&A.counters->primary_steps, (unsigned long long)stepSum);
-    }
 }
 
 // ---------------------------------------------------------------------------
@@ -1185,27 +1112,41 @@ __global__ void __launch_bounds__(AO_THREADS) ao_cached_kernel(const __grid_cons
 }
 
 // ---------------------------------------------------------------------------
-// AO kernel for ao_steps <= AOW_MAX_STEPS (the reference's 5, light_scattering.frag:231).
+// Window AO: ao_steps == AOW_STEPS (the reference's 5, light_scattering.frag:231).
 //
-// The first step of every AO ray leaves the hit voxel through the hit face (deltaPos[face] was
-// lowered by absDelta[face]); after that its normal coordinate never comes back.  So all rays of
-// a pixel stay inside a box of 2 bricks along the normal and 3 bricks along each tangent axis:
-// 12 x 12 x 8 voxels.  Each thread first copies the occupancy of those 18 bricks out of the tree
-// into a private dense bit window in shared memory ([word][thread] columns), laid out so that a
-// DDA step is ONE integer add (q += +-1 | +-strideY | +-strideZ) and the emptiness test one
-// shared-memory word + shift.  The 64 rays then run without touching the tree.
+// The first step of an AO ray leaves the hit voxel through the hit face (deltaPos[face] was lowered by absDelta[face]);
+// after that its normal coordinate never comes back.  So all rays of a pixel stay inside a box of 2 bricks along the normal
+// and 3 bricks along each tangent axis: 12 x 12 x 8 voxels.  The warp copies the occupancy of those 18 bricks out of the
+// tree into a dense window in shared memory -- ONE window per distinct (hit voxel, face, normal sign) among its 32 pixels,
+// filled cooperatively -- laid out so that a DDA step is one add on the index (q += +-1 | +-strideY | +-strideZ) and the
+// emptiness test one shared-memory byte.  The rays then run without touching the tree.
 //   face x: strides 1, 8, 96   (8 x 12 x 12 voxels)
 //   face y: strides 1, 16, 128 (12 x 8 x 12, rows padded to 16)
 //   face z: strides 1, 16, 192 (12 x 12 x 8, rows padded to 16)
 // A 4-voxel x-row of a brick lands at a multiple of 4 and never straddles a word.
-// Pixels with LIQUID voxels nearby (rays pass through them, low_res.frag:384) and rays whose first
-// step is not the forced one (possible only through accumulated rounding of pos.exact) take the
-// general loop of ao_ray_general instead.
+//
+// Where a pixel's rays start.  The primary ray leaves pos.exact exactly on the hit face along the face axis (stepping an
+// axis snaps that coordinate to an integer, and the shader un-biases only the other two: low_res.frag:343-345), so
+// (exact - round)[face] = 0 for a positive AO step and -1 for a negative one, in exact arithmetic:
+//   normal -  (primary step +): deltaPos[face] = absDelta - (-1)(-absDelta) - absDelta = -absDelta: the first step is through
+//             the face whatever the tangents do; it leaves deltaPos[face] = 0, and with both tangent deltaPos > 0 the
+//             SECOND step is along the normal too (0 wins every comparison of low_res.frag:450-488 for its own axis and
+//             loses none), leaving deltaPos[face] = absDelta.  Rays start 2 voxels out with 3 free steps.
+//   normal +  (primary step -): deltaPos[face] = absDelta - 0 - absDelta = 0: the first step is through the face when both
+//             tangent deltaPos > 0, leaving deltaPos[face] = absDelta.  Rays start 1 voxel out with 4 free steps.
+// Tangent deltaPos = absDelta - (exact - round) * delta > 0 strictly when (exact - round) lies in [2^-20, 1 - 2^-20] (for
+// the step sign used): the rounded product stays below absDelta (1 - 2^-21).  A pixel that meets all of this and has no
+// LIQUID in its window (rays pass through liquid, low_res.frag:384, a bit cannot say that) is FAST: every sample starts
+// from the same voxel with the same deltaPos[face] = absDelta -- obtained from the common formula with (exact - round)[face]
+// set to 0 -- and the occupancy of the one or two voxels already crossed is read once per pixel.  Everything else (a
+// pixel exactly on a voxel edge, pos.exact drifted by a mirror bounce, liquid nearby) is cast on the tree itself, the
+// pixel's samples dealt to the 32 lanes of the warp (ao_ray_general).
 // ---------------------------------------------------------------------------
-constexpr uint32_t AOW_MAX_STEPS = 5;
+constexpr uint32_t AOW_STEPS = 5;
 constexpr int AOW_WORDS = 48;
 constexpr uint32_t AOW_BYTE_SLOTS = 4;    // windows per warp in byte mode ...
-constexpr uint32_t AOW_BYTE_WORDS = 384;  // ... of 16 x 12 x 8 bytes: 4 * 384 = 32 * 48 words, the warp's share of sWin
+constexpr uint32_t AOW_BYTE_WORDS = 384;  // ... of 16 x 12 x 8 bytes: 4 * 384 = 32 * 48 words, the warp's share of window memory
+constexpr uint32_t AOW_WARP_WORDS = 32u * AOW_WORDS;  // a warp's share of window memory
 
 // One table entry per (orientation = face*2 + negative normal, sample): what buildRay derives
 // from the direction, precomputed on the host with the same IEEE operations.
@@ -1244,112 +1185,130 @@ __device__ __noinline__ uint32_t ao_ray_general(const DeviceWorld& W, int hx, in
     return state != 0u ? 1u : 0u;
 }
 
-// The rays of one pixel through its window.  BYTES: one byte per voxel (the window index is the shared-memory byte
-// address itself), else one bit per voxel, MSB-first inside each byte (index = 8 * address + bit number).
-struct AowRayArgs {
-    int x, y, z;                           // hit voxel
-    float q0f, q1f;                        // window index of the hit voxel / after the forced first step, as fp32 denormals
-    float a0x, a1x, a0y, a1y, a0z, a1z;    // (pos.exact - pos.round) for a positive / negative step sign
-    uint32_t nSteps;
-    bool liquid, f2;
-    uint32_t acc1;                         // FORCED: occupancy of the voxel behind the hit face, in the form the ray loop gathers
-};
+// Occupancy of window voxel q.  BYTES: one byte per voxel, q is the shared-memory byte address itself, result 0 / 1.  Else one
+// bit per voxel, MSB-first inside each byte, q = 8 * address + bit number: the byte, replicated to the four byte lanes by one
+// multiply, is shifted left by q & 31 = 8 k + (q & 7), which leaves bit 7 - (q & 7) in the sign.
+template <bool BYTES>
+__device__ __forceinline__ uint32_t aow_occ(uint32_t q) {
+    uint32_t byte;
+    if (BYTES) {
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q) : "memory");
+        return byte;
+    }
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
+    return (byte * 0x01010101u) << (q & 31u);
+}
 
-// FORCED: the kernel has proved for every pixel of the warp that the first step of each of its rays is the forced one
-// through the hit face (and no window holds LIQUID): that step is then three additions -- deltaPos[face] gets back the
-// absDelta[face] it was lowered by, the same rounded sum the loop would do -- the ray starts at the voxel behind the face,
-// whose occupancy was read once for the pixel, and nothing has to be looked at before using the window.
-template <uint32_t NSTEPS, bool BYTES, bool FORCED>
-__device__ __forceinline__ uint32_t aow_cast_rays(const DeviceWorld& W, const AoDir* __restrict__ dirs, const AowRayArgs& a) {
-    const uint32_t nSteps = a.nSteps;
+// The rays of one FAST pixel (see above): from window index qSf (an fp32 DENORMAL whose bit pattern is the index:
+// denormals add like integers, so a step is a predicated FADD on the FMA pipe instead of select + integer add on the
+// half-rate ALU pipe), acc0 = occupancy of the voxels already crossed, three free steps -- four when FOUR (some pixel of the
+// warp has a positive normal) and this lane's pixel is one of those (`fourth`; the others stand still in that step).
+// No early exit on a hit: the warp runs until its last ray is done anyway, a ray that has hit stays inside the window, and
+// without the branch the load of one step overlaps the compares of the next.
+// move = false: the lane has no fast pixel; it walks along without going anywhere (strides 0).
+// skip: bit g set = no voxel that a ray of sample group g can still enter is occupied, for any pixel of the warp
+// (AO_OPT_OCTANT): those rays are not cast; they are occluded iff one of the voxels already crossed was.
+template <bool BYTES, bool FOUR>
+__device__ __forceinline__ uint32_t aow_cast_rays(const AoDir* __restrict__ dirs, float qSf, uint32_t acc0, float a0x, float a1x,
+                                                  float a0y, float a1y, float a0z, float a1z, bool move, bool fourth, uint32_t skip) {
     uint32_t occluded = 0;
     for (uint32_t g = 0; g < 4u; g++) {
         const uint32_t kBegin = c_aoSeg[g], kEnd = c_aoSeg[g + 1u];
         if (kBegin == kEnd) continue;
-        // every sample of the group steps the same way along each axis: (exact - round) is chosen once, from the first one
+        if ((skip >> g) & 1u) {
+            occluded += (BYTES ? acc0 : acc0 >> 31) * (kEnd - kBegin);
+            continue;
+        }
+        // every sample of the group steps the same way along each axis: the strides and (exact - round) are the group's
         const AoDir first = dirs[kBegin];
-        const float ax = first.qx < 0 ? a.a1x : a.a0x, ay = first.qy < 0 ? a.a1y : a.a0y, az = first.qz < 0 ? a.a1z : a.a0z;
+        const float qx = move ? first.qx : 0.0f, qy = move ? first.qy : 0.0f, qz = move ? first.qz : 0.0f;
+        const float q4x = fourth ? qx : 0.0f, q4y = fourth ? qy : 0.0f, q4z = fourth ? qz : 0.0f;
+        const float ax = first.qx < 0 ? a1x : a0x, ay = first.qy < 0 ? a1y : a0y, az = first.qz < 0 ? a1z : a0z;
         for (uint32_t k = kBegin; k < kEnd; k++) {
             const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
-            const float4 v1 = __ldg(reinterpret_cast<const float4*>(dirs + k) + 1);
             const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
-            const float qx = v0.w, qy = v1.x, qz = v1.y;  // never 0: the sign says which way the ray steps
             const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
-            // deltaPos = absDelta - (exact - round) * delta ; deltaPos[face] -= absDelta[face].  The table holds
-            // absDelta[face] for the x and y faces and 0 otherwise (v - 0 = v exactly), so no branch on the face here
-            float px = FSUB(FSUB(adx, FMUL(ax, ix)), v1.z);
-            float py = FSUB(FSUB(ady, FMUL(ay, iy)), v1.w);
+            // deltaPos = absDelta - (exact - round) * delta (low_res.frag:379); (exact - round)[face] comes in as 0
+            float px = FSUB(adx, FMUL(ax, ix));
+            float py = FSUB(ady, FMUL(ay, iy));
             float pz = FSUB(adz, FMUL(az, iz));
-            if (a.f2) pz = FSUB(pz, adz);
-
-            // The window index lives in a float DENORMAL (bit pattern = index, exact): a step is a predicated FADD on the
-            // FMA pipe instead of select + integer add on the half-rate ALU pipe, and the address (and bit number) are
-            // read straight from the bit pattern.  No early exit on a hit: the warp runs until its last ray is done anyway,
-            // a ray that has hit stays inside the window (it covers every position ao_steps steps can reach), and without
-            // the branch the load of one step overlaps the compares of the next.
-            float qf = FORCED ? a.q1f : a.q0f;
-            uint32_t acc = FORCED ? a.acc1 : 0u;
-            bool window = FORCED ? true : !a.liquid;
-            if (FORCED) {  // v1.z / v1.w: absDelta[face] for an x / y face, else 0 (v + 0 = v)
-                px = FADD(px, v1.z);
-                py = FADD(py, v1.w);
-                if (a.f2) pz = FADD(pz, adz);
-            }
+            float qf = qSf;
+            uint32_t acc = acc0;
 #pragma unroll
-            for (uint32_t i = FORCED ? 1u : 0u; i < (NSTEPS ? NSTEPS : AOW_MAX_STEPS); i++) {
-                if (NSTEPS == 0 && i >= nSteps) break;
+            for (uint32_t i = 0; i < 3u; i++) {
                 const bool bx = px < py && px < pz;
                 const bool by = !bx && py < pz;
                 const bool bz = !bx && !by;
-                if (i == 0) {
-                    if (!window) break;
-                    // the first step must be the forced one through the hit face, else the window does not cover the ray
-                    // (possible only through accumulated rounding of pos.exact): look where the index would go
-                    const float qn = qf + (bx ? qx : (by ? qy : qz));
-                    window = qn == a.q1f;  // compared as numbers = as bit patterns: both are positive denormals
-                    if (!window) break;
-                }
                 if (bx) { qf += qx; px = FADD(px, adx); }
                 if (by) { qf += qy; py = FADD(py, ady); }
                 if (bz) { qf += qz; pz = FADD(pz, adz); }
-                const uint32_t q = __float_as_uint(qf);
-                uint32_t byte;
-                if (BYTES) {
-                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q) : "memory");
-                    acc |= byte;  // 0 or 1
-                } else {
-                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q >> 3) : "memory");
-                    // the byte in all four lanes of a word: a shift by q & 31 = 8 * k + (q & 7) leaves bit 7 - (q & 7) in the sign
-                    acc |= (byte * 0x01010101u) << (q & 31u);
-                }
+                acc |= aow_occ<BYTES>(__float_as_uint(qf));
             }
-            if (window)
-                occluded += BYTES ? acc : acc >> 31;
-            else  // nothing has moved yet: (px, py, pz) is the state before the first step
-                occluded += ao_ray_general(W, a.x, a.y, a.z, px, py, pz, adx, ady, adz, qx < 0 ? -1 : 1, qy < 0 ? -1 : 1,
-                                           qz < 0 ? -1 : 1, nSteps);
+            if (FOUR) {
+                const bool bx = px < py && px < pz;
+                const bool by = !bx && py < pz;
+                const bool bz = !bx && !by;
+                if (bx) qf += q4x;
+                if (by) qf += q4y;
+                if (bz) qf += q4z;
+                acc |= aow_occ<BYTES>(__float_as_uint(qf));
+            }
+            occluded += BYTES ? acc : acc >> 31;
         }
     }
     return occluded;
 }
 
-// NSTEPS: ao_steps known at compile time (the loop unrolls), 0 = read it from the frame parameters.
-template <uint32_t NSTEPS>
-__global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_constant__ FrameArgs A, const AoDir* __restrict__ table) {
-    // one window per DISTINCT (hit voxel, face, normal sign) of the warp, 48 words each.  Neighbouring pixels mostly see
-    // the same voxel face (1.14 distinct windows per 8x4 pixel tile of the benchmark frame), and the window depends on
-    // nothing else, so the warp builds each one ONCE, cooperatively (one lane per 4^3 brick), instead of 32 times.
-    __shared__ uint32_t sWin[AO_THREADS / 32][32][AOW_WORDS];
-    __shared__ uint32_t sLiquid[AO_THREADS / 32];
+// The voxels a ray can still enter with n free steps, relative to where it stands: i + j + k in 1..n steps along the two
+// tangents (in the sample group's directions) and the normal.  Sorted by i + j + k: the first 19 entries are n = 3, all 34
+// are n = 4.  Three bits per entry, 21 entries per 64-bit word.
+struct OctantTable {
+    unsigned long long i[2], j[2], k[2];
+};
+__host__ __device__ constexpr OctantTable make_octant_table() {
+    OctantTable t{{0ull, 0ull}, {0ull, 0ull}, {0ull, 0ull}};
+    int n = 0;
+    for (int sum = 1; sum <= 4; sum++)
+        for (int i = 0; i <= sum; i++)
+            for (int j = 0; i + j <= sum; j++) {
+                const int k = sum - i - j;
+                t.i[n / 21] |= (unsigned long long)i << (3 * (n % 21));
+                t.j[n / 21] |= (unsigned long long)j << (3 * (n % 21));
+                t.k[n / 21] |= (unsigned long long)k << (3 * (n % 21));
+                n++;
+            }
+    return t;
+}
+constexpr uint32_t OCTANT_VOXELS_3 = 19, OCTANT_VOXELS_4 = 34;
 
-    const uint32_t nSeeds = A.counters->ao_seed_count;
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if ((t & ~31u) >= nSeeds) return;  // whole warp beyond the list
-    const bool valid = t < nSeeds;
+__device__ __forceinline__ AoSeed shuffle_seed(const AoSeed& s, int src) {
+    AoSeed o;
+    o.ex = __shfl_sync(0xffffffffu, s.ex, src);
+    o.ey = __shfl_sync(0xffffffffu, s.ey, src);
+    o.ez = __shfl_sync(0xffffffffu, s.ez, src);
+    o.x = __shfl_sync(0xffffffffu, s.x, src);
+    o.y = __shfl_sync(0xffffffffu, s.y, src);
+    o.z = __shfl_sync(0xffffffffu, s.z, src);
+    o.r = __shfl_sync(0xffffffffu, s.r, src);
+    o.g = __shfl_sync(0xffffffffu, s.g, src);
+    o.b = __shfl_sync(0xffffffffu, s.b, src);
+    o.pixel = __shfl_sync(0xffffffffu, s.pixel, src);
+    o.face_sign = __shfl_sync(0xffffffffu, s.face_sign, src);
+    o.frame_pixel = __shfl_sync(0xffffffffu, s.frame_pixel, src);
+    return o;
+}
+
+// AO of up to 32 hit pixels by one warp.  Called by all 32 lanes; every lane holds a seed -- lanes without a pixel of their
+// own (valid = false) a copy of some valid lane's, so that they walk along without adding windows or stores.
+// warpWin: AOW_WARP_WORDS words of shared memory owned by this warp, liquidWord: one more.
+__device__ __forceinline__ void aow_warp(const FrameArgs& A, const AoSeed& s, bool valid, uint32_t* warpWin, uint32_t* liquidWord) {
+    // one window per DISTINCT (hit voxel, face, normal sign) of the warp.  Neighbouring pixels mostly see the same voxel
+    // face (1.14 distinct windows per 8x4 pixel tile of the benchmark frame), and the window depends on nothing else, so
+    // the warp builds each one ONCE, cooperatively (one lane per 4^3 brick), instead of 32 times.
+    const uint32_t lane = threadIdx.x & 31u;
     const rc_frame_params& P = A.p;
     const DeviceWorld& W = A.world;
-    const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];  // idle lanes of the last warp shadow a real seed
+    const AoDir* table = reinterpret_cast<const AoDir*>(A.ao_table);
     const int face = (int)(s.face_sign & 3u);
     const bool negNormal = (s.face_sign & 4u) != 0u;
     const bool f0 = face == 0, f1 = face == 1, f2 = face >= 2;
@@ -1375,9 +1334,9 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
     // warp's share exactly; a DDA step then needs no shift / mask to reach its voxel.  More: one bit per voxel.
     const bool byteMode = nSlots <= AOW_BYTE_SLOTS;
     const uint32_t slotWords = byteMode ? AOW_BYTE_WORDS : (uint32_t)AOW_WORDS;
-    uint32_t* const warpWin = &sWin[warp][0][0];
+    __syncwarp();  // the warp's previous chunk / tile is done with the windows
     for (uint32_t i = lane; i < nSlots * slotWords; i += 32u) warpWin[i] = 0u;
-    if (lane == 0u) sLiquid[warp] = 0u;
+    if (lane == 0u) *liquidWord = 0u;
     __syncwarp();
 
     // fill: task = (window, brick); 18 bricks per window (2 along the normal, 3 x 3 across)
@@ -1401,9 +1360,14 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
                 Region r;
                 fetch_region(W, cur, wrap_coord(W, (lb0x + bx) << 2), wrap_coord(W, (lb0y + by) << 2), wrap_coord(W, (lb0z + bz) << 2), r);
                 if (r.mask != 0ull) {
-                    if (r.info & BR_LIQUID) atomicOr(&sLiquid[warp], 1u << sl);
+                    if (r.info & BR_LIQUID) atomicOr(liquidWord, 1u << sl);
                     uint32_t* win = warpWin + sl * slotWords;
                     const int pBrick = (bx << 2) + sY * (by << 2) + sZ * (bz << 2);
+#ifdef RC_CHECKED
+                    // bounds of the window fill (compute-sanitizer is closed on the pool: -DRC_CHECKED builds trap instead)
+                    if (pBrick < 0 || pBrick + 3 + sY * 3 + sZ * 3 >= 32 * AOW_WORDS || (sl + 1u) * slotWords > AOW_WARP_WORDS)
+                        __trap();  // a window is 32 * AOW_WORDS voxels (bits, or bytes in byte mode)
+#endif
 #pragma unroll
                     for (int z2 = 0; z2 < 4; z2++) {
                         const uint32_t slice = (uint32_t)(r.mask >> (16 * z2)) & 0xFFFFu;
@@ -1428,57 +1392,332 @@ __global__ void __launch_bounds__(AO_THREADS) ao_window_kernel(const __grid_cons
         }
     }
     __syncwarp();
-    if (!valid) return;
-    const bool liquid = ((sLiquid[warp] >> slot) & 1u) != 0u;
+    const bool liquid = ((*liquidWord >> slot) & 1u) != 0u;
 
     const float fx = (float)s.x, fy = (float)s.y, fz = (float)s.z;
     // (pos.exact - pos.round) for a positive and for a negative step sign (exact is biased by -1)
-    const float a0x = FSUB(s.ex, fx), a1x = FSUB(FSUB(s.ex, 1.0f), fx);
-    const float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
-    const float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
+    float a0x = FSUB(s.ex, fx), a1x = FSUB(FSUB(s.ex, 1.0f), fx);
+    float a0y = FSUB(s.ey, fy), a1y = FSUB(FSUB(s.ey, 1.0f), fy);
+    float a0z = FSUB(s.ez, fz), a1z = FSUB(FSUB(s.ez, 1.0f), fz);
+    const int strideN = f0 ? 1 : (f1 ? strideY : strideZ);
     const int q0 = (s.x - (b0x << 2)) + strideY * (s.y - (b0y << 2)) + strideZ * (s.z - (b0z << 2));
-    // index of the hit voxel, counted from shared address 0: (8 *) address of this lane's window + q0, carried as the
-    // fp32 denormal with that bit pattern (< 2^23)
+    // index of the voxel the rays start from, counted from shared address 0: (8 *) address of this lane's window + its
+    // index in the window: 1 voxel out from the hit voxel for a positive normal, 2 for a negative one
     const uint32_t winAddr = (uint32_t)__cvta_generic_to_shared(warpWin + slot * slotWords);
-    const float q0f = __uint_as_float((byteMode ? winAddr : 8u * winAddr) + (uint32_t)q0);
-    const uint32_t nSteps = NSTEPS ? NSTEPS : P.ao_steps;
-    const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
+    const uint32_t q1 = (byteMode ? winAddr : 8u * winAddr) + (uint32_t)(q0 + (negNormal ? -strideN : strideN));
+    const uint32_t qS = negNormal ? q1 - (uint32_t)strideN : q1;
+#ifdef RC_CHECKED
+    {
+        // every window index a ray of this pixel can reach (5 steps from the hit voxel, the first through the face) lies
+        // inside the lane's window
+        const int tang = 4 * (f0 ? strideY + strideZ : (f1 ? 1 + strideZ : 1 + strideY));
+        const int lo = q0 + (negNormal ? -5 * strideN : strideN) - tang, hi = q0 + (negNormal ? -strideN : 5 * strideN) + tang;
+        if (lo < 0 || hi >= 32 * AOW_WORDS) __trap();
+    }
+#endif
 
-    // the index after the forced first step (through the hit face): q0 + sign(normal) * stride(face)
-    const float q1f = q0f + __uint_as_float((negNormal ? 0x80000000u : 0u) | (uint32_t)(f0 ? 1 : (f1 ? strideY : strideZ)));
-
-    // With pos.exact exactly on the hit face (its face coordinate = the voxel's, + 1 for a positive normal) and inside the
-    // voxel along both tangents, every sample's first step IS the forced one: deltaPos[face] = (absDelta - 1 * absDelta) -
-    // absDelta = -absDelta < 0 exactly, and a tangent deltaPos = absDelta - (0..1) * absDelta >= 0 (one rounded product,
-    // never above absDelta).  If that holds for the whole warp (and no window holds LIQUID) the rays skip that step's
-    // compares and the look-before-you-leap; pixels that fail it (rounding of pos.exact along the primary ray) keep the
-    // general loop for their warp.
+    // FAST pixel (see the top of this section): pos.exact on the hit face, strictly inside the voxel along both tangents
+    // for either step sign, no LIQUID in the window
     const float aF = f0 ? a0x : (f1 ? a0y : a0z);
-    const bool forcedPixel = !liquid && aF == (negNormal ? 0.0f : 1.0f) && a0x >= 0.0f && a0x <= 1.0f && a0y >= 0.0f &&
-                             a0y <= 1.0f && a0z >= 0.0f && a0z <= 1.0f;
-    const bool forced = NSTEPS == AOW_MAX_STEPS && __all_sync(__activemask(), forcedPixel);
-    uint32_t acc1 = 0u;
-    if (forced) {
-        const uint32_t q1 = __float_as_uint(q1f);
-        uint32_t byte;
-        if (byteMode) {
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q1) : "memory");
-            acc1 = byte;
+    const float tlo = 9.5367431640625e-07f, thi = 1.0f - 9.5367431640625e-07f;  // 2^-20, 1 - 2^-20
+    const float ta0 = f0 ? a0y : a0x, ta1 = f0 ? a1y : a1x, tb0 = f2 ? a0y : a0z, tb1 = f2 ? a1y : a1z;  // the two tangent axes
+    const bool fast = !liquid && aF == 0.0f && ta0 >= tlo && ta0 <= thi && tb0 >= tlo && tb0 <= thi && -ta1 >= tlo && -ta1 <= thi &&
+                      -tb1 >= tlo && -tb1 <= thi;
+    uint32_t occluded = 0u;
+    if (__any_sync(0xffffffffu, fast)) {
+        const bool four = __any_sync(0xffffffffu, fast && !negNormal);
+        uint32_t acc0 = byteMode ? aow_occ<true>(q1) : aow_occ<false>(q1);
+        if (negNormal) acc0 |= byteMode ? aow_occ<true>(qS) : aow_occ<false>(qS);
+        // AO_OPT_OCTANT: which sample groups (signs of the two tangent components) can still meet an occupied voxel at
+        // all?  The free steps from qS each go along one axis in the group's direction: 19 (3 steps) or 34 (4 steps)
+        // voxels per group.  Tested once per distinct window, the lanes sharing the 4 x 19 / 34 voxels; a group is skipped
+        // when it is empty for every window of the warp (the loop over groups stays warp-uniform).
+        uint32_t skip = 0u;
+        if ((A.ao_opts & AO_OPT_OCTANT) != 0u && byteMode) {
+            constexpr OctantTable OT = make_octant_table();
+            uint32_t myOcc = 0u;
+            for (uint32_t sl = 0; sl < nSlots; sl++) {
+                const int src = (int)__fns(leaders, 0u, (int)sl + 1);
+                const uint32_t lqS = __shfl_sync(0xffffffffu, qS, src);  // shared byte address of that window's start voxel
+                const uint32_t lfs = __shfl_sync(0xffffffffu, s.face_sign, src);
+                const int lface = (int)(lfs & 3u);
+                const int st1 = aow_stride_y(lface), st2 = aow_stride_z(lface);
+                const int sN = (lfs & 4u) ? -sel3i(lface, 1, st1, st2) : sel3i(lface, 1, st1, st2);
+                const int sU = sel3i(lface, st1, st2, 1), sV = sel3i(lface, st2, 1, st1);  // axes (face + 1) % 3, (face + 2) % 3
+                const uint32_t nVox = (lfs & 4u) ? OCTANT_VOXELS_3 : OCTANT_VOXELS_4;
+                uint32_t h = 0u;
+                for (uint32_t t = lane; t < 4u * nVox; t += 32u) {
+                    const uint32_t g = t / nVox, o = t - g * nVox;
+                    const uint32_t wd = o >= 21u ? 1u : 0u, sh = 3u * (o - 21u * wd);
+                    const int vi = (int)(((wd ? OT.i[1] : OT.i[0]) >> sh) & 7ull), vj = (int)(((wd ? OT.j[1] : OT.j[0]) >> sh) & 7ull),
+                              vk = (int)(((wd ? OT.k[1] : OT.k[0]) >> sh) & 7ull);
+                    const int off = vi * ((g & 1u) ? -sU : sU) + vj * ((g & 2u) ? -sV : sV) + vk * sN;
+                    h |= aow_occ<true>(lqS + (uint32_t)off) << g;
+                }
+                h = __reduce_or_sync(0xffffffffu, h);
+                if (slot == sl) myOcc = h;
+            }
+            // lanes whose pixel is not fast do not cast window rays: they have no say
+            skip = __reduce_and_sync(0xffffffffu, fast ? (~myOcc & 15u) : 15u);
+        }
+        // (exact - round) of the face axis: absDelta - 0 * delta = absDelta
+        if (f0) a0x = a1x = 0.0f;
+        else if (f1) a0y = a1y = 0.0f;
+        else a0z = a1z = 0.0f;
+        const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
+        const float qSf = __uint_as_float(qS);
+        const bool fourth = !negNormal;
+        if (byteMode)
+            occluded = four ? aow_cast_rays<true, true>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
+                            : aow_cast_rays<true, false>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
+        else
+            occluded = four ? aow_cast_rays<false, true>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
+                            : aow_cast_rays<false, false>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
+    }
+    // The other pixels, one at a time: their samples dealt to the lanes, each ray on the tree itself (castAo as it stands)
+    unsigned slow = __ballot_sync(0xffffffffu, valid && !fast);
+    while (slow) {
+        const int src = __ffs(slow) - 1;
+        slow &= slow - 1u;
+        const int hx = __shfl_sync(0xffffffffu, s.x, src), hy = __shfl_sync(0xffffffffu, s.y, src), hz = __shfl_sync(0xffffffffu, s.z, src);
+        const float hex = __shfl_sync(0xffffffffu, s.ex, src), hey = __shfl_sync(0xffffffffu, s.ey, src),
+                    hez = __shfl_sync(0xffffffffu, s.ez, src);
+        const uint32_t hfs = __shfl_sync(0xffffffffu, s.face_sign, src);
+        const int hface = (int)(hfs & 3u);
+        const AoDir* hd = table + (size_t)(hface * 2 + ((hfs & 4u) ? 1 : 0)) * RC_MAX_AO_SAMPLES;
+        const float hfx = (float)hx, hfy = (float)hy, hfz = (float)hz;
+        uint32_t cnt = 0u;
+        for (uint32_t k = lane; k < P.ao_samples; k += 32u) {
+            const float4 v0 = __ldg(reinterpret_cast<const float4*>(hd + k));
+            const float4 v1 = __ldg(reinterpret_cast<const float4*>(hd + k) + 1);
+            const float ix = v0.x, iy = v0.y, iz = v0.z;
+            const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
+            const bool nx = v0.w < 0, ny = v1.x < 0, nz = v1.y < 0;  // the strides' signs are the ray's step signs
+            // pos.exact re-biased for the ray's signs; deltaPos = absDelta - (exact - round) * delta; deltaPos[face] -= absDelta[face]
+            const float ex = nx ? FSUB(hex, 1.0f) : hex, ey = ny ? FSUB(hey, 1.0f) : hey, ez = nz ? FSUB(hez, 1.0f) : hez;
+            float px = FSUB(adx, FMUL(FSUB(ex, hfx), ix));
+            float py = FSUB(ady, FMUL(FSUB(ey, hfy), iy));
+            float pz = FSUB(adz, FMUL(FSUB(ez, hfz), iz));
+            if (hface == 0) px = FSUB(px, adx);
+            else if (hface == 1) py = FSUB(py, ady);
+            else pz = FSUB(pz, adz);
+            cnt += ao_ray_general(W, hx, hy, hz, px, py, pz, adx, ady, adz, nx ? -1 : 1, ny ? -1 : 1, nz ? -1 : 1, AOW_STEPS);
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if ((int)lane == src) occluded = cnt;
+    }
+    if (valid) {
+        const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
+        store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
+        if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
+    }
+}
+
+
+// ---------------------------------------------------------------------------
+// One 8x4-pixel tile by one warp: the pixel of low_res.frag main() for each lane, the stores, and the AO of the tile's hit
+// pixels -- cast by this same warp right away (FUSED: the seeds never leave the registers, there is no seed list and no
+// second launch) or appended to the seed list for an AO kernel.
+// ---------------------------------------------------------------------------
+template <bool FUSED>
+__device__ __forceinline__ void trace_tile(const FrameArgs& A, uint32_t px, uint32_t localRow, uint32_t lane, uint32_t* warpWin,
+                                           uint32_t* liquidWord, const uint4* top, uint32_t ntop) {
+    // local band -> global row
+    const uint32_t band = (localRow / BAND_ROWS) * A.world_size + A.rank;
+    const uint32_t py = band * BAND_ROWS + (localRow % BAND_ROWS);
+    const bool active = px < A.p.width && py < A.p.height && localRow < A.local_rows;
+
+    PixelResult R;
+    R.traced = false;
+    R.shadowRay = false;
+    R.aoSeed = false;
+    R.hit.kind = RC_KIND_SKY;
+    R.hit.steps = 0;
+#ifdef RC_COST_MAP
+    const long long costT0 = clock64();
+    R.mark[0] = R.mark[1] = R.mark[2] = 0;
+#endif
+    shade_pixel(A, active, px, py, R, top, ntop);
+    if (active) {
+        const uint32_t idx = local_index(A, px, localRow);
+        // AO pixels get their final colour from the AO rays
+        if (!(R.aoSeed)) store_pixel(A, idx, frame_pixel_of(A, px, localRow), R.color);
+        if (A.hits) A.hits[idx] = R.hit;
+#ifdef RC_COST_MAP
+        // developer probe (tools/cost_map.py): cycles this warp spent in shade_pixel, in the alpha channel of the float frame
+        if (A.rgba32f) {
+            const long long t1 = clock64();
+            const long long m0 = R.mark[0] ? R.mark[0] : t1, m1 = R.mark[1] ? R.mark[1] : m0, m2 = R.mark[2] ? R.mark[2] : t1;
+            // x: to the end of loop A / free flight, y: ratios + replay, z: loop B + shading, w: everything (rest = shadow ray)
+            A.rgba32f[idx] = make_float4((float)(m0 - costT0), (float)(m1 - m0), (float)(m2 - m1), (float)(t1 - costT0));
+        }
+#endif
+    }
+
+    // AO seeds
+    const bool seed = active && R.aoSeed;
+    const unsigned seedMask = __ballot_sync(0xffffffffu, seed);
+    if (seedMask) {
+        const int leader = __ffs(seedMask) - 1;
+        AoSeed s;
+        s.ex = R.sx_;
+        s.ey = R.sy_;
+        s.ez = R.sz_;
+        s.x = R.hit.x;
+        s.y = R.hit.y;
+        s.z = R.hit.z;
+        s.r = R.color.x;
+        s.g = R.color.y;
+        s.b = R.color.z;
+        s.pixel = local_index(A, px, localRow);
+        const uint32_t sneg = R.hit.face == 0 ? (R.hit.flags & RC_HF_STEPX_NEG)
+                                              : (R.hit.face == 1 ? (R.hit.flags & RC_HF_STEPY_NEG) : (R.hit.flags & RC_HF_STEPZ_NEG));
+        // normal sign = -step[face]: negative normal iff the step was positive
+        s.face_sign = (uint32_t)R.hit.face | (sneg ? 0u : 4u);
+        s.frame_pixel = frame_pixel_of(A, px, localRow);
+        if (FUSED) {
+            if ((int)lane == leader) atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
+            // lanes without a hit pixel walk along with the first seeded lane's
+            const AoSeed sh = shuffle_seed(s, leader);
+            if (!seed) s = sh;
+            aow_warp(A, s, seed, warpWin, liquidWord);
         } else {
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(byte) : "r"(q1 >> 3) : "memory");
-            acc1 = (byte * 0x01010101u) << (q1 & 31u);
+            // warp-aggregated append
+            unsigned base = 0;
+            if ((int)lane == leader) base = atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (seed) {
+                const uint32_t at = base + __popc(seedMask & ((1u << lane) - 1u));
+#ifdef RC_CHECKED
+                if (at >= A.local_rows * A.p.width) __trap();  // seed cursor beyond the list
+#endif
+                A.ao_seeds[at] = s;
+            }
         }
     }
-    const AowRayArgs ra{s.x, s.y, s.z, q0f, q1f, a0x, a1x, a0y, a1y, a0z, a1z, nSteps, liquid, f2, acc1};
-    uint32_t occluded;
-    if (forced)
-        occluded = byteMode ? aow_cast_rays<NSTEPS, true, true>(W, dirs, ra) : aow_cast_rays<NSTEPS, false, true>(W, dirs, ra);
-    else
-        occluded = byteMode ? aow_cast_rays<NSTEPS, true, false>(W, dirs, ra) : aow_cast_rays<NSTEPS, false, false>(W, dirs, ra);
-    const float ao = FSUB(1.0f, FMUL(P.ao_strength, FDIV((float)occluded, (float)P.ao_samples)));
-    store_pixel(A, s.pixel, s.frame_pixel, F3{FMUL(s.r, ao), FMUL(s.g, ao), FMUL(s.b, ao)});
-    if (A.hits) A.hits[s.pixel].ao_occluded = (uint8_t)occluded;
+
+    // frame statistics: one atomic per warp per counter
+    const unsigned tracedMask = __ballot_sync(0xffffffffu, active && R.traced);
+    const unsigned shadowMask = __ballot_sync(0xffffffffu, active && R.shadowRay);
+    const unsigned hitMask = __ballot_sync(0xffffffffu, active && R.hit.kind == RC_KIND_HIT);
+    unsigned stepSum = active ? (unsigned)R.hit.steps : 0u;
+    for (int o = 16; o > 0; o >>= 1) stepSum += __shfl_xor_sync(0xffffffffu, stepSum, o);
+    if (lane == 0) {
+        if (tracedMask) atomicAdd(&A.counters->primary_rays, (unsigned long long)__popc(tracedMask));
+        if (shadowMask) atomicAdd(&A.counters->shadow_rays, (unsigned long long)__popc(shadowMask));
+        if (hitMask) atomicAdd(&A.counters->hit_pixels, (unsigned long long)__popc(hitMask));
+        if (stepSum) atomicAdd(&A.counters->primary_steps, (unsigned long long)stepSum);
+    }
 }
+
+// grid.x = ceil(width/16), grid.y = local_rows/8 ; block = 128 threads = 4 warps,
+// each warp an 8x4 pixel tile, the block a 16x8 tile.
+#ifndef RC_PRIMARY_WARPS
+#define RC_PRIMARY_WARPS 4  // warps per CTA: 4 = a 16x8 pixel tile, 2 = 16x4, 1 = 8x4
+#endif
+#ifndef RC_PRIMARY_MIN_BLOCKS
+#define RC_PRIMARY_MIN_BLOCKS (32 / RC_PRIMARY_WARPS)  // 64 registers: 32 warps per SM
+#endif
+constexpr uint32_t PRIMARY_TILE_W = RC_PRIMARY_WARPS >= 2 ? 16u : 8u, PRIMARY_TILE_H = RC_PRIMARY_WARPS >= 4 ? 8u : 4u;
+// dynamic shared memory of the kernels that cast AO rays: [warps][AOW_WARP_WORDS] windows, [warps] liquid words
+constexpr uint32_t aow_smem_bytes(uint32_t warps) { return warps * (AOW_WARP_WORDS + 1u) * 4u; }
+
+// FUSED = false: primary + shading + shadow rays, hit pixels append AO seeds (SCHED_TWO_KERNELS, SCHED_AO_PERSISTENT).
+// FUSED = true: the AO rays too (SCHED_FUSED; needs aow_smem_bytes(RC_PRIMARY_WARPS) of dynamic shared memory).
+template <bool FUSED>
+__global__ void __launch_bounds__(32 * RC_PRIMARY_WARPS, RC_PRIMARY_MIN_BLOCKS) primary_kernel(const __grid_constant__ FrameArgs A) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    // an AO kernel launched behind this one with programmatic stream serialization may take the SM slots this grid's last
+    // wave leaves free; it waits (griddepcontrol.wait) for the whole grid before it reads a seed
+    asm volatile("griddepcontrol.launch_dependents;");
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t px = blockIdx.x * PRIMARY_TILE_W + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t localRow = blockIdx.y * PRIMARY_TILE_H + (warp >> 1) * 4u + (lane >> 3);
+    trace_tile<FUSED>(A, px, localRow, lane, FUSED ? smem + warp * AOW_WARP_WORDS : nullptr,
+                      FUSED ? smem + RC_PRIMARY_WARPS * AOW_WARP_WORDS + warp : nullptr, nullptr, 0u);
+}
+
+// SCHED_PERSISTENT / SCHED_PERSISTENT_STAGED: resident warps pull 8x4-pixel tiles from a global atomic queue
+// (FrameCounters::tile_cursor) until the frame is done.  Tile order: Morton inside super-tiles of 8x8 tiles (64x32 pixels),
+// super-tiles row by row -- consecutive queue entries are neighbours on the screen, so the warps of an SM work on rays
+// that share tree nodes.  STAGED: the top tree levels (the breadth-first prefix of DeviceWorld::n_top nodes: root,
+// 256^3 and 64^3 levels) are copied into shared memory once per CTA and every descent reads them from there.
+constexpr uint32_t PERSISTENT_WARPS = 4;
+constexpr uint32_t STAGED_MAX_NODES = 1024;  // 16 KB
+template <bool STAGED>
+__global__ void __launch_bounds__(32 * PERSISTENT_WARPS, RC_PRIMARY_MIN_BLOCKS) frame_persistent_kernel(const __grid_constant__ FrameArgs A) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t* const warpWin = smem + warp * AOW_WARP_WORDS;
+    uint32_t* const liquidWord = smem + PERSISTENT_WARPS * AOW_WARP_WORDS + warp;
+    const uint4* top = nullptr;
+    uint32_t ntop = 0u;
+    if (STAGED) {
+        // after the windows and liquid words (PERSISTENT_WARPS * (AOW_WARP_WORDS + 1) words: a multiple of 16 bytes)
+        uint4* t = reinterpret_cast<uint4*>(smem + PERSISTENT_WARPS * (AOW_WARP_WORDS + 1u));
+        ntop = min(A.world.n_top, STAGED_MAX_NODES);
+        for (uint32_t i = threadIdx.x; i < ntop; i += blockDim.x) t[i] = __ldg(&A.world.nodes[i]);
+        __syncthreads();
+        top = t;
+    }
+    const uint32_t tilesX = (A.p.width + 7u) / 8u, tilesY = (A.local_rows + 3u) / 4u;
+    const uint32_t supersX = (tilesX + 7u) / 8u, supersY = (tilesY + 7u) / 8u;
+    const uint32_t nTiles = supersX * supersY * 64u;
+    // the next tile is claimed while the current one is traced: the atomic's round trip never shows
+    uint32_t next = 0u;
+    if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor, 1u);
+    for (;;) {
+        const uint32_t t = __shfl_sync(0xffffffffu, next, 0);
+        if (t >= nTiles) break;
+        if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor, 1u);
+        const uint32_t sup = t >> 6, m = t & 63u;
+        // Morton: even bits of m -> x, odd bits -> y
+        const uint32_t mx = (m & 1u) | ((m >> 1) & 2u) | ((m >> 2) & 4u), my = ((m >> 1) & 1u) | ((m >> 2) & 2u) | ((m >> 3) & 4u);
+        const uint32_t tx = (sup % supersX) * 8u + mx, ty = (sup / supersX) * 8u + my;
+        if (tx >= tilesX || ty >= tilesY) continue;
+        trace_tile<true>(A, tx * 8u + (lane & 7u), ty * 4u + (lane >> 3), lane, warpWin, liquidWord, top, ntop);
+    }
+}
+
+// SCHED_TWO_KERNELS: one warp per 32 consecutive seeds of the list, grid sized for the worst case (every pixel a hit);
+// warps beyond the list leave at once.
+#ifndef RC_AO_MIN_BLOCKS
+#define RC_AO_MIN_BLOCKS 8  // 64 registers
+#endif
+__global__ void __launch_bounds__(AO_THREADS, RC_AO_MIN_BLOCKS) ao_window_kernel(const __grid_constant__ FrameArgs A) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    const uint32_t nSeeds = A.counters->ao_seed_count;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t warp = threadIdx.x >> 5;
+    if ((t & ~31u) >= nSeeds) return;  // whole warp beyond the list
+    const bool valid = t < nSeeds;
+    const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];  // idle lanes of the last warp shadow a real seed
+    aow_warp(A, s, valid, smem + warp * AOW_WARP_WORDS, smem + (AO_THREADS / 32) * AOW_WARP_WORDS + warp);
+}
+
+// SCHED_AO_PERSISTENT: as many CTAs as the device holds at once; every warp pulls 32-seed chunks from a global atomic cursor
+// (FrameCounters::ao_cursor) until the list is empty -- no CTAs beyond the list, no tail of half-empty waves.  Launched with
+// programmatic stream serialization: the grid may become resident while the primary grid drains, and waits here until
+// that grid has completed and its seeds are visible.
+__global__ void __launch_bounds__(AO_THREADS, RC_AO_MIN_BLOCKS) ao_window_persistent_kernel(const __grid_constant__ FrameArgs A) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const uint32_t nSeeds = *(volatile const unsigned int*)&A.counters->ao_seed_count;
+    const uint32_t nChunks = (nSeeds + 31u) / 32u;
+    uint32_t next = 0u;
+    if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor, 1u);
+    for (;;) {
+        const uint32_t c = __shfl_sync(0xffffffffu, next, 0);
+        if (c >= nChunks) break;
+        if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor, 1u);
+        const uint32_t t = c * 32u + lane;
+        const bool valid = t < nSeeds;
+        const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];
+        aow_warp(A, s, valid, smem + warp * AOW_WARP_WORDS, smem + (AO_THREADS / 32) * AOW_WARP_WORDS + warp);
+    }
+}
+
 
 // Frame composition after the NCCL gather: row y of the frame lives in rank (y/16) % world,
 // local row ((y/16) / world) * 16 + y % 16. One thread per 16-byte (or 4-byte) word of the frame:
@@ -1673,9 +1912,8 @@ __global__ void detmath_kernel(const float* in, uint32_t n, float* outSin, float
     outExp[t] = det_exp(in[t]);
 }
 
-static AoDir* g_aoTable = nullptr;  // [6][RC_MAX_AO_SAMPLES], device
-
-cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream) {
+// *table: AoDir[6][RC_MAX_AO_SAMPLES] on the current device (allocated here on first use; one per device context).
+cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream, void** table) {
     if (n > RC_MAX_AO_SAMPLES) return cudaErrorInvalidValue;
     float inv[3 * RC_MAX_AO_SAMPLES];
     for (uint32_t i = 0; i < 3 * n; i++) inv[i] = 1.0f / dirs[i];  // IEEE division, as the oracle's buildRay does per ray
@@ -1729,36 +1967,98 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 o.ly = face == 1 ? fabsf(iv[1]) : 0.0f;
             }
     }
-    if (!g_aoTable) {
-        e = cudaMalloc((void**)&g_aoTable, sizeof(host));
+    if (!*table) {
+        e = cudaMalloc(table, sizeof(host));
         if (e != cudaSuccess) return e;
     }
-    e = cudaMemcpyAsync(g_aoTable, host, sizeof(host), cudaMemcpyHostToDevice, stream);
+    e = cudaMemcpyAsync(*table, host, sizeof(host), cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
     return cudaStreamSynchronize(stream);  // inv[] lives on this stack frame
 }
 
-void release_hemisphere() {
-    if (g_aoTable) cudaFree(g_aoTable);
-    g_aoTable = nullptr;
+void release_hemisphere(void* table) {
+    if (table) cudaFree(table);
 }
 
-cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream) {
+// Kernels with dynamic shared memory above 48 KB need the opt-in once per device; cheap enough to repeat per launch.
+template <typename K>
+static cudaError_t allow_smem(K kernel, uint32_t bytes) {
+    if (bytes <= 48u * 1024u) return cudaSuccess;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+cudaError_t launch_frame(const FrameArgs& args, uint32_t schedule, int numSms, cudaEvent_t midEvent, cudaStream_t stream,
+                         uint32_t* launches, uint32_t* scheduleUsed) {
+    *launches = 0;
+    const bool ao = args.p.ao_samples > 0 && args.local_rows > 0;
+    // the window code serves ao_steps == 5 (the reference's count, light_scattering.frag:231); other counts walk the tree
+    // with a brick cache (ao_cached_kernel)
+    const bool window = ao && args.ao_table && args.p.ao_steps == AOW_STEPS;
+    const bool fusable = !ao || window;
+    if (schedule >= SCHED_COUNT) schedule = SCHED_TWO_KERNELS;
+    if (schedule >= SCHED_FUSED && !fusable) schedule = SCHED_TWO_KERNELS;
+    if (schedule == SCHED_AO_PERSISTENT && !window) schedule = SCHED_TWO_KERNELS;
+    *scheduleUsed = schedule;
+    if (args.local_rows == 0 || args.p.width == 0) return cudaSuccess;
+    cudaError_t e;
+
+    if (schedule == SCHED_PERSISTENT || schedule == SCHED_PERSISTENT_STAGED) {
+        const bool staged = schedule == SCHED_PERSISTENT_STAGED;
+        const uint32_t ntop = staged ? (args.world.n_top < STAGED_MAX_NODES ? args.world.n_top : STAGED_MAX_NODES) : 0u;
+        const uint32_t bytes = aow_smem_bytes(PERSISTENT_WARPS) + ntop * 16u;
+        const unsigned blocks = (unsigned)numSms * (unsigned)RC_PRIMARY_MIN_BLOCKS;
+        if (staged) {
+            if ((e = allow_smem(frame_persistent_kernel<true>, bytes)) != cudaSuccess) return e;
+            frame_persistent_kernel<true><<<blocks, 32 * PERSISTENT_WARPS, bytes, stream>>>(args);
+        } else {
+            if ((e = allow_smem(frame_persistent_kernel<false>, bytes)) != cudaSuccess) return e;
+            frame_persistent_kernel<false><<<blocks, 32 * PERSISTENT_WARPS, bytes, stream>>>(args);
+        }
+        ++*launches;
+        return cudaGetLastError();
+    }
+
     dim3 grid((args.p.width + PRIMARY_TILE_W - 1u) / PRIMARY_TILE_W, (args.local_rows + PRIMARY_TILE_H - 1u) / PRIMARY_TILE_H);
-    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-    primary_kernel<<<grid, 32 * RC_PRIMARY_WARPS, 0, stream>>>(args);
-    return cudaGetLastError();
-}
+    if (schedule == SCHED_FUSED) {
+        const uint32_t bytes = aow_smem_bytes(RC_PRIMARY_WARPS);
+        if ((e = allow_smem(primary_kernel<true>, bytes)) != cudaSuccess) return e;
+        primary_kernel<true><<<grid, 32 * RC_PRIMARY_WARPS, bytes, stream>>>(args);
+        ++*launches;
+        return cudaGetLastError();
+    }
+    primary_kernel<false><<<grid, 32 * RC_PRIMARY_WARPS, 0, stream>>>(args);
+    ++*launches;
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (midEvent && (e = cudaEventRecord(midEvent, stream)) != cudaSuccess) return e;
+    if (!ao) return cudaSuccess;
 
-cudaError_t launch_ao(const FrameArgs& args, uint32_t maxSeeds, cudaStream_t stream) {
-    if (maxSeeds == 0) return cudaSuccess;
+    const uint32_t maxSeeds = args.local_rows * args.p.width;
+    const uint32_t bytes = aow_smem_bytes(AO_THREADS / 32);
+    if (schedule == SCHED_AO_PERSISTENT) {
+        // as many CTAs as fit at once (64 registers x 128 threads: 8 per SM), never more than the list could need
+        unsigned blocks = (unsigned)numSms * (unsigned)RC_AO_MIN_BLOCKS;
+        const unsigned most = (maxSeeds + AO_THREADS - 1u) / AO_THREADS;
+        if (blocks > most) blocks = most;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(blocks);
+        cfg.blockDim = dim3(AO_THREADS);
+        cfg.dynamicSmemBytes = bytes;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = midEvent ? 0 : 1;  // an event between the two launches: plain stream order
+        e = cudaLaunchKernelEx(&cfg, ao_window_persistent_kernel, args);
+        ++*launches;
+        return e;
+    }
     const unsigned blocks = (maxSeeds + AO_THREADS - 1u) / AO_THREADS;
-    if (args.p.ao_steps == AOW_MAX_STEPS && g_aoTable)
-        ao_window_kernel<AOW_MAX_STEPS><<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
-    else if (args.p.ao_steps < AOW_MAX_STEPS && g_aoTable)
-        ao_window_kernel<0><<<blocks, AO_THREADS, 0, stream>>>(args, g_aoTable);
+    if (window)
+        ao_window_kernel<<<blocks, AO_THREADS, bytes, stream>>>(args);
     else
         ao_cached_kernel<<<blocks, AO_THREADS, 0, stream>>>(args);
+    ++*launches;
     return cudaGetLastError();
 }
 

@@ -40,9 +40,9 @@ struct FrameCounters {
     unsigned long long hit_pixels;
     unsigned long long primary_steps;
     unsigned int ao_seed_count;
-    unsigned int tile_cursor;  // persistent-kernel work queue
+    unsigned int tile_cursor;  // persistent primary kernel: next 8x4-pixel tile (global atomic work queue)
     unsigned int free_flight_rays;  // primary rays that ended in the free-flight loop
-    unsigned int pad;
+    unsigned int ao_cursor;    // persistent AO kernel: next 32-seed chunk (global atomic work queue)
 };
 
 struct FrameArgs {
@@ -72,17 +72,40 @@ struct FrameArgs {
     rc_hit* hits;            // optional
     AoSeed* ao_seeds;        // optional (ao_samples > 0)
     FrameCounters* counters;
+    const void* ao_table;    // AoDir[6][RC_MAX_AO_SAMPLES] of the window AO code (device), set by launch_primary / launch_ao
+    uint32_t ao_opts;        // AO_OPT_*
+    // the sun's ray (low_res.frag:373: buildRay(sunDir)) is the same for every pixel: 1 / sunDir, IEEE fp32, divided once on the host
+    float sun_inv[3];
 };
 
-// Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory.
-cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream);
-void release_hemisphere();
+// Pieces of the window AO code that can be switched off for A/B measurements and tests (same results either way).
+constexpr uint32_t AO_OPT_OCTANT = 1u;   // sample groups whose octant of reachable voxels is empty are not cast
+constexpr uint32_t AO_OPT_DEFAULT = AO_OPT_OCTANT;
 
-// Primary + shading + shadow kernel. Returns the launch error.
-cudaError_t launch_primary(const FrameArgs& args, cudaStream_t stream);
+// How a frame is scheduled on the device (rc_debug_set_option "schedule"; same pixels either way).
+enum FrameSchedule : uint32_t {
+    SCHED_TWO_KERNELS = 0,     // primary_kernel, then ao_window_kernel over the seed list (one CTA per 128 seeds)
+    SCHED_AO_PERSISTENT = 1,   // primary_kernel, then a persistent AO grid pulling 32-seed chunks from a global atomic cursor,
+                               // launched with programmatic dependent launch (its prologue overlaps the primary tail)
+    SCHED_FUSED = 2,           // one kernel: the warp that traced an 8x4 tile casts the AO rays of its hit pixels itself
+                               // (no seed list, no second launch)
+    SCHED_PERSISTENT = 3,      // SCHED_FUSED as persistent warps over a global atomic queue of Morton-ordered 8x4 tiles
+    SCHED_PERSISTENT_STAGED = 4, // SCHED_PERSISTENT with the top tree levels (DeviceWorld::n_top nodes) staged in shared memory
+    SCHED_COUNT
+};
+constexpr uint32_t SCHED_DEFAULT = SCHED_FUSED;
 
-// AO kernel over the seeds appended by the primary kernel.
-cudaError_t launch_ao(const FrameArgs& args, uint32_t max_seeds, cudaStream_t stream);
+// Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory of the current device and the oriented
+// table of the window AO code into *table (device memory, allocated on first use; pass it on as FrameArgs::ao_table).
+cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream, void** table);
+void release_hemisphere(void* table);
+
+// Whole frame: primary + shading + shadow rays, then (or fused with) the AO rays, scheduled as `schedule` says.
+// mid_event (optional): recorded between the primary and the AO kernel when they are separate launches (per-kernel
+// times; it also keeps the AO launch from overlapping the primary tail).  *launches = kernels launched.
+// A schedule that cannot serve the frame (the window AO code needs ao_steps == 5) falls back to SCHED_TWO_KERNELS.
+cudaError_t launch_frame(const FrameArgs& args, uint32_t schedule, int num_sms, cudaEvent_t mid_event, cudaStream_t stream,
+                         uint32_t* launches, uint32_t* schedule_used);
 
 // De-interleave gathered per-rank band buffers into a bottom-up frame (see rc_compose_frame).
 cudaError_t launch_compose(const void* gathered, void* dst, uint32_t width, uint32_t height, uint32_t world_size,

@@ -5,6 +5,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -82,15 +83,33 @@ struct Context {
     bool haveFrame = false;
     rc_frame_params frame{};
     uint32_t localRows = 0, localBands = 0;
-    bool frameHasHits = false, frameHasF32 = false;
+    bool frameHasHits = false, frameHasF32 = false, frameHasKernelTimes = false;
     uint32_t hemiLoaded = 0;
+    void* aoTable = nullptr;  // oriented direction table of the window AO code (device)
     uint32_t launches = 0;
+    int numSms = 0;
+    // how frames are scheduled on the device / which AO specialisations run (rc_debug_set_option; same pixels either way)
+    uint32_t schedule = SCHED_DEFAULT, scheduleUsed = SCHED_DEFAULT, aoOpts = AO_OPT_DEFAULT;
     cudaEvent_t evStart = nullptr, evPrimary = nullptr, evEnd = nullptr;
 
-    std::string lastError;
+    // rc_init_multi: this device may store into device 0's memory (peer access enabled), its frame target pointers are
+    // device 0's (not to be freed / unmapped here), and the event the owner's stream waits for after each frame
+    bool peerToOwner = false, targetAliased = false;
+    cudaEvent_t evFrameDone = nullptr;
 };
 
-Context g;
+// One context per device.  rc_init drives one device (contexts[0]); rc_init_multi drives several from the one host thread
+// the reference's render loop runs on (src/main.cpp:208-219): the public entry points at the end of this file walk the
+// contexts, everything above them is written for "the current context" g.
+constexpr int RC_MAX_DEVICES = 16;
+Context contexts[RC_MAX_DEVICES];
+Context* cur = &contexts[0];
+int nContexts = 1;
+#define g (*cur)
+std::string lastError;
+// device side of the last rc_update_world on context 0, replayed on the other devices
+WorldPatch lastPatch;
+int lastUpdateMode = 0;  // 0 patched in place, 1 whole world installed again
 
 int fail(int code, const char* fmt, ...) {
     char buf[512];
@@ -98,7 +117,7 @@ int fail(int code, const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(buf, sizeof(buf), fmt, ap);
     va_end(ap);
-    g.lastError = buf;
+    lastError = buf;
     return code;
 }
 
@@ -142,11 +161,13 @@ void freeFrameBuffers() {
 void closeFrameTarget() {
     for (int i = 0; i < 2; i++) {
         if (!g.target.ptr[i]) continue;
+        if (g.targetAliased) continue;  // rc_init_multi: device 0's allocation, freed by its own context
         if (g.target.owner) cudaFree(g.target.ptr[i]);
         else cudaIpcCloseMemHandle(g.target.ptr[i]);
         g.target.ptr[i] = nullptr;
     }
     g.target = Context::FrameTarget();
+    g.targetAliased = false;
 }
 
 // gen_hemisphare_distrib.py:4-12 with num_pts = n, in double, rounded to fp32;
@@ -181,10 +202,16 @@ extern "C" {
 
 int rc_abi_version(void) { return RC_ABI_VERSION; }
 
-const char* rc_last_error(void) { return g.lastError.c_str(); }
+#ifndef RC_BUILD_ID
+#define RC_BUILD_ID "unknown"
+#endif
+// sha256 of kernels.cu + kernels.h + free_flight.h as compiled into this library (csrc/Makefile): ties a profiler capture
+// (profiles/traffic.json records the same digest) to the kernels that actually ran
+const char* rc_build_id(void) { return RC_BUILD_ID; }
 
-int rc_init(int device) {
-    if (g.initialized) rc_shutdown();
+const char* rc_last_error(void) { return lastError.c_str(); }
+
+static int one_init(int device) {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0)
@@ -197,6 +224,7 @@ int rc_init(int device) {
     if (prop.major < 10)
         return fail(RC_ERR_UNSUPPORTED, "rc_init: device %d is sm_%d%d; librc is built for sm_100a only", device, prop.major,
                     prop.minor);
+    g.numSms = prop.multiProcessorCount;
     CUDA_TRY(cudaStreamCreateWithFlags(&g.ownStream, cudaStreamNonBlocking));
     g.stream = g.ownStream;
     CUDA_TRY(cudaMalloc((void**)&g.dCounters, sizeof(FrameCounters)));
@@ -210,18 +238,19 @@ int rc_init(int device) {
     g.worldSize = 1;
     g.hemiLoaded = 0;
     g.initialized = true;
-    g.lastError.clear();
+    lastError.clear();
     return RC_OK;
 }
 
-void rc_shutdown(void) {
+static void one_shutdown(void) {
     if (!g.initialized) return;
     cudaSetDevice(g.device);
     cudaStreamSynchronize(g.stream);
     freeWorld();
     freeFrameBuffers();
     closeFrameTarget();
-    release_hemisphere();
+    release_hemisphere(g.aoTable);
+    g.aoTable = nullptr;
     if (g.dCounters) cudaFree(g.dCounters);
     if (g.dSkyTops) cudaFree(g.dSkyTops);
     if (g.dSkyGate) cudaFree(g.dSkyGate);
@@ -235,6 +264,9 @@ void rc_shutdown(void) {
     if (g.hPick) cudaFreeHost(g.hPick);
     g.dPick = nullptr;
     g.hPick = nullptr;
+    if (g.evFrameDone) cudaEventDestroy(g.evFrameDone);
+    g.evFrameDone = nullptr;
+    g.peerToOwner = false;
     if (g.evStart) cudaEventDestroy(g.evStart);
     if (g.evPrimary) cudaEventDestroy(g.evPrimary);
     if (g.evEnd) cudaEventDestroy(g.evEnd);
@@ -255,14 +287,14 @@ void rc_shutdown(void) {
     g.initialized = false;
 }
 
-int rc_set_stream(void* cuda_stream) {
+static int one_set_stream(void* cuda_stream) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_set_stream: call rc_init first");
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     g.stream = cuda_stream ? (cudaStream_t)cuda_stream : g.ownStream;
     return RC_OK;
 }
 
-int rc_set_shard(uint32_t rank, uint32_t world_size) {
+static int one_set_shard(uint32_t rank, uint32_t world_size) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_set_shard: call rc_init first");
     if (world_size == 0 || rank >= world_size)
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_set_shard: rank %u of %u", rank, world_size);
@@ -361,9 +393,10 @@ static int ensureSkyGate(uint32_t maxSteps) {
     return RC_OK;
 }
 
-// Replaces the device world with pw (arrays get slack for later appends) and fills g.info.
-static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
+// Replaces the device world of the current context with pw (arrays get slack for later appends) and fills g.info.
+static int installDevice(uint64_t refBytes, const PackedWorld& pw, double flattenMs) {
     auto t1 = std::chrono::steady_clock::now();
+    CUDA_TRY(cudaSetDevice(g.device));
     CUDA_TRY(cudaStreamSynchronize(g.stream));  // no frame may still read the old world
     freeWorld();
     g.capNodes = pw.nodes.size() + pw.nodes.size() / 4 + 4096;
@@ -384,18 +417,46 @@ static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
     auto t2 = std::chrono::steady_clock::now();
 
     publishWorld(pw.max_depth, pw.nodes.size(), pw.voxels.size(), pw.palette.size());
+    g.world.n_top = pw.level_begin.size() > 3 ? pw.level_begin[3] : (pw.level_begin.empty() ? 0u : pw.level_begin.back());
     g.info.ref_nodes = pw.ref_nodes;
     g.info.ref_bytes = refBytes;
     g.info.null_children = pw.null_children;
     g.info.flatten_ms = flattenMs;
     g.info.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
-    g.packed = std::move(pw);
     g.hostCopyStale = false;
     g.haveWorld = true;
+    g.haveFrame = false;
     return refreshSky();
 }
 
-int rc_upload_world(const rc_world_desc* desc) {
+// ... and keeps pw as the context's host copy (debug lookups, rc_save_world, the baseline of rc_update_world).
+static int installWorld(uint64_t refBytes, PackedWorld&& pw, double flattenMs) {
+    const int rcode = installDevice(refBytes, pw, flattenMs);
+    if (rcode != RC_OK) return rcode;
+    g.packed = std::move(pw);
+    return RC_OK;
+}
+
+// The other devices of rc_init_multi get the world context 0 holds: same arrays, no host copy of their own.
+static int installOnOtherDevices() {
+    const Context& owner = contexts[0];
+    for (int i = 1; i < nContexts; i++) {
+        cur = &contexts[i];
+        g.tracking = FlattenTracking();
+        const int rcode = installDevice(owner.info.ref_bytes, owner.packed, owner.info.flatten_ms);
+        if (rcode != RC_OK) {
+            cur = &contexts[0];
+            return rcode;
+        }
+        g.packed = PackedWorld();
+        g.packed.max_depth = owner.packed.max_depth;
+        g.hostCopyStale = true;
+    }
+    cur = &contexts[0];
+    return RC_OK;
+}
+
+static int one_upload_world(const rc_world_desc* desc) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_upload_world: call rc_init first");
     if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_upload_world: null desc");
     CUDA_TRY(cudaSetDevice(g.device));
@@ -410,7 +471,7 @@ int rc_upload_world(const rc_world_desc* desc) {
 }
 
 // Contiguous runs of the sorted indices (gaps up to 256 nodes are copied along: fewer, larger copies).
-static int uploadNodeRanges(std::vector<uint32_t> idx, uint64_t limit, uint64_t* bytes) {
+static int uploadNodeRanges(const PackedWorld& pw, std::vector<uint32_t> idx, uint64_t limit, uint64_t* bytes) {
     std::sort(idx.begin(), idx.end());
     size_t i = 0;
     while (i < idx.size()) {
@@ -418,7 +479,7 @@ static int uploadNodeRanges(std::vector<uint32_t> idx, uint64_t limit, uint64_t*
         size_t j = i;
         while (j + 1 < idx.size() && idx[j + 1] < limit && idx[j + 1] - idx[j] <= 256) j++;
         const size_t first = idx[i], count = idx[j] - idx[i] + 1;
-        CUDA_TRY(cudaMemcpyAsync(g.dNodes + first, g.packed.nodes.data() + first, count * sizeof(PackedNode),
+        CUDA_TRY(cudaMemcpyAsync(g.dNodes + first, pw.nodes.data() + first, count * sizeof(PackedNode),
                                  cudaMemcpyHostToDevice, g.stream));
         *bytes += count * sizeof(PackedNode);
         i = j + 1;
@@ -426,7 +487,48 @@ static int uploadNodeRanges(std::vector<uint32_t> idx, uint64_t limit, uint64_t*
     return RC_OK;
 }
 
-int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+// Device side of an incremental update, on the current context: the patched nodes in place, the appended tails, the
+// sky tops; ordered after the frames already enqueued on the stream.  pw = the patched host world (context 0's).
+static int applyPatchDevice(const PackedWorld& pw, const WorldPatch& patch, uint64_t refBytes, uint64_t* uploadedBytes) {
+    int rcode;
+    CUDA_TRY(cudaSetDevice(g.device));
+    if (pw.nodes.size() > g.capNodes || pw.voxels.size() > g.capVoxels || pw.palette.size() > g.capPalette) {
+        // out of slack: new, larger arrays with everything copied again (still no flatten)
+        lastUpdateMode = 1;
+        if ((rcode = installDevice(refBytes, pw, 0.0)) != RC_OK) return rcode;
+        *uploadedBytes += g.info.packed_bytes;
+        return RC_OK;
+    }
+    if ((rcode = uploadNodeRanges(pw, patch.node_index, patch.nodes_before, uploadedBytes)) != RC_OK) return rcode;
+    if (pw.nodes.size() > patch.nodes_before) {
+        const size_t n = pw.nodes.size() - patch.nodes_before;
+        CUDA_TRY(cudaMemcpyAsync(g.dNodes + patch.nodes_before, pw.nodes.data() + patch.nodes_before, n * sizeof(PackedNode),
+                                 cudaMemcpyHostToDevice, g.stream));
+        *uploadedBytes += n * sizeof(PackedNode);
+    }
+    if (pw.voxels.size() > patch.voxels_before) {
+        const size_t n = pw.voxels.size() - patch.voxels_before;
+        CUDA_TRY(cudaMemcpyAsync(g.dVoxels + patch.voxels_before, pw.voxels.data() + patch.voxels_before, n * 4,
+                                 cudaMemcpyHostToDevice, g.stream));
+        *uploadedBytes += n * 4;
+    }
+    if (pw.palette.size() > patch.palette_before) {
+        const size_t n = pw.palette.size() - patch.palette_before;
+        CUDA_TRY(cudaMemcpyAsync(g.dPalette + patch.palette_before, pw.palette.data() + patch.palette_before,
+                                 n * sizeof(PaletteEntry), cudaMemcpyHostToDevice, g.stream));
+        *uploadedBytes += n * sizeof(PaletteEntry);
+    }
+    CUDA_TRY(cudaStreamSynchronize(g.stream));  // the copies read pageable host vectors
+    g.world.n_nodes = (uint32_t)pw.nodes.size();
+    g.info.packed_nodes = pw.nodes.size();
+    g.info.packed_voxels = pw.voxels.size();
+    g.info.packed_materials = pw.palette.size();
+    g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
+    g.info.ref_bytes = refBytes;
+    return refreshSky();
+}
+
+static int one_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
                     const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_update_world: call rc_init first");
     if (!desc) return fail(RC_ERR_INVALID_ARGUMENT, "rc_update_world: null desc");
@@ -442,7 +544,13 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
         rcode = update_world(*desc, dirty_node_blocks, n_dirty_node_blocks, dirty_array_blocks, n_dirty_array_blocks, g.packed,
                              g.tracking, patch, st, err);
     if (rcode < 0) {
-        g.tracking = FlattenTracking();  // g.packed may be half patched: force a full flatten next time
+        // g.packed may be half patched while the device still holds the old world: force a full flatten next time, and
+        // have rc_save_world / the debug lookups fetch nodes and voxels back from the device (what is rendered) instead
+        // of trusting the host copy
+        g.tracking = FlattenTracking();
+        g.packed.nodes.clear();
+        g.packed.voxels.clear();
+        g.hostCopyStale = true;
         return fail(rcode, "%s", err.c_str());
     }
     if (rcode == 1) {
@@ -456,6 +564,7 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
         rcode = installWorld(desc->node_bytes_used + desc->array_bytes_used, std::move(pw), ui.host_ms);
         if (rcode != RC_OK) return rcode;
         g.tracking = std::move(tr);
+        lastUpdateMode = 1;
         ui.full_rebuild = 1;
         ui.uploaded_bytes = g.info.packed_bytes;
         ui.upload_ms = g.info.upload_ms;
@@ -472,42 +581,9 @@ int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks
     ui.garbage_nodes = g.tracking.garbage_nodes;
     ui.garbage_voxels = g.tracking.garbage_voxels;
 
-    // device side, ordered after the frames already enqueued on the stream
-    if (pw.nodes.size() > g.capNodes || pw.voxels.size() > g.capVoxels || pw.palette.size() > g.capPalette) {
-        // out of slack: new, larger arrays with everything copied again (still no flatten)
-        PackedWorld copy = pw;
-        rcode = installWorld(desc->node_bytes_used + desc->array_bytes_used, std::move(copy), 0.0);
-        if (rcode != RC_OK) return rcode;
-        ui.uploaded_bytes = g.info.packed_bytes;
-    } else {
-        if ((rcode = uploadNodeRanges(patch.node_index, patch.nodes_before, &ui.uploaded_bytes)) != RC_OK) return rcode;
-        if (pw.nodes.size() > patch.nodes_before) {
-            const size_t n = pw.nodes.size() - patch.nodes_before;
-            CUDA_TRY(cudaMemcpyAsync(g.dNodes + patch.nodes_before, pw.nodes.data() + patch.nodes_before, n * sizeof(PackedNode),
-                                     cudaMemcpyHostToDevice, g.stream));
-            ui.uploaded_bytes += n * sizeof(PackedNode);
-        }
-        if (pw.voxels.size() > patch.voxels_before) {
-            const size_t n = pw.voxels.size() - patch.voxels_before;
-            CUDA_TRY(cudaMemcpyAsync(g.dVoxels + patch.voxels_before, pw.voxels.data() + patch.voxels_before, n * 4,
-                                     cudaMemcpyHostToDevice, g.stream));
-            ui.uploaded_bytes += n * 4;
-        }
-        if (pw.palette.size() > patch.palette_before) {
-            const size_t n = pw.palette.size() - patch.palette_before;
-            CUDA_TRY(cudaMemcpyAsync(g.dPalette + patch.palette_before, pw.palette.data() + patch.palette_before,
-                                     n * sizeof(PaletteEntry), cudaMemcpyHostToDevice, g.stream));
-            ui.uploaded_bytes += n * sizeof(PaletteEntry);
-        }
-        CUDA_TRY(cudaStreamSynchronize(g.stream));  // the copies read pageable host vectors
-        g.world.n_nodes = (uint32_t)pw.nodes.size();
-        g.info.packed_nodes = pw.nodes.size();
-        g.info.packed_voxels = pw.voxels.size();
-        g.info.packed_materials = pw.palette.size();
-        g.info.packed_bytes = pw.nodes.size() * sizeof(PackedNode) + pw.voxels.size() * 4 + pw.palette.size() * sizeof(PaletteEntry);
-        g.info.ref_bytes = desc->node_bytes_used + desc->array_bytes_used;
-        if ((rcode = refreshSky()) != RC_OK) return rcode;
-    }
+    lastPatch = patch;
+    lastUpdateMode = 0;
+    if ((rcode = applyPatchDevice(pw, patch, desc->node_bytes_used + desc->array_bytes_used, &ui.uploaded_bytes)) != RC_OK) return rcode;
     auto t2 = std::chrono::steady_clock::now();
     ui.host_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     ui.upload_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
@@ -526,7 +602,7 @@ int rc_save_world(const char* path) {
     return RC_OK;
 }
 
-int rc_load_world(const char* path) {
+static int one_load_world(const char* path) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_load_world: call rc_init first");
     CUDA_TRY(cudaSetDevice(g.device));
     auto t0 = std::chrono::steady_clock::now();
@@ -539,7 +615,7 @@ int rc_load_world(const char* path) {
     return installWorld(0, std::move(pw), std::chrono::duration<double, std::milli>(t1 - t0).count());
 }
 
-int rc_generate_world(const rc_gen_params* params, rc_gen_info* info) {
+static int one_generate_world(const rc_gen_params* params, rc_gen_info* info) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_generate_world: call rc_init first");
     if (!params) return fail(RC_ERR_INVALID_ARGUMENT, "rc_generate_world: null params");
     CUDA_TRY(cudaSetDevice(g.device));
@@ -565,6 +641,7 @@ int rc_generate_world(const rc_gen_params* params, rc_gen_info* info) {
                              g.stream));
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     publishWorld(params->max_depth, gw.n_nodes, gw.n_voxels, gw.palette.size());
+    g.world.n_top = gw.level_begin.size() > 3 ? gw.level_begin[3] : (gw.level_begin.empty() ? 0u : gw.level_begin.back());
     // what the reference's pools would hold for this world: a 16-byte node per packed node and per voxel,
     // a 256-byte child array per branch (src/voxel_data/types.hpp:29-47)
     g.info.ref_nodes = gw.n_nodes + gw.n_voxels;
@@ -602,7 +679,7 @@ int rc_world_info_get(rc_world_info* out) {
     return RC_OK;
 }
 
-int rc_render_frame(const rc_frame_params* params) {
+static int one_render_frame(const rc_frame_params* params) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_render_frame: call rc_init first");
     if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_render_frame: call rc_upload_world first");
     if (!params) return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame: null params");
@@ -645,7 +722,7 @@ int rc_render_frame(const rc_frame_params* params) {
         if (g.hemiLoaded != p.ao_samples) {
             std::vector<float> tab(3 * (size_t)p.ao_samples);
             hemisphereTable(p.ao_samples, tab.data());
-            CUDA_TRY(upload_hemisphere(tab.data(), p.ao_samples, g.stream));
+            CUDA_TRY(upload_hemisphere(tab.data(), p.ao_samples, g.stream, &g.aoTable));
             g.hemiLoaded = p.ao_samples;
         }
     }
@@ -688,17 +765,17 @@ int rc_render_frame(const rc_frame_params* params) {
     a.hits = (p.flags & RC_F_HITS) ? g.dHits : nullptr;
     a.ao_seeds = p.ao_samples > 0 ? g.dSeeds : nullptr;
     a.counters = g.dCounters;
+    a.ao_table = p.ao_samples > 0 ? g.aoTable : nullptr;
+    a.ao_opts = g.aoOpts;
+    for (int k = 0; k < 3; k++) a.sun_inv[k] = 1.0f / p.sun_dir[k];  // IEEE fp32, as buildRay(sunDir) divides (low_res.frag:67)
 
+    // per-kernel times need an event between the two launches, which also keeps the AO grid from becoming resident
+    // while the primary grid drains: only on request
+    const bool kernelTimes = (p.flags & RC_F_KERNEL_TIMES) != 0;
     g.launches = 0;
     CUDA_TRY(cudaMemsetAsync(g.dCounters, 0, sizeof(FrameCounters), g.stream));
     CUDA_TRY(cudaEventRecord(g.evStart, g.stream));
-    CUDA_TRY(launch_primary(a, g.stream));
-    g.launches++;
-    CUDA_TRY(cudaEventRecord(g.evPrimary, g.stream));
-    if (p.ao_samples > 0 && localRows > 0) {
-        CUDA_TRY(launch_ao(a, (uint32_t)((size_t)localRows * p.width), g.stream));
-        g.launches++;
-    }
+    CUDA_TRY(launch_frame(a, g.schedule, g.numSms, kernelTimes ? g.evPrimary : nullptr, g.stream, &g.launches, &g.scheduleUsed));
     CUDA_TRY(cudaEventRecord(g.evEnd, g.stream));
     CUDA_TRY(cudaMemcpyAsync(g.hCounters, g.dCounters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, g.stream));
 
@@ -707,11 +784,12 @@ int rc_render_frame(const rc_frame_params* params) {
     g.localBands = localBands;
     g.frameHasHits = (p.flags & RC_F_HITS) != 0;
     g.frameHasF32 = (p.flags & RC_F_RGBA32F) != 0;
+    g.frameHasKernelTimes = kernelTimes && g.scheduleUsed < SCHED_FUSED;
     g.haveFrame = true;
     return RC_OK;
 }
 
-int rc_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void* handles_out) {
+static int one_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void* handles_out) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_create: call rc_init first");
     if (width == 0 || height == 0 || width > 65536 || height > 65536 || slots == 0 || slots > 2 || !handles_out)
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_target_create: %ux%u, %u slots", width, height, slots);
@@ -734,7 +812,7 @@ int rc_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void
     return RC_OK;
 }
 
-int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const void* handles) {
+static int one_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const void* handles) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_open: call rc_init first");
     if (width == 0 || height == 0 || slots == 0 || slots > 2 || !handles)
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_target_open: %ux%u, %u slots", width, height, slots);
@@ -759,7 +837,7 @@ int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const 
     return RC_OK;
 }
 
-int rc_frame_target_close(void) {
+static int one_frame_target_close(void) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_target_close: call rc_init first");
     CUDA_TRY(cudaSetDevice(g.device));
     CUDA_TRY(cudaStreamSynchronize(g.stream));
@@ -774,7 +852,7 @@ void* rc_frame_target_device(uint32_t slot) {
 
 int rc_frame_target_last_slot(void) { return g.initialized ? g.target.lastSlot : -1; }
 
-int rc_sync(void) {
+static int one_sync(void) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_sync: call rc_init first");
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     return RC_OK;
@@ -812,7 +890,7 @@ static int copyRowsToHost(void* dst, const void* src, size_t bytesPerPixel, cuda
     return RC_OK;
 }
 
-int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket) {
+static int one_read_image_async(void* dst, size_t dst_bytes, int* ticket) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_image_async: call rc_init first");
     if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_read_image_async: no frame rendered");
     if (!dst || !ticket) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image_async: null dst / ticket");
@@ -851,7 +929,7 @@ int rc_host_unregister(void* ptr) {
     return RC_OK;
 }
 
-int rc_wait_image(int ticket) {
+static int one_wait_image(int ticket) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_wait_image: call rc_init first");
     if (ticket < 0 || ticket > 1 || !g.slot[ticket].evCopied)
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_wait_image: ticket %d was not issued by rc_read_image_async", ticket);
@@ -859,7 +937,7 @@ int rc_wait_image(int ticket) {
     return RC_OK;
 }
 
-int rc_read_image(void* dst, size_t dst_bytes, int format) {
+static int one_read_image(void* dst, size_t dst_bytes, int format) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_image: call rc_init first");
     if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_read_image: no frame rendered");
     if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: null dst");
@@ -875,7 +953,7 @@ int rc_read_image(void* dst, size_t dst_bytes, int format) {
     return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: unknown format %d", format);
 }
 
-int rc_read_hits(rc_hit* dst, size_t n) {
+static int one_read_hits(rc_hit* dst, size_t n) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_hits: call rc_init first");
     if (!g.haveFrame || !g.frameHasHits) return fail(RC_ERR_NO_FRAME, "rc_read_hits: no frame rendered with RC_F_HITS");
     if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_hits: null dst");
@@ -884,7 +962,7 @@ int rc_read_hits(rc_hit* dst, size_t n) {
     return copyRowsToHost(dst, g.dHits, sizeof(rc_hit));
 }
 
-int rc_frame_stats_get(rc_frame_stats* out) {
+static int one_frame_stats_get(rc_frame_stats* out) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_stats_get: call rc_init first");
     if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_frame_stats_get: no frame rendered");
     if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_stats_get: null out");
@@ -898,9 +976,12 @@ int rc_frame_stats_get(rc_frame_stats* out) {
     out->kernel_launches = g.launches;
     out->free_flight_rays = g.hCounters->free_flight_rays;
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, g.evStart, g.evPrimary) == cudaSuccess) out->primary_ms = ms;
-    if (cudaEventElapsedTime(&ms, g.evPrimary, g.evEnd) == cudaSuccess) out->ao_ms = ms;
+    if (g.frameHasKernelTimes) {
+        if (cudaEventElapsedTime(&ms, g.evStart, g.evPrimary) == cudaSuccess) out->primary_ms = ms;
+        if (cudaEventElapsedTime(&ms, g.evPrimary, g.evEnd) == cudaSuccess) out->ao_ms = ms;
+    }
     if (cudaEventElapsedTime(&ms, g.evStart, g.evEnd) == cudaSuccess) out->total_ms = ms;
+    out->schedule = g.scheduleUsed;
     return RC_OK;
 }
 
@@ -1110,6 +1191,24 @@ int rc_debug_load_host(const char* path, rc_world_info* info) {
     return RC_OK;
 }
 
+// Scheduling / specialisation switches for A/B measurements and parity tests (every setting renders the same pixels):
+//   "schedule"  0 two kernels, 1 persistent AO grid + programmatic dependent launch, 2 fused, 3 persistent fused,
+//               4 persistent fused with the top tree levels staged in shared memory
+//   "ao_opts"   bit 0: AO sample groups whose octant of reachable voxels is empty are not cast
+static int one_debug_set_option(const char* name, int value) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_set_option: call rc_init first");
+    if (!name) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: null name");
+    if (!strcmp(name, "schedule")) {
+        if (value < 0 || value >= (int)SCHED_COUNT) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: schedule %d", value);
+        g.schedule = (uint32_t)value;
+    } else if (!strcmp(name, "ao_opts")) {
+        g.aoOpts = (uint32_t)value & AO_OPT_DEFAULT;
+    } else {
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: unknown option %s", name);
+    }
+    return RC_OK;
+}
+
 int rc_debug_struct_sizes(uint32_t out[5]) {
     if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_struct_sizes: null out");
     out[0] = (uint32_t)sizeof(rc_world_desc);
@@ -1135,6 +1234,293 @@ int rc_debug_detmath(const float* in, uint32_t n, float* out_sin, float* out_exp
     cudaFree(dIn);
     cudaFree(dS);
     cudaFree(dE);
+    return RC_OK;
+}
+
+
+// =====================================================================================================================
+// Public entry points: rc_init drives one device; rc_init_multi several, from the caller's one thread (the reference's host
+// is one process with one render loop, src/main.cpp:173-232).  With n devices the library owns the sharding: device i
+// renders the 16-row bands with band % n == i of every frame (its kernels run on its own stream, all launched before any
+// is waited for), every device holds the whole world, and rc_read_image / rc_read_image_async / rc_read_hits copy each
+// device's bands straight to their place in the caller's frame -- one PCIe link per device, no device-side gather.  Pass
+// page-locked memory (rc_host_register) for those copies to run concurrently.
+// =====================================================================================================================
+struct UseContext {  // selects a context for the duration of a call; the current one is contexts[0] otherwise
+    explicit UseContext(int i) { cur = &contexts[i]; }
+    ~UseContext() { cur = &contexts[0]; }
+};
+
+int rc_init_multi(int n_devices, const int* devices) {
+    if (n_devices < 1 || n_devices > RC_MAX_DEVICES || !devices)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_init_multi: %d devices (1..%d)", n_devices, RC_MAX_DEVICES);
+    // tests on a one-GPU box: RC_ALLOW_DUPLICATE_DEVICES=1 lets one device play several (every code path of the multi-device
+    // entry points runs; nothing gets faster)
+    const char* dup = getenv("RC_ALLOW_DUPLICATE_DEVICES");
+    const bool allowDup = dup && dup[0] == '1';
+    for (int i = 0; i < n_devices && !allowDup; i++)
+        for (int j = 0; j < i; j++)
+            if (devices[i] == devices[j]) return fail(RC_ERR_INVALID_ARGUMENT, "rc_init_multi: device %d listed twice", devices[i]);
+    rc_shutdown();
+    for (int i = 0; i < n_devices; i++) {
+        cur = &contexts[i];
+        const int rcode = one_init(devices[i]);
+        if (rcode != RC_OK) {
+            nContexts = i;
+            cur = &contexts[0];
+            const std::string why = lastError;
+            rc_shutdown();
+            lastError = why;
+            return rcode;
+        }
+        g.rank = (uint32_t)i;
+        g.worldSize = (uint32_t)n_devices;
+    }
+    nContexts = n_devices;
+    // peer access to device 0 (rc_frame_target_create: every device's kernels may store into ONE frame there)
+    for (int i = 1; i < n_devices; i++) {
+        cur = &contexts[i];
+        int can = 0;
+        if (g.device == contexts[0].device) {
+            g.peerToOwner = true;  // the same device (RC_ALLOW_DUPLICATE_DEVICES)
+        } else if (cudaSetDevice(g.device) == cudaSuccess && cudaDeviceCanAccessPeer(&can, g.device, contexts[0].device) == cudaSuccess && can) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(contexts[0].device, 0);
+            if (e == cudaSuccess || e == cudaErrorPeerAccessAlreadyEnabled) g.peerToOwner = true;
+            (void)cudaGetLastError();
+        }
+        if (cudaEventCreateWithFlags(&g.evFrameDone, cudaEventDisableTiming) != cudaSuccess) g.evFrameDone = nullptr;
+    }
+    cur = &contexts[0];
+    return RC_OK;
+}
+
+int rc_init(int device) { return rc_init_multi(1, &device); }
+
+int rc_device_count(void) { return contexts[0].initialized ? nContexts : 0; }
+
+void rc_shutdown(void) {
+    for (int i = nContexts - 1; i >= 0; i--) {
+        cur = &contexts[i];
+        one_shutdown();
+    }
+    nContexts = 1;
+    cur = &contexts[0];
+}
+
+int rc_set_stream(void* cuda_stream) {
+    if (nContexts > 1) return fail(RC_ERR_UNSUPPORTED, "rc_set_stream: with rc_init_multi the library owns one stream per device");
+    return one_set_stream(cuda_stream);
+}
+
+int rc_set_shard(uint32_t rank, uint32_t world_size) {
+    if (nContexts > 1) return fail(RC_ERR_UNSUPPORTED, "rc_set_shard: with rc_init_multi the library shards frames over its own devices");
+    return one_set_shard(rank, world_size);
+}
+
+int rc_upload_world(const rc_world_desc* desc) {
+    const int rcode = one_upload_world(desc);  // flatten once, on the host
+    return rcode != RC_OK ? rcode : installOnOtherDevices();
+}
+
+int rc_update_world(const rc_world_desc* desc, const uint32_t* dirty_node_blocks, uint32_t n_dirty_node_blocks,
+                    const uint32_t* dirty_array_blocks, uint32_t n_dirty_array_blocks, rc_update_info* info) {
+    int rcode = one_update_world(desc, dirty_node_blocks, n_dirty_node_blocks, dirty_array_blocks, n_dirty_array_blocks, info);
+    if (rcode != RC_OK || nContexts == 1) return rcode;
+    // the diff and the re-flatten happened once, on context 0's mirror: the other devices get the same bytes
+    if (lastUpdateMode == 1) return installOnOtherDevices();
+    const Context& owner = contexts[0];
+    for (int i = 1; i < nContexts && rcode == RC_OK; i++) {
+        UseContext use(i);
+        uint64_t bytes = 0;
+        rcode = applyPatchDevice(owner.packed, lastPatch, owner.info.ref_bytes, &bytes);
+        if (info) info->uploaded_bytes += bytes;
+    }
+    return rcode;
+}
+
+int rc_load_world(const char* path) {
+    const int rcode = one_load_world(path);
+    return rcode != RC_OK ? rcode : installOnOtherDevices();
+}
+
+int rc_generate_world(const rc_gen_params* params, rc_gen_info* info) {
+    // every device builds the world itself (10 ms for the 2048^2 world): no host copy, no transfer between devices
+    int rcode = one_generate_world(params, info);
+    for (int i = 1; i < nContexts && rcode == RC_OK; i++) {
+        UseContext use(i);
+        rcode = one_generate_world(params, nullptr);
+    }
+    return rcode;
+}
+
+int rc_debug_set_option(const char* name, int value) {
+    int rcode = RC_OK;
+    for (int i = 0; i < nContexts && rcode == RC_OK; i++) {
+        UseContext use(i);
+        rcode = one_debug_set_option(name, value);
+    }
+    return rcode;
+}
+
+int rc_render_frame(const rc_frame_params* params) {
+    if (nContexts == 1) return one_render_frame(params);
+    // all devices' kernels are queued before anything is waited for: they run side by side
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        const int rcode = one_render_frame(params);
+        if (rcode != RC_OK) return rcode;
+    }
+    // one frame on device 0 written by every device (rc_frame_target_create): complete, in device 0's stream order, once
+    // every device's kernels have finished
+    if (contexts[0].target.lastSlot >= 0) {
+        for (int i = 1; i < nContexts; i++) {
+            Context& c = contexts[i];
+            if (!c.evFrameDone || c.target.lastSlot < 0) continue;
+            CUDA_TRY(cudaSetDevice(c.device));
+            CUDA_TRY(cudaEventRecord(c.evFrameDone, c.stream));
+            CUDA_TRY(cudaSetDevice(contexts[0].device));
+            CUDA_TRY(cudaStreamWaitEvent(contexts[0].stream, c.evFrameDone, 0));
+        }
+    }
+    return RC_OK;
+}
+
+int rc_frame_target_create(uint32_t width, uint32_t height, uint32_t slots, void* handles_out) {
+    if (nContexts == 1) return one_frame_target_create(width, height, slots, handles_out);
+    // device 0 owns the frame; the others reach it through peer access (no IPC handles inside one process)
+    uint8_t scratch[2 * RC_IPC_HANDLE_BYTES];
+    for (int i = 1; i < nContexts; i++)
+        if (!contexts[i].peerToOwner)
+            return fail(RC_ERR_UNSUPPORTED, "rc_frame_target_create: device %d has no peer access to device %d", contexts[i].device,
+                        contexts[0].device);
+    for (int i = 1; i < nContexts; i++) {
+        UseContext use(i);
+        CUDA_TRY(cudaSetDevice(g.device));
+        CUDA_TRY(cudaStreamSynchronize(g.stream));
+        closeFrameTarget();
+    }
+    const int rcode = one_frame_target_create(width, height, slots, handles_out ? handles_out : scratch);
+    if (rcode != RC_OK) return rcode;
+    for (int i = 1; i < nContexts; i++) {
+        Context& c = contexts[i];
+        c.target = contexts[0].target;
+        c.target.owner = false;
+        c.targetAliased = true;
+    }
+    return RC_OK;
+}
+
+int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const void* handles) {
+    if (nContexts > 1)
+        return fail(RC_ERR_UNSUPPORTED, "rc_frame_target_open: with rc_init_multi the frame target lives on the library's device 0");
+    return one_frame_target_open(width, height, slots, handles);
+}
+
+int rc_frame_target_close(void) {
+    int rcode = RC_OK;
+    for (int i = nContexts - 1; i >= 0; i--) {  // the aliases first, the owner last
+        UseContext use(i);
+        const int r = one_frame_target_close();
+        if (r != RC_OK) rcode = r;
+    }
+    return rcode;
+}
+
+int rc_sync(void) {
+    int rcode = RC_OK;
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        const int r = one_sync();
+        if (r != RC_OK) rcode = r;
+    }
+    return rcode;
+}
+
+int rc_read_image(void* dst, size_t dst_bytes, int format) {
+    if (nContexts == 1) return one_read_image(dst, dst_bytes, format);
+    // every device queues the copy of its bands, then all are waited for: the links work in parallel
+    const Context& c0 = contexts[0];
+    if (!c0.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_image: call rc_init first");
+    if (!c0.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_read_image: no frame rendered");
+    if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: null dst");
+    const size_t pixels = (size_t)c0.frame.width * c0.frame.height;
+    const size_t bpp = format == RC_RGBA8 ? 4 : (format == RC_RGBA32F ? 16 : 0);
+    if (!bpp) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_image: unknown format %d", format);
+    if (format == RC_RGBA32F && !c0.frameHasF32) return fail(RC_ERR_NO_FRAME, "rc_read_image: frame was rendered without RC_F_RGBA32F");
+    if (dst_bytes < pixels * bpp) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_image: need %zu bytes", pixels * bpp);
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        CUDA_TRY(cudaSetDevice(g.device));
+        const int rcode = copyRowsToHost(dst, format == RC_RGBA8 ? (const void*)g.dRgba8 : (const void*)g.dRgba32f, bpp, nullptr, false);
+        if (rcode != RC_OK) return rcode;
+    }
+    return rc_sync();
+}
+
+int rc_read_hits(rc_hit* dst, size_t n) {
+    if (nContexts == 1) return one_read_hits(dst, n);
+    const Context& c0 = contexts[0];
+    if (!c0.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_read_hits: call rc_init first");
+    if (!c0.haveFrame || !c0.frameHasHits) return fail(RC_ERR_NO_FRAME, "rc_read_hits: no frame rendered with RC_F_HITS");
+    if (!dst) return fail(RC_ERR_INVALID_ARGUMENT, "rc_read_hits: null dst");
+    if (n < (size_t)c0.frame.width * c0.frame.height) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_read_hits: need %zu records", (size_t)c0.frame.width * c0.frame.height);
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        CUDA_TRY(cudaSetDevice(g.device));
+        const int rcode = copyRowsToHost(dst, g.dHits, sizeof(rc_hit), nullptr, false);
+        if (rcode != RC_OK) return rcode;
+    }
+    return rc_sync();
+}
+
+int rc_read_image_async(void* dst, size_t dst_bytes, int* ticket) {
+    int first = -1;
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        int t = -1;
+        const int rcode = one_read_image_async(dst, dst_bytes, &t);
+        if (rcode != RC_OK) return rcode;
+        if (i == 0) first = t;
+        else if (t != first) return fail(RC_ERR_CUDA, "rc_read_image_async: the devices' frame slots ran out of step (%d vs %d)", t, first);
+    }
+    if (ticket) *ticket = first;
+    return RC_OK;
+}
+
+int rc_wait_image(int ticket) {
+    int rcode = RC_OK;
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        const int r = one_wait_image(ticket);
+        if (r != RC_OK) rcode = r;
+    }
+    return rcode;
+}
+
+int rc_frame_stats_get(rc_frame_stats* out) {
+    if (nContexts == 1) return one_frame_stats_get(out);
+    if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_stats_get: null out");
+    rc_frame_stats sum;
+    memset(&sum, 0, sizeof(sum));
+    for (int i = 0; i < nContexts; i++) {
+        UseContext use(i);
+        rc_frame_stats s;
+        const int rcode = one_frame_stats_get(&s);
+        if (rcode != RC_OK) return rcode;
+        sum.primary_rays += s.primary_rays;
+        sum.shadow_rays += s.shadow_rays;
+        sum.ao_rays += s.ao_rays;
+        sum.hit_pixels += s.hit_pixels;
+        sum.primary_steps += s.primary_steps;
+        sum.kernel_launches += s.kernel_launches;
+        sum.free_flight_rays += s.free_flight_rays;
+        // the devices run side by side: the frame takes as long as the slowest of them
+        sum.primary_ms = s.primary_ms > sum.primary_ms ? s.primary_ms : sum.primary_ms;
+        sum.ao_ms = s.ao_ms > sum.ao_ms ? s.ao_ms : sum.ao_ms;
+        sum.total_ms = s.total_ms > sum.total_ms ? s.total_ms : sum.total_ms;
+        sum.schedule = s.schedule;
+    }
+    *out = sum;
     return RC_OK;
 }
 

@@ -121,19 +121,48 @@ int load_packed(PackedWorld& w, const char* path, std::string& err) {
     w.ref_nodes = h.ref_nodes;
     w.null_children = h.null_children;
     if (checksum(w) != h.checksum) return bad("checksum mismatch");
-    // structural check: every child run inside its array (a corrupt blob must not send the kernel out of bounds)
-    for (size_t i = 0; i < w.nodes.size(); i++) {
-        const PackedNode& n = w.nodes[i];
-        const uint32_t kind = n.kind & PK_KIND_MASK;
-        const uint64_t cnt = (uint64_t)__builtin_popcountll(n.mask);
-        if (kind == PK_INNER) {
+    // Structural check, by walking from the root the way the kernels do: fetch_region / world_tops_kernel pick the array a
+    // child run is read from by the tree LEVEL (children of a node whose cells have shift 0 are voxels, all others are
+    // nodes), lookup() by the node's kind -- so every reachable node must have the kind its level implies, every child run
+    // must lie inside the array that level reads, and a node must not be reachable at two levels.  Nodes no walk can
+    // reach (runs abandoned by rc_update_world) are never indexed and are not looked at.
+    {
+        const int rootShift = 2 * ((int)w.max_depth - 2);
+        std::vector<uint8_t> level(w.nodes.size(), 0xFF);  // shift / 2 of the node's child cells, 0xFF = not reached
+        std::vector<uint32_t> todo;
+        todo.push_back(0u);
+        level[0] = (uint8_t)(rootShift / 2);
+        while (!todo.empty()) {
+            const uint32_t i = todo.back();
+            todo.pop_back();
+            const PackedNode& n = w.nodes[i];
+            const uint32_t kind = n.kind & PK_KIND_MASK;
+            const int shift = 2 * (int)level[i];
+            const uint64_t cnt = (uint64_t)__builtin_popcountll(n.mask);
+            if (shift == 0) {
+                if (kind != PK_BRICK) return bad("a node at the brick level is not a brick");
+                if (n.base + cnt > w.voxels.size()) return bad("voxel run outside the voxel array");
+                continue;
+            }
+            if (kind != PK_INNER) return bad(kind == PK_BRICK ? "a brick above the brick level" : kind == PK_LEAF ? "a leaf with children" : "unknown node kind");
             if (n.base + cnt > w.nodes.size()) return bad("child run outside the node array");
-        } else if (kind == PK_BRICK) {
-            if (n.base + cnt > w.voxels.size()) return bad("voxel run outside the voxel array");
-        } else if (kind == PK_LEAF) {
-            if ((n.base & MATERIAL_INDEX_MASK) >= w.palette.size() || n.base == 0) return bad("leaf material outside the palette");
-        } else {
-            return bad("unknown node kind");
+            for (uint64_t c = 0; c < cnt; c++) {
+                const uint32_t ci = n.base + (uint32_t)c;
+                const PackedNode& ch = w.nodes[ci];
+                const uint32_t ck = ch.kind & PK_KIND_MASK;
+                if (ck == PK_LEAF) {
+                    if ((ch.base & MATERIAL_INDEX_MASK) >= w.palette.size() || ch.base == 0) return bad("leaf material outside the palette");
+                    continue;
+                }
+                if (ck != PK_INNER && ck != PK_BRICK) return bad("unknown node kind");
+                const uint8_t lv = (uint8_t)(shift / 2 - 1);
+                if (level[ci] == 0xFF) {
+                    level[ci] = lv;
+                    todo.push_back(ci);
+                } else if (level[ci] != lv) {
+                    return bad("a node is reachable at two tree levels");
+                }
+            }
         }
     }
     for (uint32_t v : w.voxels)

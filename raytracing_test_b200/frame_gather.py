@@ -93,6 +93,7 @@ class ShardedRayCaster:
         self._target_open = False
         self._copy_stream = None
         self._pending = {}  # frame slot -> event of the read-back still reading it (rank 0)
+        self.completion_signal = "one-element NCCL all-reduce behind the kernels as the completion signal"
 
     def close(self):
         if self._target_open:

@@ -14,6 +14,11 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RC_LIBRC") or os.path.join(PKG_DIR, "librc.so")  # RC_LIBRC: a variant build (kernel tuning)
 
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F, RC_F_NO_FREE_FLIGHT, RC_F_NO_LEAP, RC_F_ALWAYS_TAIL = 1, 2, 4, 8, 16, 32, 64
+RC_F_KERNEL_TIMES = 128
+# rc_debug_set_option("schedule", ...): how a frame is scheduled on the device (csrc/kernels.h FrameSchedule)
+SCHED_TWO_KERNELS, SCHED_AO_PERSISTENT, SCHED_FUSED, SCHED_PERSISTENT, SCHED_PERSISTENT_STAGED = range(5)
+SCHEDULES = {"two_kernels": 0, "ao_persistent": 1, "fused": 2, "persistent": 3, "persistent_staged": 4}
+AO_OPT_OCTANT = 1
 RC_RGBA8, RC_RGBA32F = 0, 1
 RC_IPC_HANDLE_BYTES = 64
 RC_ALL_BLOCKS = 0xFFFFFFFF
@@ -108,7 +113,7 @@ class FrameStats(ctypes.Structure):
         ("hit_pixels", ctypes.c_uint64), ("primary_steps", ctypes.c_uint64),
         ("kernel_launches", ctypes.c_uint32), ("free_flight_rays", ctypes.c_uint32),
         ("primary_ms", ctypes.c_float), ("ao_ms", ctypes.c_float), ("total_ms", ctypes.c_float),
-        ("reserved2", ctypes.c_float),
+        ("schedule", ctypes.c_uint32),
     ]
 
     def as_dict(self):
@@ -118,6 +123,9 @@ class FrameStats(ctypes.Structure):
 # name -> (restype, argtypes); every symbol include/rc.h and include/rc_debug.h declare
 ABI = {
     "rc_init": (ctypes.c_int, [ctypes.c_int]),
+    "rc_init_multi": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p]),
+    "rc_device_count": (ctypes.c_int, []),
+    "rc_build_id": (ctypes.c_char_p, []),
     "rc_shutdown": (None, []),
     "rc_last_error": (ctypes.c_char_p, []),
     "rc_abi_version": (ctypes.c_int, []),
@@ -166,6 +174,7 @@ ABI = {
     "rc_debug_lookup_device": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
     "rc_debug_palette": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
     "rc_debug_struct_sizes": (ctypes.c_int, [ctypes.c_void_p]),
+    "rc_debug_set_option": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int]),
     "rc_debug_detmath": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
 }
 
@@ -234,7 +243,8 @@ def default_proj_plane(width, height):
 
 def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
                  ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
-                 render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None, free_flight=True, leap=True, always_tail=False):
+                 render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None, free_flight=True, leap=True,
+                 always_tail=False, kernel_times=False):
     p = FrameParams()
     p.origin[:] = [float(v) for v in origin]
     p.camera_dir[:] = [float(v) for v in camera_dir]
@@ -255,6 +265,8 @@ def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao
         flags |= RC_F_NO_LEAP
     if always_tail:
         flags |= RC_F_ALWAYS_TAIL
+    if kernel_times:
+        flags |= RC_F_KERNEL_TIMES
     pp = default_proj_plane(width, height) if proj_plane is None else proj_plane
     p.proj_plane[:] = [float(pp[0]), float(pp[1])]
     p.delta_time, p.ao_strength = delta_time, ao_strength
@@ -271,10 +283,23 @@ class RayCaster:
     """The reference host's view of the library: init -> upload_world -> render_frame -> read_image."""
 
     def __init__(self, device=0):
+        """device: a CUDA device index (rc_init), or a list of them (rc_init_multi: one process, one thread, the library
+        deals the bands of every frame to its devices)."""
         self.lib = load_library()
-        _check(self.lib, self.lib.rc_init(device))
-        self.device = device
+        if isinstance(device, (list, tuple)):
+            devs = (ctypes.c_int * len(device))(*[int(d) for d in device])
+            _check(self.lib, self.lib.rc_init_multi(len(device), devs))
+            self.devices = [int(d) for d in device]
+            self.device = self.devices[0]
+        else:
+            _check(self.lib, self.lib.rc_init(device))
+            self.device = device
+            self.devices = [device]
         self._last = None
+
+    def build_id(self):
+        """sha256 of the kernel sources librc.so was compiled from (rc_build_id)."""
+        return self.lib.rc_build_id().decode()
 
     def close(self):
         if self.lib is not None:
@@ -289,6 +314,12 @@ class RayCaster:
 
     def set_stream(self, cuda_stream):
         _check(self.lib, self.lib.rc_set_stream(cuda_stream))
+
+    def set_option(self, name, value):
+        """rc_debug_set_option: "schedule" (int or a key of SCHEDULES), "ao_opts" (AO_OPT_* bits)."""
+        if isinstance(value, str):
+            value = SCHEDULES[value]
+        _check(self.lib, self.lib.rc_debug_set_option(name.encode(), int(value)))
 
     def set_shard(self, rank, world_size):
         _check(self.lib, self.lib.rc_set_shard(rank, world_size))

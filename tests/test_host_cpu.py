@@ -318,3 +318,63 @@ def test_world_blob_round_trip_and_validation(rcmod, world_desc, tmp_path):
         assert e.value.code == -4, name
     with pytest.raises(rcmod.RcError):
         rcmod.load_host(str(tmp_path / "does_not_exist.rcpw"))
+
+
+def test_world_blob_with_a_valid_checksum_but_inconsistent_levels_is_refused(rcmod, tmp_path):
+    """The kernels pick the array a child run is read from by tree LEVEL (fetch_region, world_tops_kernel) or by node kind
+    (lookup): a blob whose checksum is right but whose kinds contradict the levels -- a brick above the brick level, an inner
+    node at it, a header depth that shifts every level -- would send them out of bounds.  load walks the tree from the
+    root and refuses those."""
+    import struct
+
+    from raytracing_test_b200 import voxel_host as vh
+
+    host = vh.World(6)
+    for (x, y, z) in [(5, 5, 5), (70, 3, 9), (300, 40, 2), (301, 40, 2)]:
+        host.put_block(x, y, z, 0x123456, 0, 0.0)
+    host.put_block(64, 64, 64, 0x5, 0, 0.0, 4)  # a 16^3 uniform cell: a LEAF child
+    rcmod.flatten_host(host.describe())
+    path = str(tmp_path / "small.rcpw")
+    rcmod.save_host(path)
+    blob = bytearray(open(path, "rb").read())
+    n_nodes, n_voxels, n_palette = struct.unpack_from("<QQQ", blob, 16)
+    assert rcmod.load_host(path).packed_nodes == n_nodes
+
+    def fnv(data):
+        h = 0xCBF29CE484222325
+        for b in data:
+            h = ((h ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+        return h
+
+    def variant(name, edit):
+        b = bytearray(blob)
+        edit(b)
+        struct.pack_into("<Q", b, 56, fnv(bytes(b[64:])))  # the checksum covers the payload: make it right again
+        out = str(tmp_path / f"{name}.rcpw")
+        open(out, "wb").write(b)
+        return out
+
+    kinds = [struct.unpack_from("<I", blob, 64 + 16 * i + 12)[0] & 0xFF for i in range(n_nodes)]
+    inner = [i for i, k in enumerate(kinds) if k == 0]
+    brick = [i for i, k in enumerate(kinds) if k == 1]
+    assert inner and brick and kinds[0] == 0
+
+    def set_kind(i, k):
+        return lambda b: struct.pack_into("<I", b, 64 + 16 * i + 12, k)
+
+    cases = {
+        "brick_above_brick_level": set_kind(inner[-1], 1),
+        "inner_at_brick_level": set_kind(brick[0], 0),
+        "leaf_root": set_kind(0, 2),
+        "unknown_kind": set_kind(brick[-1], 7),
+        "shallower_header": lambda b: struct.pack_into("<I", b, 12, 5),
+        "deeper_header": lambda b: struct.pack_into("<I", b, 12, 7),
+        "child_run_outside": lambda b: struct.pack_into("<I", b, 64 + 16 * inner[-1] + 8, n_nodes),
+    }
+    for name, edit in cases.items():
+        with pytest.raises(rcmod.RcError) as e:
+            rcmod.load_host(variant(name, edit))
+        assert e.value.code == -4, name
+    # the untouched blob still loads (the variants did not poison anything)
+    assert rcmod.load_host(variant("same", lambda b: None)).packed_nodes == n_nodes
+    host.close()

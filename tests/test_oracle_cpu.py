@@ -183,11 +183,23 @@ def test_det_sin_exp_close_to_libm(ob):
     assert L.oracle_expf(0.0) == 1.0 and L.oracle_sinf(0.0) == 0.0
 
 
-def test_hemisphere_table_kat(ob):
-    # gen_hemisphare_distrib.py with num_pts = 20 prints (x, z, y); first entry as pasted into
-    # light_scattering.frag:134
+def test_hemisphere_table_kat(ob, rcmod):
+    # gen_hemisphare_distrib.py with num_pts = 20 prints (x, z, y); ALL 20 entries as pasted into
+    # light_scattering.frag:133-154 (tests/golden/hemisphere20.json, parsed from the shader by
+    # tools/make_golden_hemisphere.py): the oracle's generator and librc's (rc_hemisphere_table, what the AO kernels use)
+    # must give exactly those numbers after rounding to fp32
+    import json
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "hemisphere20.json")) as f:
+        lit = json.load(f)["literals_x_up_y"]
+    assert len(lit) == 20
+    want20 = np.array([[np.float32(float(x)), np.float32(float(y)), np.float32(float(up))] for x, up, y in lit], dtype=np.float32)
     tab = np.zeros((20, 3), dtype=np.float32)
     ob.oracle_lib().oracle_hemisphere(20, tab.ctypes.data)
+    assert np.array_equal(tab.view(np.uint32), want20.view(np.uint32)), np.argwhere(tab != want20)
+    tab2 = np.zeros((20, 3), dtype=np.float32)
+    assert rcmod.load_library().rc_hemisphere_table(20, tab2.ctypes.data) == 0
+    assert np.array_equal(tab2.view(np.uint32), want20.view(np.uint32)), np.argwhere(tab2 != want20)
     x, y, up = tab[0]
     assert x == np.float32(0.07430756460710652) and up == np.float32(0.97875) and y == np.float32(-0.19111991874778692)
     # the script's formula, evaluated independently in numpy

@@ -19,9 +19,14 @@ with rc.RayCaster(0) as c:
         c.upload_world(vh.World.default().describe())
     else:
         c.generate_world(world, world, 7)
-    p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao, max_steps=max_steps)
+    if "RC_SCHEDULE" in os.environ:  # A/B captures: rc_debug_set_option
+        c.set_option("schedule", int(os.environ["RC_SCHEDULE"]))
+    if "RC_AO_OPTS" in os.environ:
+        c.set_option("ao_opts", int(os.environ["RC_AO_OPTS"]))
+    p = rc.frame_params(w, h, pos, d, sun, shadows=sh, ao_samples=ao, max_steps=max_steps,
+                        kernel_times=bool(int(os.environ.get("RC_KERNEL_TIMES", "0"))))
     for _ in range(frames):
         c.render_frame(p)
         c.sync()
     st = c.stats()
-    print(f"{w}x{h} shadows={sh} ao={ao}: primary {st.primary_ms:.3f} ms ao {st.ao_ms:.3f} ms")
+    print(f"{w}x{h} shadows={sh} ao={ao} schedule {st.schedule}: total {st.total_ms:.3f} ms (primary {st.primary_ms:.3f} ms ao {st.ao_ms:.3f} ms)")
