@@ -493,6 +493,9 @@ def run_b200_arm(args, workload):
 
     def device_ms(render, n):
         """Mean device time of n frames (CUDA events on the launching stream, L2 flushed before each, outside the events)."""
+        for _ in range(2):  # buffers this kind of frame needs (hit records ...) are allocated on first use: not in the timing
+            render()
+        torch.cuda.synchronize(dev)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
         for i in range(n):
             flush.zero_()
@@ -562,8 +565,8 @@ def run_b200_arm(args, workload):
     ms_hits = max_over_ranks(device_ms(lambda: sc.render(params_hits), n_side))
     if world_size == 1 and golden:
         checked.append(("hit records of the timed frame", sha256_of(sc.caster.read_hits()), "hits_sha256"))
-    # (b) per-kernel device times: librc's own events around each kernel (RC_F_KERNEL_TIMES) under the two-kernel schedule;
-    # the default schedule is ONE fused kernel, whose time is the frame's
+    # (b) per-kernel device times: librc's own events around each kernel (RC_F_KERNEL_TIMES; the event between the two
+    # launches is why the timed frames above do not ask for them); a fused schedule (--schedule A/B runs) is ONE kernel
     kern_ms = {}
     names = {v: k for k, v in rc.SCHEDULES.items()}
     tot = []
@@ -571,11 +574,10 @@ def run_b200_arm(args, workload):
         flush.zero_()
         sc.render(params)
         tot.append(sc.stats().total_ms)  # synchronises
-    kern_ms[names[schedule_used]] = float(np.mean(tot))
-    if not args.schedule:
+    kern_ms["frame"] = float(np.mean(tot))
+    if schedule_used < rc.SCHED_FUSED:
         p_kt = rc.frame_params(w, h, pos, d, sun, kernel_times=True, **kw)
         p_kt_tail = rc.frame_params(w, h, pos, d, sun, kernel_times=True, always_tail=True, **kw)
-        sc.caster.set_option("schedule", "two_kernels")
         k_primary, k_ao, k_tail = [], [], []
         for _ in range(n_side):
             flush.zero_()
@@ -587,10 +589,9 @@ def run_b200_arm(args, workload):
             flush.zero_()
             sc.render(p_kt_tail)
             k_tail.append(sc.stats().primary_ms)
-        kern_ms["two_kernels_primary"] = float(np.mean(k_primary))
-        kern_ms["two_kernels_ao"] = float(np.mean(k_ao))
-        kern_ms["two_kernels_primary_with_free_flight_tail"] = float(np.mean(k_tail))
-        sc.caster.set_option("schedule", schedule_used)
+        kern_ms["primary"] = float(np.mean(k_primary))
+        kern_ms["ao"] = float(np.mean(k_ao))
+        kern_ms["primary_with_free_flight_tail"] = float(np.mean(k_tail))
         sc.render(params)
     barrier()
 
@@ -769,11 +770,13 @@ def run_b200_arm(args, workload):
         fused = schedule_used >= rc.SCHED_FUSED
         per_kernel = {}
         if fused:
-            per_kernel["primary_kernel"] = (sum(ab), kern_ms[names[schedule_used]],
+            per_kernel["primary_kernel"] = (sum(ab), kern_ms["frame"],
                                             "one fused launch: primary + shadow + AO rays (schedule %s)" % names[schedule_used])
-        if "two_kernels_primary" in kern_ms:
-            per_kernel["two_kernels/primary_kernel"] = (ab[0] + ab[1], kern_ms["two_kernels_primary"], "A/B schedule: primary + shadow rays")
-            per_kernel["two_kernels/ao_window_kernel"] = (ab[2], kern_ms["two_kernels_ao"], "A/B schedule: AO rays over the seed list")
+        else:
+            ao_name = "ao_window_persistent_kernel" if schedule_used == rc.SCHED_AO_PERSISTENT else "ao_window_kernel"
+            per_kernel["primary_kernel"] = (ab[0] + ab[1], kern_ms["primary"], "primary + shadow rays, shading, AO seeds")
+            if ao:
+                per_kernel[ao_name] = (ab[2], kern_ms["ao"], "AO rays over the seed list (ao_steps = 5: dense-window kernel)")
         for name, (bytes_, ms, what) in per_kernel.items():
             if ms > 0:
                 ach = bytes_ / (ms * 1e-3) / 1e9
@@ -791,14 +794,15 @@ def run_b200_arm(args, workload):
                                         "capture": rec.get("source"), "ncu_issue_active_pct": rec.get("ncu_issue_active_pct")}
                     if not stale:
                         r["issue_slots"]["frac"] = inst / (r["ms"] * 1e-3) / slots_per_s
-        dom = "primary_kernel" if "primary_kernel" in roof_all else (max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None)
+        dom = max(roof_all, key=lambda k: roof_all[k]["ms"]) if roof_all else None
         if dom:
             rec = records.get(dom, {})
             traffic = rec.get("dram_bytes_per_launch")
             # what the launch cannot avoid moving: the packed world once (upper bound on the part of it the rays touch), the
             # RGBA8 frame out, and -- two-kernel schedules only -- the AO seed list written and read back (48 B per hit pixel)
-            seeds = 0 if fused else 2 * 48 * int(st.hit_pixels)
-            compulsory = (int(info.packed_bytes) + w * h * 4 // world_size + seeds)
+            seeds = 0 if fused else 48 * int(st.hit_pixels)  # written by the primary kernel, read by the AO kernel
+            compulsory = int(info.packed_bytes) + seeds + (w * h * 4 // world_size if (fused or dom == "primary_kernel") else
+                                                           4 * int(st.hit_pixels))
             roof = {"bound": "hbm", "kernel": dom, "schedule": names[schedule_used], "achieved": roof_all[dom]["achieved"], "peak": peak,
                     "unit": "GB/s", "frac": roof_all[dom]["frac"],
                     # the capture is of one GPU rendering the whole frame; a rank of N renders 1/N of its bands
@@ -812,8 +816,9 @@ def run_b200_arm(args, workload):
                             "4 B per child index, counted by the oracle); the kernel's region caching avoids most of them, so "
                             "frac exceeds 1 and says how far the design is from the reference's traffic, not how close to the "
                             "HBM limit; traffic = DRAM bytes of one launch from the ncu capture in profiles/ (null when that "
-                            "capture is of other kernel sources than the librc.so that ran); compulsory_bytes = packed world + "
-                            "this rank's share of the frame (+ seed list)"}
+                            "capture is of other kernel sources than the librc.so that ran); compulsory_bytes = what this launch "
+                            "cannot avoid moving: the packed world once (upper bound), the AO seed list (48 B per hit pixel, "
+                            "two-kernel schedules) and the pixels it stores"}
     if strong is not None:
         strong["tN_ms"] = ms_per_step
         strong["n_gpus"] = world_size

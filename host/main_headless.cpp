@@ -7,7 +7,7 @@
 // voxel.  INTEGRATION.md shows the same loop as a patch to the real src/main.cpp.
 //
 //   rc_headless [--frames N] [--size WxH] [--ao S] [--out prefix] [--edit] [--gpu-pick] [--gen-device] [--device D] [--gpus N]
-//               [--still] [--dump-last FILE]
+//               [--devices a,b,c] [--still] [--dump-last FILE]
 //
 // --gpus N: rc_init_multi over devices D .. D+N-1 -- the same loop, one process, one thread; the library deals the bands of
 // every frame to its devices and rc_read_image lands each device's bands in the (page-locked) host frame.
@@ -53,7 +53,7 @@ static void cameraDirFor(double rotationX, double rotationY, float out[3]) {
 int main(int argc, char** argv) {
     int frames = 16, width = 1920, height = 1080, ao = 64, device = 0, gpus = 1;
     bool edit = false, gpuPick = false, genDevice = false, still = false;
-    std::string out, dumpLast;
+    std::string out, dumpLast, deviceList;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() { return i + 1 < argc ? argv[++i] : ""; };
@@ -63,6 +63,7 @@ int main(int argc, char** argv) {
         else if (a == "--out") out = next();
         else if (a == "--device") device = atoi(next());
         else if (a == "--gpus") gpus = atoi(next());
+        else if (a == "--devices") deviceList = next();  // e.g. 0,2,3 (instead of --device D --gpus N)
         else if (a == "--still") still = true;
         else if (a == "--dump-last") dumpLast = next();
         else if (a == "--edit") edit = true;
@@ -75,9 +76,18 @@ int main(int argc, char** argv) {
         }
     }
 
-    if (gpus > 1) {  // createWindow(); setupOpenGl();                                src/main.cpp:176-179
+    if (gpus > 1 || !deviceList.empty()) {  // createWindow(); setupOpenGl();         src/main.cpp:176-179
         std::vector<int> devices;
-        for (int i = 0; i < gpus; i++) devices.push_back(device + i);
+        if (deviceList.empty()) {
+            for (int i = 0; i < gpus; i++) devices.push_back(device + i);
+        } else {
+            for (const char* p = deviceList.c_str(); *p;) {
+                devices.push_back(atoi(p));
+                while (*p && *p != ',') p++;
+                if (*p == ',') p++;
+            }
+            gpus = (int)devices.size();
+        }
         check(rc_init_multi(gpus, devices.data()), "rc_init_multi");
     } else {
         check(rc_init(device), "rc_init");

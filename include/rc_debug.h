@@ -48,8 +48,9 @@ int rc_debug_load_host(const char* path, rc_world_info* info);
 
 /* Scheduling / specialisation switches for A/B measurements and parity tests; every setting renders the same pixels.
  *   "schedule": 0 primary kernel + AO kernel, 1 primary kernel + persistent AO grid (atomic chunk cursor, programmatic
- *               dependent launch), 2 one fused kernel (default), 3 persistent fused kernel over a global atomic queue of
- *               Morton-ordered 8x4 tiles, 4 the same with the top tree levels staged in shared memory
+ *               dependent launch), 2 one fused kernel, 3 persistent fused kernel over a global atomic queue of
+ *               Morton-ordered 8x4 tiles, 4 the same with the top tree levels staged in shared memory, 5 (default): 0 or 1,
+ *               whichever is faster for the frame's size
  *   "ao_opts" : bit 0 empty sample octants skipped (default 1) */
 int rc_debug_set_option(const char* name, int value);
 

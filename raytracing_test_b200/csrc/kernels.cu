@@ -503,6 +503,12 @@ __device__ __forceinline__ int sky_gate_distance(const FrameArgs& A, int x, int 
     return d;
 }
 
+// The copy of the frame statistics this CTA adds to (FrameCounterBlock: spread over lines so that the atomics of 65 k warps
+// do not queue on one).
+__device__ __forceinline__ FrameCounters& counter_slot(const FrameArgs& A) {
+    return A.counters->slot[(blockIdx.x + 13u * blockIdx.y) & (COUNTER_SLOTS - 1u)];
+}
+
 struct PixelResult {
     F3 color;
     rc_hit hit;
@@ -718,7 +724,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
             // same comparisons, same additions (nextIntersectDDA, low_res.frag:446-491); nothing else per step
             {
                 const unsigned m = __activemask();
-                if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&A.counters->free_flight_rays, (unsigned)__popc(m));
+                if ((int)(threadIdx.x & 31u) == __ffs(m) - 1) atomicAdd(&counter_slot(A).free_flight_rays, (unsigned)__popc(m));
             }
             if (A.sky_tail) {
                 // free_flight.h: most of the remaining steps in closed form, the last few walked; the voxel the ray ends in
@@ -1013,7 +1019,7 @@ __global__ void __launch_bounds__(AO_THREADS) ao_cached_kernel(const __grid_cons
     __shared__ uint32_t sBase[AO_SLOTS][AO_THREADS];
     __shared__ uint2 sMask[AO_SLOTS][AO_THREADS];
 
-    const uint32_t nSeeds = A.counters->ao_seed_count;
+    const uint32_t nSeeds = A.counters->seed_cursor.next;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= nSeeds) return;
     const uint32_t tid = threadIdx.x;
@@ -1576,7 +1582,7 @@ __device__ __forceinline__ void trace_tile(const FrameArgs& A, uint32_t px, uint
         s.face_sign = (uint32_t)R.hit.face | (sneg ? 0u : 4u);
         s.frame_pixel = frame_pixel_of(A, px, localRow);
         if (FUSED) {
-            if ((int)lane == leader) atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
+            if ((int)lane == leader) atomicAdd(&counter_slot(A).ao_seed_count, (unsigned)__popc(seedMask));
             // lanes without a hit pixel walk along with the first seeded lane's
             const AoSeed sh = shuffle_seed(s, leader);
             if (!seed) s = sh;
@@ -1584,7 +1590,7 @@ __device__ __forceinline__ void trace_tile(const FrameArgs& A, uint32_t px, uint
         } else {
             // warp-aggregated append
             unsigned base = 0;
-            if ((int)lane == leader) base = atomicAdd(&A.counters->ao_seed_count, (unsigned)__popc(seedMask));
+            if ((int)lane == leader) base = atomicAdd(&A.counters->seed_cursor.next, (unsigned)__popc(seedMask));
             base = __shfl_sync(0xffffffffu, base, leader);
             if (seed) {
                 const uint32_t at = base + __popc(seedMask & ((1u << lane) - 1u));
@@ -1603,10 +1609,11 @@ __device__ __forceinline__ void trace_tile(const FrameArgs& A, uint32_t px, uint
     unsigned stepSum = active ? (unsigned)R.hit.steps : 0u;
     for (int o = 16; o > 0; o >>= 1) stepSum += __shfl_xor_sync(0xffffffffu, stepSum, o);
     if (lane == 0) {
-        if (tracedMask) atomicAdd(&A.counters->primary_rays, (unsigned long long)__popc(tracedMask));
-        if (shadowMask) atomicAdd(&A.counters->shadow_rays, (unsigned long long)__popc(shadowMask));
-        if (hitMask) atomicAdd(&A.counters->hit_pixels, (unsigned long long)__popc(hitMask));
-        if (stepSum) atomicAdd(&A.counters->primary_steps, (unsigned long long)stepSum);
+        FrameCounters& fc = counter_slot(A);
+        if (tracedMask) atomicAdd(&fc.primary_rays, (unsigned long long)__popc(tracedMask));
+        if (shadowMask) atomicAdd(&fc.shadow_rays, (unsigned long long)__popc(shadowMask));
+        if (hitMask) atomicAdd(&fc.hit_pixels, (unsigned long long)__popc(hitMask));
+        if (stepSum) atomicAdd(&fc.primary_steps, (unsigned long long)stepSum);
     }
 }
 
@@ -1665,11 +1672,11 @@ __global__ void __launch_bounds__(32 * PERSISTENT_WARPS, RC_PRIMARY_MIN_BLOCKS) 
     const uint32_t nTiles = supersX * supersY * 64u;
     // the next tile is claimed while the current one is traced: the atomic's round trip never shows
     uint32_t next = 0u;
-    if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor, 1u);
+    if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor.next, 1u);
     for (;;) {
         const uint32_t t = __shfl_sync(0xffffffffu, next, 0);
         if (t >= nTiles) break;
-        if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor, 1u);
+        if (lane == 0u) next = atomicAdd(&A.counters->tile_cursor.next, 1u);
         const uint32_t sup = t >> 6, m = t & 63u;
         // Morton: even bits of m -> x, odd bits -> y
         const uint32_t mx = (m & 1u) | ((m >> 1) & 2u) | ((m >> 2) & 4u), my = ((m >> 1) & 1u) | ((m >> 2) & 2u) | ((m >> 3) & 4u);
@@ -1686,7 +1693,7 @@ __global__ void __launch_bounds__(32 * PERSISTENT_WARPS, RC_PRIMARY_MIN_BLOCKS) 
 #endif
 __global__ void __launch_bounds__(AO_THREADS, RC_AO_MIN_BLOCKS) ao_window_kernel(const __grid_constant__ FrameArgs A) {
     extern __shared__ __align__(16) uint32_t smem[];
-    const uint32_t nSeeds = A.counters->ao_seed_count;
+    const uint32_t nSeeds = A.counters->seed_cursor.next;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t warp = threadIdx.x >> 5;
     if ((t & ~31u) >= nSeeds) return;  // whole warp beyond the list
@@ -1703,14 +1710,14 @@ __global__ void __launch_bounds__(AO_THREADS, RC_AO_MIN_BLOCKS) ao_window_persis
     extern __shared__ __align__(16) uint32_t smem[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const uint32_t nSeeds = *(volatile const unsigned int*)&A.counters->ao_seed_count;
+    const uint32_t nSeeds = *(volatile const unsigned int*)&A.counters->seed_cursor.next;
     const uint32_t nChunks = (nSeeds + 31u) / 32u;
     uint32_t next = 0u;
-    if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor, 1u);
+    if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor.next, 1u);
     for (;;) {
         const uint32_t c = __shfl_sync(0xffffffffu, next, 0);
         if (c >= nChunks) break;
-        if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor, 1u);
+        if (lane == 0u) next = atomicAdd(&A.counters->ao_cursor.next, 1u);
         const uint32_t t = c * 32u + lane;
         const bool valid = t < nSeeds;
         const AoSeed s = A.ao_seeds[valid ? t : nSeeds - 1u];
@@ -1995,7 +2002,8 @@ cudaError_t launch_frame(const FrameArgs& args, uint32_t schedule, int numSms, c
     // with a brick cache (ao_cached_kernel)
     const bool window = ao && args.ao_table && args.p.ao_steps == AOW_STEPS;
     const bool fusable = !ao || window;
-    if (schedule >= SCHED_COUNT) schedule = SCHED_TWO_KERNELS;
+    if (schedule >= SCHED_COUNT)  // SCHED_AUTO
+        schedule = (uint64_t)args.local_rows * args.p.width >= (4u << 20) ? SCHED_AO_PERSISTENT : SCHED_TWO_KERNELS;
     if (schedule >= SCHED_FUSED && !fusable) schedule = SCHED_TWO_KERNELS;
     if (schedule == SCHED_AO_PERSISTENT && !window) schedule = SCHED_TWO_KERNELS;
     *scheduleUsed = schedule;
@@ -2026,7 +2034,8 @@ cudaError_t launch_frame(const FrameArgs& args, uint32_t schedule, int numSms, c
         ++*launches;
         return cudaGetLastError();
     }
-    primary_kernel<false><<<grid, 32 * RC_PRIMARY_WARPS, 0, stream>>>(args);
+    if ((e = allow_smem(primary_kernel<false>, args.debug_primary_smem)) != cudaSuccess) return e;
+    primary_kernel<false><<<grid, 32 * RC_PRIMARY_WARPS, args.debug_primary_smem, stream>>>(args);
     ++*launches;
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (midEvent && (e = cudaEventRecord(midEvent, stream)) != cudaSuccess) return e;

@@ -34,15 +34,28 @@ struct AoSeed {
     uint32_t frame_pixel; // index into the whole frame (py * width + px)
 };
 
-struct FrameCounters {
+// Frame statistics and work-queue cursors.  Every warp adds to the statistics, so they are spread over COUNTER_SLOTS
+// copies, each on a 128-byte line of its own (one L2 line taking 300 k atomics per frame serialises them; the host adds the
+// copies up).  The seed-list cursor and the two queue cursors return values the warps wait for: they sit on lines nothing
+// else touches (slot 0's ao_seed_count is THE seed-list cursor of the two-kernel schedules; fused frames count their
+// seeds per slot).
+struct alignas(128) FrameCounters {
     unsigned long long primary_rays;
     unsigned long long shadow_rays;
     unsigned long long hit_pixels;
     unsigned long long primary_steps;
     unsigned int ao_seed_count;
-    unsigned int tile_cursor;  // persistent primary kernel: next 8x4-pixel tile (global atomic work queue)
     unsigned int free_flight_rays;  // primary rays that ended in the free-flight loop
-    unsigned int ao_cursor;    // persistent AO kernel: next 32-seed chunk (global atomic work queue)
+};
+struct alignas(128) QueueCursor {
+    unsigned int next;
+};
+constexpr uint32_t COUNTER_SLOTS = 64;
+struct FrameCounterBlock {
+    QueueCursor seed_cursor;   // two-kernel schedules: next free entry of the AO seed list = seeds appended
+    QueueCursor tile_cursor;   // persistent frame kernel: next 8x4-pixel tile (global atomic work queue)
+    QueueCursor ao_cursor;     // persistent AO kernel: next 32-seed chunk (global atomic work queue)
+    FrameCounters slot[COUNTER_SLOTS];
 };
 
 struct FrameArgs {
@@ -71,11 +84,13 @@ struct FrameArgs {
     float4* rgba32f;         // optional
     rc_hit* hits;            // optional
     AoSeed* ao_seeds;        // optional (ao_samples > 0)
-    FrameCounters* counters;
+    FrameCounterBlock* counters;
     const void* ao_table;    // AoDir[6][RC_MAX_AO_SAMPLES] of the window AO code (device), set by launch_primary / launch_ao
     uint32_t ao_opts;        // AO_OPT_*
     // the sun's ray (low_res.frag:373: buildRay(sunDir)) is the same for every pixel: 1 / sunDir, IEEE fp32, divided once on the host
     float sun_inv[3];
+    uint32_t debug_primary_smem;  // A/B probe (rc_debug_set_option "primary_smem"): dynamic shared memory the non-fused primary
+                                  // kernel is launched with although it uses none -- shows what the fused kernels' smaller L1 costs
 };
 
 // Pieces of the window AO code that can be switched off for A/B measurements and tests (same results either way).
@@ -91,9 +106,13 @@ enum FrameSchedule : uint32_t {
                                // (no seed list, no second launch)
     SCHED_PERSISTENT = 3,      // SCHED_FUSED as persistent warps over a global atomic queue of Morton-ordered 8x4 tiles
     SCHED_PERSISTENT_STAGED = 4, // SCHED_PERSISTENT with the top tree levels (DeviceWorld::n_top nodes) staged in shared memory
-    SCHED_COUNT
+    SCHED_COUNT,
+    // default: the two-kernel schedules, whichever is faster for the frame's size (measured, DESIGN section 4: below ~4 M
+    // pixels per device the one-CTA-per-128-seeds AO grid, above it the persistent AO grid; the fused kernels lose to both --
+    // their code outgrows the instruction cache once warps of one SM are in different phases)
+    SCHED_AUTO = SCHED_COUNT
 };
-constexpr uint32_t SCHED_DEFAULT = SCHED_FUSED;
+constexpr uint32_t SCHED_DEFAULT = SCHED_AUTO;
 
 // Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory of the current device and the oriented
 // table of the window AO code into *table (device memory, allocated on first use; pass it on as FrameArgs::ao_table).

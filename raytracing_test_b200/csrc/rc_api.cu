@@ -69,13 +69,13 @@ struct Context {
     rc_hit* dHits = nullptr;
     AoSeed* dSeeds = nullptr;
     size_t f32Capacity = 0, hitCapacity = 0, seedCapacity = 0;
-    FrameCounters* dCounters = nullptr;
+    FrameCounterBlock* dCounters = nullptr;
     // sky gates (kernels.h, FrameArgs::sky_gate): column-block tops of the current world, the gate table built from them
     int* dSkyTops = nullptr;
     uint4* dSkyGate = nullptr;
     int skyShift = 0;
     uint32_t skyGateSteps = 0xFFFFFFFFu;  // max_steps the table on the device was built for (none)
-    FrameCounters* hCounters = nullptr;  // pinned
+    FrameCounterBlock* hCounters = nullptr;  // pinned
     int* dPick = nullptr;
     int* hPick = nullptr;  // pinned
 
@@ -89,7 +89,7 @@ struct Context {
     uint32_t launches = 0;
     int numSms = 0;
     // how frames are scheduled on the device / which AO specialisations run (rc_debug_set_option; same pixels either way)
-    uint32_t schedule = SCHED_DEFAULT, scheduleUsed = SCHED_DEFAULT, aoOpts = AO_OPT_DEFAULT;
+    uint32_t schedule = SCHED_DEFAULT, scheduleUsed = SCHED_DEFAULT, aoOpts = AO_OPT_DEFAULT, debugPrimarySmem = 0;
     cudaEvent_t evStart = nullptr, evPrimary = nullptr, evEnd = nullptr;
 
     // rc_init_multi: this device may store into device 0's memory (peer access enabled), its frame target pointers are
@@ -227,9 +227,9 @@ static int one_init(int device) {
     g.numSms = prop.multiProcessorCount;
     CUDA_TRY(cudaStreamCreateWithFlags(&g.ownStream, cudaStreamNonBlocking));
     g.stream = g.ownStream;
-    CUDA_TRY(cudaMalloc((void**)&g.dCounters, sizeof(FrameCounters)));
-    CUDA_TRY(cudaMallocHost((void**)&g.hCounters, sizeof(FrameCounters)));
-    memset(g.hCounters, 0, sizeof(FrameCounters));
+    CUDA_TRY(cudaMalloc((void**)&g.dCounters, sizeof(FrameCounterBlock)));
+    CUDA_TRY(cudaMallocHost((void**)&g.hCounters, sizeof(FrameCounterBlock)));
+    memset(g.hCounters, 0, sizeof(FrameCounterBlock));
     CUDA_TRY(cudaEventCreate(&g.evStart));
     CUDA_TRY(cudaEventCreate(&g.evPrimary));
     CUDA_TRY(cudaEventCreate(&g.evEnd));
@@ -767,17 +767,18 @@ static int one_render_frame(const rc_frame_params* params) {
     a.counters = g.dCounters;
     a.ao_table = p.ao_samples > 0 ? g.aoTable : nullptr;
     a.ao_opts = g.aoOpts;
+    a.debug_primary_smem = g.debugPrimarySmem;
     for (int k = 0; k < 3; k++) a.sun_inv[k] = 1.0f / p.sun_dir[k];  // IEEE fp32, as buildRay(sunDir) divides (low_res.frag:67)
 
     // per-kernel times need an event between the two launches, which also keeps the AO grid from becoming resident
     // while the primary grid drains: only on request
     const bool kernelTimes = (p.flags & RC_F_KERNEL_TIMES) != 0;
     g.launches = 0;
-    CUDA_TRY(cudaMemsetAsync(g.dCounters, 0, sizeof(FrameCounters), g.stream));
+    CUDA_TRY(cudaMemsetAsync(g.dCounters, 0, sizeof(FrameCounterBlock), g.stream));
     CUDA_TRY(cudaEventRecord(g.evStart, g.stream));
     CUDA_TRY(launch_frame(a, g.schedule, g.numSms, kernelTimes ? g.evPrimary : nullptr, g.stream, &g.launches, &g.scheduleUsed));
     CUDA_TRY(cudaEventRecord(g.evEnd, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(g.hCounters, g.dCounters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.hCounters, g.dCounters, sizeof(FrameCounterBlock), cudaMemcpyDeviceToHost, g.stream));
 
     g.frame = p;
     g.localRows = localRows;
@@ -968,13 +969,18 @@ static int one_frame_stats_get(rc_frame_stats* out) {
     if (!out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_stats_get: null out");
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     memset(out, 0, sizeof(*out));
-    out->primary_rays = g.hCounters->primary_rays;
-    out->shadow_rays = g.hCounters->shadow_rays;
-    out->hit_pixels = g.hCounters->hit_pixels;
-    out->ao_rays = (uint64_t)g.hCounters->ao_seed_count * g.frame.ao_samples;
-    out->primary_steps = g.hCounters->primary_steps;
+    uint64_t seeds = g.hCounters->seed_cursor.next;  // two-kernel schedules: the seed list's length
+    for (uint32_t k = 0; k < COUNTER_SLOTS; k++) {
+        const FrameCounters& c = g.hCounters->slot[k];
+        out->primary_rays += c.primary_rays;
+        out->shadow_rays += c.shadow_rays;
+        out->hit_pixels += c.hit_pixels;
+        out->primary_steps += c.primary_steps;
+        out->free_flight_rays += c.free_flight_rays;
+        seeds += c.ao_seed_count;  // fused schedules count their seeds here
+    }
+    out->ao_rays = seeds * g.frame.ao_samples;
     out->kernel_launches = g.launches;
-    out->free_flight_rays = g.hCounters->free_flight_rays;
     float ms = 0.f;
     if (g.frameHasKernelTimes) {
         if (cudaEventElapsedTime(&ms, g.evStart, g.evPrimary) == cudaSuccess) out->primary_ms = ms;
@@ -1193,16 +1199,19 @@ int rc_debug_load_host(const char* path, rc_world_info* info) {
 
 // Scheduling / specialisation switches for A/B measurements and parity tests (every setting renders the same pixels):
 //   "schedule"  0 two kernels, 1 persistent AO grid + programmatic dependent launch, 2 fused, 3 persistent fused,
-//               4 persistent fused with the top tree levels staged in shared memory
+//               4 persistent fused with the top tree levels staged in shared memory, 5 (default) 0 or 1 by frame size
 //   "ao_opts"   bit 0: AO sample groups whose octant of reachable voxels is empty are not cast
 static int one_debug_set_option(const char* name, int value) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_set_option: call rc_init first");
     if (!name) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: null name");
     if (!strcmp(name, "schedule")) {
-        if (value < 0 || value >= (int)SCHED_COUNT) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: schedule %d", value);
+        if (value < 0 || value > (int)SCHED_AUTO) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: schedule %d", value);
         g.schedule = (uint32_t)value;
     } else if (!strcmp(name, "ao_opts")) {
         g.aoOpts = (uint32_t)value & AO_OPT_DEFAULT;
+    } else if (!strcmp(name, "primary_smem")) {  // A/B probe: see FrameArgs::debug_primary_smem
+        if (value < 0 || value > 200 * 1024) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: primary_smem %d", value);
+        g.debugPrimarySmem = (uint32_t)value;
     } else {
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: unknown option %s", name);
     }

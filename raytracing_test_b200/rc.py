@@ -16,8 +16,8 @@ LIB_PATH = os.environ.get("RC_LIBRC") or os.path.join(PKG_DIR, "librc.so")  # RC
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F, RC_F_NO_FREE_FLIGHT, RC_F_NO_LEAP, RC_F_ALWAYS_TAIL = 1, 2, 4, 8, 16, 32, 64
 RC_F_KERNEL_TIMES = 128
 # rc_debug_set_option("schedule", ...): how a frame is scheduled on the device (csrc/kernels.h FrameSchedule)
-SCHED_TWO_KERNELS, SCHED_AO_PERSISTENT, SCHED_FUSED, SCHED_PERSISTENT, SCHED_PERSISTENT_STAGED = range(5)
-SCHEDULES = {"two_kernels": 0, "ao_persistent": 1, "fused": 2, "persistent": 3, "persistent_staged": 4}
+SCHED_TWO_KERNELS, SCHED_AO_PERSISTENT, SCHED_FUSED, SCHED_PERSISTENT, SCHED_PERSISTENT_STAGED, SCHED_AUTO = range(6)
+SCHEDULES = {"two_kernels": 0, "ao_persistent": 1, "fused": 2, "persistent": 3, "persistent_staged": 4, "auto": 5}
 AO_OPT_OCTANT = 1
 RC_RGBA8, RC_RGBA32F = 0, 1
 RC_IPC_HANDLE_BYTES = 64

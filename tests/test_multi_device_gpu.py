@@ -44,14 +44,14 @@ def test_headless_cpp_host_on_several_gpus_renders_the_config5_golden(tmp_path):
     if not os.path.exists(exe):
         pytest.skip("host/rc_headless not built")
     n = 2
-    _devices(n)
+    devs = ",".join(str(v) for v in _devices(n))  # "0,1", or "0,0" on a one-GPU box (RC_ALLOW_DUPLICATE_DEVICES)
     env = dict(os.environ)
     with open(os.path.join(ROOT, "tests", "golden", "frames_big.json")) as f:
         want = json.load(f)["cases"]["config5_8k_ao64"]["rgba8_sha256"]
     got = {}
     for gpus in (1, n):
         out = str(tmp_path / f"frame_{gpus}.rgba")
-        r = subprocess.run([exe, "--gpus", str(gpus), "--frames", "2", "--size", "7680x4320", "--ao", "64", "--still", "--dump-last", out],
+        r = subprocess.run([exe] + (["--devices", devs] if gpus > 1 else []) + ["--frames", "2", "--size", "7680x4320", "--ao", "64", "--still", "--dump-last", out],
                            capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         got[gpus] = hashlib.sha256(open(out, "rb").read()).hexdigest()
@@ -61,7 +61,7 @@ def test_headless_cpp_host_on_several_gpus_renders_the_config5_golden(tmp_path):
     ppm = {}
     for gpus in (1, n):
         prefix = str(tmp_path / f"edit{gpus}_")
-        r = subprocess.run([exe, "--gpus", str(gpus), "--frames", "24", "--size", "640x360", "--ao", "16", "--edit", "--out", prefix],
+        r = subprocess.run([exe] + (["--devices", devs] if gpus > 1 else []) + ["--frames", "24", "--size", "640x360", "--ao", "16", "--edit", "--out", prefix],
                            capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         assert "click at frame" in r.stdout

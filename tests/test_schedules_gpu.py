@@ -22,7 +22,7 @@ def _render(rcmod, caster, w, h, pos, d, sun, **kw):
 @pytest.fixture()
 def restore_options(rcmod, caster):
     yield
-    caster.set_option("schedule", rcmod.SCHED_FUSED)
+    caster.set_option("schedule", rcmod.SCHED_AUTO)
     caster.set_option("ao_opts", rcmod.AO_OPT_OCTANT)
 
 

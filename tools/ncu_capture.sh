@@ -10,6 +10,7 @@ FRAME=${5:-"1920 1080 1 64 4"}   # arguments of tools/profile_frame.py (config 4
 OUT=gpurun_out
 mkdir -p $OUT
 python tools/profile_frame.py $FRAME > $OUT/${TAG}_plain.log 2>&1
+python -c "import sys; sys.path.insert(0, '.'); from raytracing_test_b200 import rc; print(rc.load_library().rc_build_id().decode())" > $OUT/${TAG}_build_id.txt
 ncu --set full --clock-control none --import-source on -k "regex:$KRE" --launch-skip $SKIP --launch-count $COUNT \
     -o $OUT/${TAG} -f python tools/profile_frame.py $FRAME > $OUT/${TAG}_ncu.log 2>&1
 ncu -i $OUT/${TAG}.ncu-rep --page raw --csv > $OUT/${TAG}_raw.csv
