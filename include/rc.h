@@ -109,6 +109,9 @@ typedef struct rc_frame_params {
 #define RC_F_NO_LEAP   0x20u /* tests / measurements: the free-flight loop walks every step instead of leaping over most of
                                 them in closed form (same frame, same hit records either way) */
 
+#define RC_F_NO_COLUMN_REGIONS 0x100u /* tests / measurements: primary rays above the highest voxel of their 16 x 16 column block
+                                         look the empty space up in the tree, cell by cell, instead of taking the whole column
+                                         above the terrain as one empty region (same frame, same hit records either way) */
 #define RC_F_KERNEL_TIMES 0x80u /* measurements: also time the primary and the AO kernel separately (rc_frame_stats.primary_ms /
                                    ao_ms).  The event between the two launches keeps the AO grid from becoming resident while
                                    the primary grid drains, and a fused frame (one kernel) has no such split: without this flag

@@ -436,6 +436,30 @@ __device__ __forceinline__ void enter_region(const DeviceWorld& W, Cursor& c, Re
     fetch_region(W, c, wrap_coord(W, p.x), wrap_coord(W, p.y), wrap_coord(W, p.z), g.r);
 }
 
+// Loop A's region entry: the column above the terrain as one empty region when the ray is above its column block's top
+// (FrameArgs::col_tops), else the tree.  colNy = steps along y before the ray leaves that region (down: to the top; up: to
+// the edge of the torus), 0 = a tree region.  Raw coordinates must be on the torus (negative ones go through the
+// reference's Morton quirk, wrap_coord: the tree decides there).
+__device__ __forceinline__ void enter_region_a(const FrameArgs& A, Cursor& c, RegionAt& g, const Pos& p, int sy, int& colNy) {
+    const DeviceWorld& W = A.world;
+    colNy = 0;
+    if (A.col_tops && (uint32_t)p.x <= W.wrap && (uint32_t)p.y <= W.wrap && (uint32_t)p.z <= W.wrap) {
+        const int top = __ldg(&A.col_tops[(((uint32_t)p.z >> A.sky_shift) * SKY_GRID) + ((uint32_t)p.x >> A.sky_shift)]);
+        if (p.y > top) {
+            g.x = p.x;
+            g.y = p.y;
+            g.z = p.z;
+            g.r.mask = 0ull;
+            g.r.base = 0u;
+            g.r.info = 0u;
+            g.r.shift = A.sky_shift;  // extent along x and z; along y: colNy
+            colNy = sy > 0 ? (int)W.wrap + 1 - p.y : p.y - top;
+            return;
+        }
+    }
+    enter_region(W, c, g, p);
+}
+
 // After a lookup: refresh the countdown. A solid voxel forces a lookup on the next step.
 __device__ __forceinline__ void after_lookup(CellCount& n, const Ray& r, const Pos& p, uint32_t word, int cellShift) {
     if (word == 0u) {
@@ -592,7 +616,8 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
 
     // :299-307
     RegionAt rg;
-    enter_region(W, cur, rg, pos);
+    int colNy;  // > 0: rg is the column above the terrain (enter_region_a), this many steps along y left in it
+    enter_region_a(A, cur, rg, pos, ray.sy, colNy);
     uint32_t word = 0u;
     {
         const int idx = brick_bit(pos.x, pos.y, pos.z);
@@ -646,6 +671,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 // work on the half-rate ALU pipe.  All values are small integers: exact in fp32.
                 CellCount n;
                 count_cell(n, ray, pos, rg.r.shift);
+                if (colNy) n.ny = colNy;  // a column region: its extent along y is not the aligned cell's
                 // a big cell that reaches above the gate: the countdown stops where the ray rises above it, the region is
                 // entered again there and the test above fires (4^3 cells keep their full count: the sibling walk below
                 // relies on it)
@@ -659,7 +685,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 // (no descent, no count_cell, no position recovery) -- five of a ray's nine region changes are of this kind.
                 // The cell's coordinates in the node (0..3) are kept biased by 4 in byte fields: a step out of the node shows
                 // up as a 3 or an 8 in its field and never borrows from the next one.
-                const bool walk = rg.r.shift == 2;
+                const bool walk = rg.r.shift == 2 && colNy == 0;
                 const uint32_t cell0 = 0x040404u + (uint32_t)((pos.x >> 2) & 3) + ((uint32_t)((pos.y >> 2) & 3) << 8) +
                                        ((uint32_t)((pos.z >> 2) & 3) << 16);
                 uint32_t cell = cell0;
@@ -701,7 +727,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 pos.z += ray.sz * (n.nz - (int)fnz) + 4 * ((int)((cell >> 16) & 0xFFu) - (int)((cell0 >> 16) & 0xFFu));
                 steps += (uint32_t)(rem0 - rem);
                 if (outOfSteps) break;
-                enter_region(W, cur, rg, pos);
+                enter_region_a(A, cur, rg, pos, ray.sy, colNy);
             } else {
                 // Brick (or uniform solid cell): step until the ray leaves it, enters an occupied voxel or runs out of
                 // steps -- all inside this one pass of the outer loop, so that a lane walking a brick does not make the
@@ -712,7 +738,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                     steps++;
                     leftBrick = left_region(rg, pos);
                 } while (!leftBrick && !((rg.r.mask >> brick_bit(pos.x, pos.y, pos.z)) & 1ull) && steps < numSteps);
-                if (leftBrick) enter_region(W, cur, rg, pos);
+                if (leftBrick) enter_region_a(A, cur, rg, pos, ray.sy, colNy);
             }
             if (rg.r.mask != 0ull) {
                 const int idx = brick_bit(pos.x, pos.y, pos.z);

@@ -74,6 +74,11 @@ struct FrameArgs {
     // tree too shallow).
     const uint4* sky_gate;
     int sky_shift;
+    // Column regions (primary loop A).  col_tops[bz][bx] = highest occupied y of column block (bx, bz) (-1: none), the same
+    // table the gates are built from.  Everything above it is empty: a ray above its block's top walks the whole
+    // 2^sky_shift x 2^sky_shift column -- down to the top, up to the edge of the torus -- as ONE empty region, found with
+    // one load instead of a tree descent.  Null: off (RC_F_NO_COLUMN_REGIONS, tree too shallow).
+    const int* col_tops;
     uint32_t sky_tail;       // 1: a free ray's final voxel / last face are needed (hit records, position debug output, or the
                              // looked-at voxel lies exactly max_steps steps from the camera's); 0: nobody can see them
     uint32_t shadow_gate;    // the table also covers the shadow rays' reach (shadow_steps <= max_steps, flags allow it)

@@ -753,6 +753,11 @@ static int one_render_frame(const rc_frame_params* params) {
             a.sky_tail = ((p.flags & (RC_F_HITS | RC_F_ALWAYS_TAIL)) || p.render_pos_data != 0 || manhattan == (long long)p.max_steps) ? 1u : 0u;
         }
     }
+    // column regions need the tops table (a tree deep enough for the column grid); the torus edge is checked per ray
+    if (!(p.flags & RC_F_NO_COLUMN_REGIONS) && g.skyShift >= 2 && g.dSkyTops) {
+        a.col_tops = g.dSkyTops;
+        a.sky_shift = g.skyShift;
+    }
     a.local_rows = localRows;
     a.n_local_bands = localBands;
     a.rgba8 = g.dRgba8;

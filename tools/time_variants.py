@@ -65,6 +65,10 @@ for smem in (0, 12 * 1024, 25 * 1024):
     _, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True)
     print(f"two kernels, primary kernel launched with {smem} B of (unused) dynamic shared memory: primary {pr:.4f} ms")
 c.set_option("primary_smem", 0)
+_, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True, column_regions=False)
+print(f"two kernels, column regions off: primary {pr:.4f} ms")
+_, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True, column_regions=True)
+print(f"two kernels, column regions on : primary {pr:.4f} ms")
 med, mn, _, _, rays, _ = run(rc.SCHED_FUSED, 1, always_tail=True)
 print(f"fused, free-flight tail forced: {med:.4f} ms")
 med, mn, _, _, rays, _ = run(rc.SCHED_FUSED, 1, hits=True)
