@@ -63,13 +63,6 @@ __device__ __forceinline__ float glsl_max(float a, float b) { return a < b ? b :
 __device__ __forceinline__ float glsl_clamp(float x, float lo, float hi) { return glsl_min(glsl_max(x, lo), hi); }
 
 __device__ __forceinline__ float dot3(F3 a, F3 b) { return FADD(FADD(FMUL(a.x, b.x), FMUL(a.y, b.y)), FMUL(a.z, b.z)); }
-__device__ __forceinline__ F3 cross3(F3 a, F3 b) {
-    F3 r;
-    r.x = FSUB(FMUL(a.y, b.z), FMUL(b.y, a.z));
-    r.y = FSUB(FMUL(a.z, b.x), FMUL(b.z, a.x));
-    r.z = FSUB(FMUL(a.x, b.y), FMUL(b.x, a.y));
-    return r;
-}
 __device__ __forceinline__ F3 scale3(F3 a, float s) { return F3{FMUL(a.x, s), FMUL(a.y, s), FMUL(a.z, s)}; }
 __device__ __forceinline__ F3 add3(F3 a, F3 b) { return F3{FADD(a.x, b.x), FADD(a.y, b.y), FADD(a.z, b.z)}; }
 __device__ __forceinline__ F3 normalize3(F3 v) { return scale3(v, FDIV(1.0f, FSQRT(dot3(v, v)))); }
@@ -454,6 +447,9 @@ __device__ __forceinline__ void enter_region_a(const FrameArgs& A, Cursor& c, Re
             g.r.info = 0u;
             g.r.shift = A.sky_shift;  // extent along x and z; along y: colNy
             colNy = sy > 0 ? (int)W.wrap + 1 - p.y : p.y - top;
+#ifdef RC_MUTATE_COLUMN  // mutation check of tests/test_sky_gates_random_gpu.py (tools/mutation_check.sh): one step too many
+            if (sy <= 0) colNy++;
+#endif
             return;
         }
     }
@@ -518,7 +514,11 @@ __device__ __forceinline__ int sky_gate_distance(const FrameArgs& A, int x, int 
     const uint32_t q = (sxNeg ? 1u : 0u) | (szNeg ? 2u : 0u);
     const uint4 g = __ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)z >> A.sky_shift)) * SKY_GRID + ((uint32_t)x >> A.sky_shift)]);
     const float slope = merge ? fminf(fmaxf(FMUL(fminf(adx, adz), fabsf(dy)), 0.0f), 16.0f) * (float)(1 << A.sky_shift) : 0.0f;
+#ifdef RC_MUTATE_GATE  // mutation check (tools/mutation_check.sh): credit the climb without the slack for phases / rounding
+    const int y1 = y + 1 + 3;
+#else
     const int y1 = y + 1;
+#endif
     int d = y1 - (int)(g.x & 0xFFFFu);
     d = min(d, y1 + max(__float2int_rd(slope) - 3, 0) - (int)(g.x >> 16));
     d = min(d, y1 + max(__float2int_rd(slope * 3.0f) - 3, 0) - (int)(g.y & 0xFFFFu));
@@ -588,9 +588,11 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     const F3 sun = F3{P.sun_dir[0], P.sun_dir[1], P.sun_dir[2]};
 
     // :279-285
-    const F3 left = cross3(camDir, F3{0.0f, 1.0f, 0.0f});
+    // left = cross(cameraDir, (0,1,0)), up = cross(cameraDir, left): the same for every pixel, from the host (FrameArgs)
+    const F3 left = F3{A.cam_left[0], A.cam_left[1], A.cam_left[2]};
+    const F3 camUp = F3{A.cam_up[0], A.cam_up[1], A.cam_up[2]};
     const F3 t1 = scale3(left, -FMUL(P.proj_plane[0], FSUB(fcx, 0.5f)));
-    const F3 t2 = scale3(scale3(cross3(camDir, left), FADD(-fcy, 0.5f)), P.proj_plane[1]);
+    const F3 t2 = scale3(scale3(camUp, FADD(-fcy, 0.5f)), P.proj_plane[1]);
     const F3 dir = normalize3(add3(add3(camDir, t1), t2));
 
     // :275,288-296

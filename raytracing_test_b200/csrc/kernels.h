@@ -94,6 +94,9 @@ struct FrameArgs {
     uint32_t ao_opts;        // AO_OPT_*
     // the sun's ray (low_res.frag:373: buildRay(sunDir)) is the same for every pixel: 1 / sunDir, IEEE fp32, divided once on the host
     float sun_inv[3];
+    // camera basis (low_res.frag:279-283), the same for every pixel: left = cross(cameraDir, (0,1,0)) (not normalised),
+    // up = cross(cameraDir, left); computed once on the host with the same single-rounded fp32 operations
+    float cam_left[3], cam_up[3];
     uint32_t debug_primary_smem;  // A/B probe (rc_debug_set_option "primary_smem"): dynamic shared memory the non-fused primary
                                   // kernel is launched with although it uses none -- shows what the fused kernels' smaller L1 costs
 };

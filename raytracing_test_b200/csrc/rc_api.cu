@@ -774,6 +774,19 @@ static int one_render_frame(const rc_frame_params* params) {
     a.ao_opts = g.aoOpts;
     a.debug_primary_smem = g.debugPrimarySmem;
     for (int k = 0; k < 3; k++) a.sun_inv[k] = 1.0f / p.sun_dir[k];  // IEEE fp32, as buildRay(sunDir) divides (low_res.frag:67)
+    {
+        // cross products of low_res.frag:279-283, one rounded operation at a time (this file is compiled with
+        // -ffp-contract=off: no fused multiply-add), exactly as the kernel's cross3 would per pixel
+        auto cross = [](const float* u, const float* v, float* r) {
+            volatile float m0 = u[1] * v[2], m1 = v[1] * u[2], m2 = u[2] * v[0], m3 = v[2] * u[0], m4 = u[0] * v[1], m5 = v[0] * u[1];
+            r[0] = m0 - m1;
+            r[1] = m2 - m3;
+            r[2] = m4 - m5;
+        };
+        const float yAxis[3] = {0.0f, 1.0f, 0.0f};
+        cross(p.camera_dir, yAxis, a.cam_left);
+        cross(p.camera_dir, a.cam_left, a.cam_up);
+    }
 
     // per-kernel times need an event between the two launches, which also keeps the AO grid from becoming resident
     // while the primary grid drains: only on request

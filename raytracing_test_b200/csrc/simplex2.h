@@ -1,6 +1,12 @@
 // simplex2.h -- 2-D OpenSimplex noise, shared by the host stand-in (voxel_host.cpp, plain C++) and the
 // device world generator (worldgen.cu): one source, so the doubles agree bit for bit on both sides
 // (no FMA contraction on either: -ffp-contract=off / -fmad=false).
+//
+// This file IS on a product path (rc_generate_world): it restates KdotJPG's public 2-D OpenSimplex with the
+// reference's constants and expression order (include/OpenSimplexNoise.cpp, lines cited below) because the generated
+// world has to equal genWorld()'s voxel for voxel, which needs identical doubles (tests/test_host_cpu.py::
+// test_simplex_noise_bit_exact).  It is a compact re-expression, not a copy: one lattice walk instead of the vendored
+// file's unrolled case tree.
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -45,14 +51,6 @@ struct Simplex2 {
         const signed char g[16] = {5, 2, 2, 5, -5, 2, -2, 5, 5, -2, 2, -5, -5, -2, -2, -5};
         const int idx = perm[(perm[xsb & 0xFF] + ysb) & 0xFF] & 0x0E;
         return g[idx] * dx + g[idx + 1] * dy;
-    }
-
-    // One lattice vertex: (2 - dx^2 - dy^2)^4 * gradient, or 0 outside its kernel.
-    RC_HD double vertex(int xsb, int ysb, double dx, double dy) const {
-        double attn = 2 - dx * dx - dy * dy;
-        if (!(attn > 0)) return 0.0;
-        attn *= attn;
-        return attn * attn * gradient(xsb, ysb, dx, dy);
     }
 
     RC_HD double eval(double x, double y) const {

@@ -15,12 +15,17 @@ pos, d, sun = vh.default_camera()
 c = rc.RayCaster(0)
 c.upload_world(host.describe())
 w, h = 1920, 1080
+c.set_option("schedule", 0)
 p = rc.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=0, hits=True, rgba32f=True)
 for _ in range(3):
     c.render_frame(p)
+hits = c.read_hits().reshape(h, w)
+if len(sys.argv) > 1 and sys.argv[1] == "notail":  # the product frame: no hit records, free-flight rays skip their tail
+    p = rc.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=0, rgba32f=True)
+    for _ in range(3):
+        c.render_frame(p)
 f4 = c.read_image(fmt=rc.RC_RGBA32F).reshape(h, w, 4).astype(np.float64)
 f = f4[:, :, 3]
-hits = c.read_hits().reshape(h, w)
 # one value per warp tile (8 wide, 4 high)
 tile = f.reshape(h // 4, 4, w // 8, 8).max(axis=(1, 3))
 kind = hits["kind"].reshape(h // 4, 4, w // 8, 8)
