@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--cpu-baseline-only", action="store_true",
                     help="internal: print the cpu_baseline object of --workload as JSON and exit (the default arm runs this leg in a "
                          "subprocess, so that the process that drives the GPU never maps an oracle library)")
+    ap.add_argument("--completion-signal", dest="signal", choices=["flags", "allreduce"], default="flags",
+                    help="N>1, direct frame: how 'frame complete' crosses the processes (flags in rank 0's memory, or the "
+                         "one-element NCCL all-reduce they replaced)")
     ap.add_argument("--schedule", default=None, choices=["two_kernels", "ao_persistent", "fused", "persistent", "persistent_staged"],
                     help="A/B runs: how librc schedules a frame on the device (default: the library's default)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
@@ -466,7 +469,7 @@ def run_b200_arm(args, workload):
     pos, d, sun = vh.default_camera()
     look = tuple(int(v) for v in host.pick(pos, d, 30)[0])  # src/main.cpp:81: the host's picking ray feeds lookingAtBlock
 
-    sc = fg.ShardedRayCaster(local_rank, rank, world_size, mode=args.frame_path)
+    sc = fg.ShardedRayCaster(local_rank, rank, world_size, mode=args.frame_path, signal=args.signal)
     if args.schedule:
         sc.caster.set_option("schedule", args.schedule)
     info = sc.upload_world(host.describe())
@@ -738,6 +741,7 @@ def run_b200_arm(args, workload):
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     build_id = sc.caster.build_id()
+    sync_timeouts = sc.caster.frame_sync_timeouts() if (rank == 0 and getattr(sc, "_sync_open", False)) else 0
     if rank != 0:
         sc.close()
         if world_size > 1:
@@ -859,6 +863,8 @@ def run_b200_arm(args, workload):
     print(json.dumps(line), flush=True)
     if parity and parity["mismatched"]:
         raise SystemExit(f"bench.py: parity_check failed: {parity['mismatched']}")
+    if sync_timeouts:
+        raise SystemExit(f"bench.py: {sync_timeouts} frame-completion waits gave up (rc_frame_sync_timeouts): a rank never signalled")
 
 
 def main():

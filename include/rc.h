@@ -304,6 +304,29 @@ int rc_frame_target_close(void);
 void* rc_frame_target_device(uint32_t slot); /* owner only: the frame, bottom row first */
 int rc_frame_target_last_slot(void);         /* slot the last rc_render_frame wrote, -1 = none */
 
+/* Frame completion across processes without a collective per frame.  With a frame target every process's kernels store into
+ * the owner's frame; what is left is telling the owner's stream that a frame is complete, and the peers' streams that a
+ * frame slot may be written again.  The owner allocates a block of flags next to the frame (rc_frame_sync_create, one more
+ * CUDA IPC handle), the peers map it (rc_frame_sync_open).  Frames are counted from 0 per sync block, the same on every
+ * process.  For frame f:
+ *   peer : rc_frame_sync_begin()  (its stream waits until the owner has allowed frame f)  -> rc_render_frame ->
+ *          rc_frame_sync_end()    (a flag store behind its kernels: "rank r has finished frame f")
+ *   owner: rc_frame_sync_allow(f + 1, stream) as soon as the slot frame f + 1 will use is free, queued on the stream that
+ *          frees it (behind the read-back of the frame that was there; NULL = the library's stream);
+ *          rc_render_frame -> rc_frame_sync_end() (its stream waits for every peer's flag: the frame is complete from there)
+ * The waits are one-warp kernels polling LOCAL memory on the owner and one word of the owner's memory on the peers, with a
+ * back-off; a wait that sees nothing for ~2 s gives up (rc_frame_sync_timeouts) instead of hanging the device.  Replaces the
+ * one-element NCCL all-reduce used as the completion signal (~50 us per frame at 8 GPUs).  rc_init_multi does not need it
+ * (one process: CUDA events). */
+int rc_frame_sync_create(void* handle_out);       /* RC_IPC_HANDLE_BYTES */
+int rc_frame_sync_open(const void* handle);
+int rc_frame_sync_close(void);
+int rc_frame_sync_begin(void);
+int rc_frame_sync_allow(uint32_t frame, void* cuda_stream);
+int rc_frame_sync_end(void);
+uint32_t rc_frame_sync_frames(void);              /* frames ended so far = the index of the next one */
+int rc_frame_sync_timeouts(uint32_t* out);
+
 /* The last frame (RC_RGBA8) as a binary PPM, top row first: the headless stand-in for looking at
  * the window. Synchronises like rc_read_image. Sharded frames: this rank's rows, others black. */
 int rc_write_ppm(const char* path);

@@ -1930,6 +1930,28 @@ __global__ void __launch_bounds__(128) sky_gate_kernel(const int* __restrict__ t
     gates[t] = make_uint4(g[0] | (g[1] << 16), g[2] | (g[3] << 16), g[4], 0u);
 }
 
+// rc_frame_sync_*: see kernels.h
+__global__ void sync_signal_kernel(uint32_t* flag, uint32_t value) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        __threadfence_system();  // this device's earlier stores (its pixels in the owner's frame) before the flag
+        atomicMax_system(flag, value);  // flags only grow: signals from two streams may arrive in either order
+    }
+}
+__global__ void sync_wait_kernel(const volatile uint32_t* flags, uint32_t strideWords, uint32_t count, uint32_t value, uint32_t* timedOut) {
+    if (blockIdx.x == 0 && threadIdx.x < count) {
+        const volatile uint32_t* f = flags + (size_t)threadIdx.x * strideWords;
+        const long long t0 = clock64();
+        while ((int)(*f - value) < 0) {
+            __nanosleep(200);
+            if (clock64() - t0 > 4000000000ll) {  // ~2 s at 2 GHz: a peer died or the protocol broke -- do not hang the device
+                atomicAdd(timedOut, 1u);
+                break;
+            }
+        }
+    }
+    __threadfence_system();
+}
+
 __global__ void lookup_kernel(DeviceWorld W, const int* xyz, uint32_t n, uint32_t* outWords, int* outShift) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -2133,6 +2155,19 @@ cudaError_t launch_world_tops(const DeviceWorld& world, int skyShift, int* tops,
 
 cudaError_t launch_sky_gates(const int* tops, int skyShift, uint32_t maxSteps, uint4* gates, cudaStream_t stream) {
     sky_gate_kernel<<<4 * SKY_GRID * SKY_GRID / 128, 128, 0, stream>>>(tops, skyShift, maxSteps, gates);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sync_signal(uint32_t* flag, uint32_t value, cudaStream_t stream) {
+    sync_signal_kernel<<<1, 32, 0, stream>>>(flag, value);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sync_wait(const uint32_t* flags, uint32_t strideWords, uint32_t count, uint32_t value, uint32_t* timedOut,
+                             cudaStream_t stream) {
+    if (count == 0) return cudaSuccess;
+    if (count > 64) return cudaErrorInvalidValue;
+    sync_wait_kernel<<<1, 64, 0, stream>>>(flags, strideWords, count, value, timedOut);
     return cudaGetLastError();
 }
 

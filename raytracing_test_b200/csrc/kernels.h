@@ -149,6 +149,14 @@ cudaError_t launch_world_tops(const DeviceWorld& world, int sky_shift, int* tops
 // tops -> the gate table of FrameArgs::sky_gate for a step budget (4 * SKY_GRID * SKY_GRID entries of 16 bytes).
 cudaError_t launch_sky_gates(const int* tops, int sky_shift, uint32_t max_steps, uint4* gates, cudaStream_t stream);
 
+// Cross-process frame completion without a collective (rc_frame_sync_*): flags in the frame owner's memory.
+// signal: *flag = max(*flag, value), after everything queued before it on the stream (system-scope fence).
+// wait: lanes 0 .. count-1 each spin on flags[lane * stride_words] until it has reached `value` (wrap-safe compare), with
+// a back-off; gives up after ~2 s and raises *timed_out instead of hanging the device.
+cudaError_t launch_sync_signal(uint32_t* flag, uint32_t value, cudaStream_t stream);
+cudaError_t launch_sync_wait(const uint32_t* flags, uint32_t stride_words, uint32_t count, uint32_t value, uint32_t* timed_out,
+                             cudaStream_t stream);
+
 // Single-voxel lookups through the same device code path the kernels use (tests).
 cudaError_t launch_lookup(const DeviceWorld& world, const int* xyz, uint32_t n, uint32_t* out_words, int* out_shift,
                           cudaStream_t stream);

@@ -63,6 +63,14 @@ struct Context {
         uint32_t seq = 0;
         int lastSlot = -1;
     } target;
+    // rc_frame_sync_*: completion flags in the frame owner's memory (one process per GPU, no collective per frame).
+    // Layout (uint32 words, 32 words = 128 bytes per flag): [0] go = frames the peers may start, [32 * (1 + r)] done[r] = frames
+    // rank r has finished storing, [32 * 65] timed-out waits
+    struct FrameSync {
+        uint32_t* block = nullptr;
+        bool owner = false;
+        uint32_t frames = 0;  // frames begun through rc_frame_sync_begin / end
+    } fsync;
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evRendered = nullptr;
     float4* dRgba32f = nullptr;
@@ -158,6 +166,16 @@ void freeFrameBuffers() {
     g.haveFrame = false;
 }
 
+constexpr uint32_t SYNC_FLAG_WORDS = 32, SYNC_MAX_RANKS = 64, SYNC_BLOCK_WORDS = SYNC_FLAG_WORDS * (SYNC_MAX_RANKS + 2);
+
+void closeFrameSync() {
+    if (g.fsync.block) {
+        if (g.fsync.owner) cudaFree(g.fsync.block);
+        else cudaIpcCloseMemHandle(g.fsync.block);
+    }
+    g.fsync = Context::FrameSync();
+}
+
 void closeFrameTarget() {
     for (int i = 0; i < 2; i++) {
         if (!g.target.ptr[i]) continue;
@@ -249,6 +267,7 @@ static void one_shutdown(void) {
     freeWorld();
     freeFrameBuffers();
     closeFrameTarget();
+    closeFrameSync();
     release_hemisphere(g.aoTable);
     g.aoTable = nullptr;
     if (g.dCounters) cudaFree(g.dCounters);
@@ -1441,6 +1460,96 @@ int rc_frame_target_open(uint32_t width, uint32_t height, uint32_t slots, const 
     if (nContexts > 1)
         return fail(RC_ERR_UNSUPPORTED, "rc_frame_target_open: with rc_init_multi the frame target lives on the library's device 0");
     return one_frame_target_open(width, height, slots, handles);
+}
+
+// ---- rc_frame_sync_*: frame completion across processes without a collective ------------------------------------------
+int rc_frame_sync_create(void* handle_out) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_create: call rc_init first");
+    if (nContexts > 1) return fail(RC_ERR_UNSUPPORTED, "rc_frame_sync_create: rc_init_multi orders its devices with events");
+    if (!handle_out) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_sync_create: null handle");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameSync();
+    CUDA_TRY(cudaMalloc((void**)&g.fsync.block, SYNC_BLOCK_WORDS * 4));
+    g.fsync.owner = true;
+    CUDA_TRY(cudaMemset(g.fsync.block, 0, SYNC_BLOCK_WORDS * 4));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, g.fsync.block));
+    memcpy(handle_out, &h, sizeof(h));
+    return RC_OK;
+}
+
+int rc_frame_sync_open(const void* handle) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_open: call rc_init first");
+    if (nContexts > 1) return fail(RC_ERR_UNSUPPORTED, "rc_frame_sync_open: rc_init_multi orders its devices with events");
+    if (!handle) return fail(RC_ERR_INVALID_ARGUMENT, "rc_frame_sync_open: null handle");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameSync();
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return fail(RC_ERR_CUDA, "rc_frame_sync_open: cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+    g.fsync.block = (uint32_t*)p;
+    g.fsync.owner = false;
+    return RC_OK;
+}
+
+int rc_frame_sync_close(void) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_close: call rc_init first");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    closeFrameSync();
+    return RC_OK;
+}
+
+// Frame f (0, 1, 2 ... counted per sync block) of a peer may start storing into the owner's frame target once the owner
+// has allowed it: its slot is free again (whatever read the frame that was there before has finished).
+//   peer : rc_frame_sync_begin()  -- its stream waits for go >= f          -> rc_render_frame -> rc_frame_sync_end()
+//   owner: rc_frame_sync_allow(f + 1, stream) whenever slot (f + 1) % slots is known to be free, on the stream that frees it
+//          (the copy stream behind a read-back, or its own stream when nothing reads that slot); rc_render_frame ->
+//          rc_frame_sync_end()  -- its stream waits for done[r] >= f + 1 of every peer: the frame is complete from there on.
+int rc_frame_sync_begin(void) {
+    if (!g.initialized || !g.fsync.block) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_begin: no sync block (rc_frame_sync_create / open)");
+    CUDA_TRY(cudaSetDevice(g.device));
+    if (!g.fsync.owner)
+        CUDA_TRY(launch_sync_wait(g.fsync.block, SYNC_FLAG_WORDS, 1, g.fsync.frames, g.fsync.block + SYNC_FLAG_WORDS * (SYNC_MAX_RANKS + 1), g.stream));
+    return RC_OK;
+}
+
+int rc_frame_sync_allow(uint32_t frame, void* cuda_stream) {
+    if (!g.initialized || !g.fsync.block || !g.fsync.owner) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_allow: not the owner of a sync block");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(launch_sync_signal(g.fsync.block, frame, cuda_stream ? (cudaStream_t)cuda_stream : g.stream));
+    return RC_OK;
+}
+
+int rc_frame_sync_end(void) {
+    if (!g.initialized || !g.fsync.block) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_end: no sync block (rc_frame_sync_create / open)");
+    if (g.worldSize > SYNC_MAX_RANKS) return fail(RC_ERR_UNSUPPORTED, "rc_frame_sync_end: more than %u ranks", SYNC_MAX_RANKS);
+    CUDA_TRY(cudaSetDevice(g.device));
+    const uint32_t done = g.fsync.frames + 1u;
+    if (g.fsync.owner) {
+        if (g.worldSize > 1)
+            CUDA_TRY(launch_sync_wait(g.fsync.block + SYNC_FLAG_WORDS * 2, SYNC_FLAG_WORDS, g.worldSize - 1, done,
+                                      g.fsync.block + SYNC_FLAG_WORDS * (SYNC_MAX_RANKS + 1), g.stream));
+    } else {
+        CUDA_TRY(launch_sync_signal(g.fsync.block + SYNC_FLAG_WORDS * (1 + g.rank), done, g.stream));
+    }
+    g.fsync.frames = done;
+    return RC_OK;
+}
+
+uint32_t rc_frame_sync_frames(void) { return g.initialized ? g.fsync.frames : 0u; }
+
+// Owner: waits that gave up (a peer that never signalled) since rc_frame_sync_create; synchronises the stream.
+int rc_frame_sync_timeouts(uint32_t* out) {
+    if (!g.initialized || !g.fsync.block || !out) return fail(RC_ERR_NOT_INITIALIZED, "rc_frame_sync_timeouts: no sync block");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    CUDA_TRY(cudaMemcpy(out, g.fsync.block + SYNC_FLAG_WORDS * (SYNC_MAX_RANKS + 1), 4, cudaMemcpyDeviceToHost));
+    return RC_OK;
 }
 
 int rc_frame_target_close(void) {

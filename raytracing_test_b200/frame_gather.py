@@ -5,8 +5,11 @@ rank holds the whole flattened world and renders the 16-row bands with band % wo
   direct (default on CUDA): rank 0 owns the whole frame (rc_frame_target_create), the other ranks
       map it through CUDA IPC (rc_frame_target_open) and every rank's kernels store each finished
       pixel straight into it over NVLink peer memory -- the transfer is fused into the tracing
-      kernels, there is no gather and no compose pass.  The only collective is a one-element
-      all-reduce after the kernels: the cross-process "frame complete" signal on the streams.
+      kernels, there is no gather and no compose pass.  "Frame complete" crosses the processes as
+      flags in rank 0's memory (rc_frame_sync_*: one store behind each peer's kernels, one polling
+      warp on rank 0's stream, and the other way round for "this frame slot may be written again");
+      no collective per frame (signal="allreduce": the one-element NCCL all-reduce this replaces,
+      kept for A/B and as the fall-back when the flag block cannot be mapped).
   gather: the compact band buffers are gathered to rank 0 over NCCL and de-interleaved by one
       librc kernel (rc_compose_frame).  Kept as the comparison baseline and for hosts without
       peer access.
@@ -70,10 +73,15 @@ class ShardedRayCaster:
     """rc.RayCaster for one rank of a one-process-per-GPU job. All ranks call render(); rank 0's
     frame() returns the composed RGBA8 frame as a device tensor [height, width, 4]."""
 
-    def __init__(self, device_index, rank=None, world_size=None, group=None, mode="direct", slots=2):
+    def __init__(self, device_index, rank=None, world_size=None, group=None, mode="direct", slots=2, signal="flags"):
         if mode not in ("direct", "gather"):
             raise ValueError("mode must be 'direct' or 'gather'")
+        if signal not in ("flags", "allreduce"):
+            raise ValueError("signal must be 'flags' or 'allreduce'")
         self.mode = mode
+        self.signal = signal
+        self._sync_open = False
+        self._allowed_by_copy = set()  # frames whose slot is released by a read-back in flight (rank 0, signal "flags")
         self.slots = slots
         self.group = group
         self.rank = dist.get_rank(group) if rank is None else rank
@@ -93,7 +101,7 @@ class ShardedRayCaster:
         self._target_open = False
         self._copy_stream = None
         self._pending = {}  # frame slot -> event of the read-back still reading it (rank 0)
-        self.completion_signal = "one-element NCCL all-reduce behind the kernels as the completion signal"
+        self.completion_signal = "not sharded"
 
     def close(self):
         if self._target_open:
@@ -108,9 +116,42 @@ class ShardedRayCaster:
     def _close_target(self):
         # nobody may unmap / free while a peer's kernels can still write
         self._meet()
+        if self._sync_open:
+            self.caster.frame_sync_close()
+            self._sync_open = False
         self.caster.frame_target_close()
         self._frames = None
         self._target_open = False
+        self._pending.clear()
+        self._allowed_by_copy.clear()
+
+    def _open_sync(self):
+        """Rank 0 allocates the completion flags, everyone else maps them; all ranks end up with the same answer."""
+        box = [None]
+        if self.rank == 0:
+            try:
+                box[0] = self.caster.frame_sync_create()
+            except rc.RcError as e:
+                box[0] = e
+        dist.broadcast_object_list(box, src=0, group=self.group)
+        ok = torch.ones(1, dtype=torch.int32, device=self.device)
+        if isinstance(box[0], Exception):
+            ok.zero_()
+        elif self.rank != 0:
+            try:
+                self.caster.frame_sync_open(box[0])
+            except rc.RcError:
+                ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        torch.cuda.synchronize(self.device)
+        if int(ok.item()) == 0:
+            try:
+                self.caster.frame_sync_close()
+            except rc.RcError:
+                pass
+            return False
+        self._sync_open = True
+        return True
 
     def _open_target(self, w, h):
         """Rank 0 allocates the frame(s), everyone else maps them (CUDA IPC handles travel as bytes)."""
@@ -151,7 +192,13 @@ class ShardedRayCaster:
                 print(f"frame_gather: direct frame unavailable ({self.fallback_reason}); using the NCCL gather path", file=sys.stderr)
             return False
         self._target_open = True
-        self._meet()  # every peer has the frame mapped before anyone renders into it
+        if self.signal == "flags" and not self._open_sync():
+            self.signal = "allreduce"
+        self.completion_signal = (
+            "frame completion by per-rank flags in rank 0's memory (rc_frame_sync_*: a store behind each peer's kernels, one "
+            "polling warp on rank 0's stream), no collective per frame" if self.signal == "flags" else
+            "one-element NCCL all-reduce behind the kernels as the completion signal")
+        self._meet()  # every peer has the frame (and the flags) mapped before anyone renders into it
         return True
 
     def upload_world(self, desc):
@@ -169,11 +216,36 @@ class ShardedRayCaster:
         if direct and self._dims != (w, h):
             direct = self._open_target(w, h)
             self._dims = (w, h) if direct else None
+        flags = direct and self._sync_open
+        if flags:
+            # frame f of this sync block goes into slot f % slots (target and flags were created together)
+            f = self.caster.frame_sync_frames()
+            if self.rank == 0:
+                # rank 0's own kernels overwrite that slot too: the read-back that last used it must be done
+                ev = self._pending.pop(f % self.slots, None)
+                if ev is not None:
+                    torch.cuda.current_stream(self.device).wait_event(ev)
+                # the peers may start frame f + 1 as soon as ITS slot is free: now, unless a read-back still uses it (then
+                # the copy stream says so when that copy is done, read_frame_async)
+                if (f + 1) in self._allowed_by_copy:
+                    self._allowed_by_copy.discard(f + 1)
+                else:
+                    self.caster.frame_sync_allow(f + 1)
+            else:
+                self.caster.frame_sync_begin()
         self.caster.render_frame(params)
         pr = padded_rows(h, self.world)
         local = device_bytes(self.caster.device_image_ptr(rc.RC_RGBA8), pr * w * 4, self.device)
         if self.world == 1:
             self._frame = local[: h * w * 4].view(h, w, 4)
+            return
+        if flags:
+            slot = self.caster.frame_target_last_slot()
+            self.caster.frame_sync_end()
+            if self.rank == 0:
+                self._frame = self._frames[slot]
+                self._slot = slot
+                self._frame_index = f
             return
         if direct:
             # frame complete on rank 0 <=> every rank's kernels have finished: a one-element all-reduce queued
@@ -222,6 +294,11 @@ class ShardedRayCaster:
         done = torch.cuda.Event()
         done.record(self._copy_stream)
         self._pending[self._slot] = done
+        if self._sync_open:
+            # this slot is free again once the copy has left it: the copy stream tells the peers so
+            nxt = self._frame_index + self.slots
+            self.caster.frame_sync_allow(nxt, self._copy_stream.cuda_stream)
+            self._allowed_by_copy.add(nxt)
         return done
 
     def stats(self):

@@ -154,6 +154,14 @@ ABI = {
     "rc_frame_target_close": (ctypes.c_int, []),
     "rc_frame_target_device": (ctypes.c_void_p, [ctypes.c_uint32]),
     "rc_frame_target_last_slot": (ctypes.c_int, []),
+    "rc_frame_sync_create": (ctypes.c_int, [ctypes.c_void_p]),
+    "rc_frame_sync_open": (ctypes.c_int, [ctypes.c_void_p]),
+    "rc_frame_sync_close": (ctypes.c_int, []),
+    "rc_frame_sync_begin": (ctypes.c_int, []),
+    "rc_frame_sync_allow": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
+    "rc_frame_sync_end": (ctypes.c_int, []),
+    "rc_frame_sync_frames": (ctypes.c_uint32, []),
+    "rc_frame_sync_timeouts": (ctypes.c_int, [ctypes.c_void_p]),
     "rc_read_hits": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
     "rc_sync": (ctypes.c_int, []),
     "rc_frame_stats_get": (ctypes.c_int, [ctypes.POINTER(FrameStats)]),
@@ -380,6 +388,34 @@ class RayCaster:
 
     def frame_target_ptr(self, slot):
         return self.lib.rc_frame_target_device(slot)
+
+    def frame_sync_create(self):
+        h = ctypes.create_string_buffer(RC_IPC_HANDLE_BYTES)
+        _check(self.lib, self.lib.rc_frame_sync_create(h))
+        return h.raw
+
+    def frame_sync_open(self, handle):
+        _check(self.lib, self.lib.rc_frame_sync_open(ctypes.create_string_buffer(bytes(handle), RC_IPC_HANDLE_BYTES)))
+
+    def frame_sync_close(self):
+        _check(self.lib, self.lib.rc_frame_sync_close())
+
+    def frame_sync_begin(self):
+        _check(self.lib, self.lib.rc_frame_sync_begin())
+
+    def frame_sync_allow(self, frame, cuda_stream=None):
+        _check(self.lib, self.lib.rc_frame_sync_allow(int(frame), cuda_stream))
+
+    def frame_sync_end(self):
+        _check(self.lib, self.lib.rc_frame_sync_end())
+
+    def frame_sync_frames(self):
+        return int(self.lib.rc_frame_sync_frames())
+
+    def frame_sync_timeouts(self):
+        n = ctypes.c_uint32(0)
+        _check(self.lib, self.lib.rc_frame_sync_timeouts(ctypes.byref(n)))
+        return int(n.value)
 
     def frame_target_last_slot(self):
         return self.lib.rc_frame_target_last_slot()

@@ -66,6 +66,11 @@ def main():
         prev[0].synchronize()
         landed.append((prev[2], prev[1].numpy().copy()))
     torch.cuda.synchronize()
+    # the frames above were signalled complete by flags in rank 0's memory (rc_frame_sync_*), no collective per frame; no
+    # wait gave up
+    assert direct.signal == "flags", "flag block could not be mapped: the all-reduce fall-back ran instead"
+    if rank == 0:
+        assert direct.caster.frame_sync_timeouts() == 0
 
     # host delivery with no device-side gather: every rank reads its own bands back into ONE shared page-locked
     # host frame; rank 0 sees each frame complete and intact
@@ -93,6 +98,25 @@ def main():
     assert rank != 0 or host_ok == len(yaws)
     sink.close()
     direct.close()
+
+    # the completion signal this replaced (one-element NCCL all-reduce per frame): same frames, pipelined read-back included
+    ar = fg.ShardedRayCaster(local, rank, world, mode="direct", signal="allreduce")
+    ar.upload_world(host.describe())
+    w, h = 1280, 720
+    prev = None
+    for i, yaw in enumerate(yaws):
+        ar.render(rc.frame_params(w, h, pos, camera_dir(yaw, 15.0), sun, shadows=True, ao_samples=16))
+        ev = ar.read_frame_async(pinned[i & 1])
+        if prev is not None and rank == 0:
+            prev[0].synchronize()
+            assert np.array_equal(prev[1].numpy(), alone[(1280, 720, prev[2])]), f"all-reduce signal: pipelined frame (yaw {prev[2]}) differs"
+        prev = (ev, pinned[i & 1], yaw)
+    if rank == 0:
+        prev[0].synchronize()
+        assert np.array_equal(prev[1].numpy(), alone[(1280, 720, prev[2])])
+    torch.cuda.synchronize()
+    assert ar.signal == "allreduce"
+    ar.close()
 
     gather = fg.ShardedRayCaster(local, rank, world, mode="gather")
     gather.upload_world(host.describe())
