@@ -336,6 +336,25 @@ int rc_write_ppm(const char* path);
  * Asynchronous: enqueues the kernels and returns. */
 int rc_render_frame(const rc_frame_params* params);
 
+/* rc_render_frame for callers that cannot allocate device memory -- code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc.  No counterpart in the reference.
+ * Same parameters, same pixels as rc_render_frame, but the RC_RGBA8 frame (bottom row first, width * height * 4 bytes) is
+ * written into DEVICE memory the caller owns (rgba8_device), and everything else a frame needs -- counters, sky-gate
+ * table, AO direction table, AO seed list -- lives in a fixed array inside the library (static __device__, 12.9 MB,
+ * held by every GPU that loads librc.so until the process exits) instead of buffers grown with cudaMalloc.  The call
+ * never calls cudaMalloc / cudaFree or any allocating routine; it only queues kernels on the library's stream
+ * (rc_set_stream) and returns.  Limits: width * height <= RC_STATIC_MAX_PIXELS (e.g. 640 x 360 or 512 x 512; larger
+ * frames are refused with RC_ERR_INVALID_ARGUMENT and a message, use rc_render_frame); RGBA8 only (RC_F_HITS, RC_F_RGBA32F,
+ * RC_F_KERNEL_TIMES are refused); one device, unsharded (rc_init, not rc_init_multi / rc_set_shard); no frame target.
+ * The first call with a new ao_samples or max_steps (or after a world change) also rebuilds the small tables (a kernel
+ * and a few host-to-device copies; still no allocation).  rc_frame_stats_get, rc_read_image, rc_device_image keep
+ * describing the last rc_render_frame, not this call.  Every call shares the one scratch array, which keeps the last
+ * call's contents (what must start at zero is cleared by the call itself): calls that could overlap on the GPU -- issued
+ * on different streams through rc_set_stream without ordering between them -- race on it; calls on one stream are
+ * ordered and safe.  rc_sync (or a synchronise of the stream) makes the frame visible. */
+#define RC_STATIC_MAX_PIXELS 262144u
+int rc_render_frame_static(const rc_frame_params* params, void* rgba8_device, size_t rgba8_bytes);
+
 /* Replaces glfwSwapBuffers / glReadPixels (src/main.cpp:216,38): waits for the
  * frame and copies it to host memory.  dst_bytes >= width*height*(4|16). */
 int rc_read_image(void* dst, size_t dst_bytes, int format);

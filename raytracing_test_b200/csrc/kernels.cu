@@ -2024,6 +2024,7 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
                 o.ly = face == 1 ? fabsf(iv[1]) : 0.0f;
             }
     }
+    static_assert(sizeof(host) == AO_TABLE_BYTES, "kernels.h states the table's size");
     if (!*table) {
         e = cudaMalloc(table, sizeof(host));
         if (e != cudaSuccess) return e;

@@ -122,8 +122,12 @@ enum FrameSchedule : uint32_t {
 };
 constexpr uint32_t SCHED_DEFAULT = SCHED_AUTO;
 
+// Bytes of the oriented AO direction table (AoDir[6][RC_MAX_AO_SAMPLES], 32 bytes per entry; kernels.cu asserts it).
+constexpr size_t AO_TABLE_BYTES = 6u * RC_MAX_AO_SAMPLES * 32u;
+
 // Loads the AO direction table (3*n floats: x, y, up) into __constant__ memory of the current device and the oriented
-// table of the window AO code into *table (device memory, allocated on first use; pass it on as FrameArgs::ao_table).
+// table of the window AO code into *table (device memory, AO_TABLE_BYTES, allocated on first use -- a non-null *table is
+// used as it is, nothing is allocated; pass it on as FrameArgs::ao_table).
 cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream, void** table);
 void release_hemisphere(void* table);
 

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdarg.h>
+#include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -99,6 +100,11 @@ struct Context {
     // how frames are scheduled on the device / which AO specialisations run (rc_debug_set_option; same pixels either way)
     uint32_t schedule = SCHED_DEFAULT, scheduleUsed = SCHED_DEFAULT, aoOpts = AO_OPT_DEFAULT, debugPrimarySmem = 0;
     cudaEvent_t evStart = nullptr, evPrimary = nullptr, evEnd = nullptr;
+
+    // rc_render_frame_static: device address of rc_static_scratch on this device (cudaGetSymbolAddress at rc_init), the
+    // ao_samples its AO table holds and the step budget its gate table was built for
+    unsigned char* staticScratch = nullptr;
+    uint32_t staticHemi = 0, staticGateSteps = 0xFFFFFFFFu;
 
     // rc_init_multi: this device may store into device 0's memory (peer access enabled), its frame target pointers are
     // device 0's (not to be freed / unmapped here), and the event the owner's stream waits for after each frame
@@ -216,6 +222,30 @@ int growBuffer(T*& ptr, size_t& capacity, size_t need) {
 
 }  // namespace
 
+// ---- rc_render_frame_static: scratch that is never allocated -----------------------------------------------------------
+// Everything a frame needs besides the world, the caller's parameters and the caller's output frame, for frames of up to
+// RC_STATIC_MAX_PIXELS pixels: the frame counters / queue cursors, the sky-gate table, the oriented AO direction table and
+// the AO seed list.  One file-scope array in device memory, held by every GPU that loads the library until the process
+// exits (12.9 MB).  In host code the array's NAME is only a stand-in: the device address comes from cudaGetSymbolAddress,
+// once per device at rc_init (one_init), and that pointer is what the kernels get.
+struct StaticScratch {
+    FrameCounterBlock counters;                           // cleared before every frame (static_scratch_clear_kernel)
+    alignas(256) uint4 skyGate[4 * SKY_GRID * SKY_GRID];  // rebuilt when the step budget or the world changes
+    alignas(256) unsigned char aoTable[AO_TABLE_BYTES];   // rebuilt when ao_samples changes
+    alignas(256) AoSeed seeds[RC_STATIC_MAX_PIXELS];      // written by the primary kernel before the AO kernel reads it
+};
+static_assert(offsetof(StaticScratch, skyGate) % 256 == 0 && offsetof(StaticScratch, aoTable) % 256 == 0 &&
+                  offsetof(StaticScratch, seeds) % 256 == 0,
+              "every part of the static scratch starts on a 256-byte boundary");
+static __device__ __align__(256) unsigned char rc_static_scratch[sizeof(StaticScratch)];
+
+// Device code names the array directly.  The counters and cursors must start at zero; the rest is overwritten before it
+// is read.
+__global__ void static_scratch_clear_kernel() {
+    uint32_t* w = reinterpret_cast<uint32_t*>(rc_static_scratch + offsetof(StaticScratch, counters));
+    for (uint32_t i = threadIdx.x; i < sizeof(FrameCounterBlock) / 4u; i += blockDim.x) w[i] = 0u;
+}
+
 extern "C" {
 
 int rc_abi_version(void) { return RC_ABI_VERSION; }
@@ -251,6 +281,10 @@ static int one_init(int device) {
     CUDA_TRY(cudaEventCreate(&g.evStart));
     CUDA_TRY(cudaEventCreate(&g.evPrimary));
     CUDA_TRY(cudaEventCreate(&g.evEnd));
+    // the static scratch of rc_render_frame_static as THIS device sees it (the device is current: cudaSetDevice above)
+    CUDA_TRY(cudaGetSymbolAddress((void**)&g.staticScratch, rc_static_scratch));
+    g.staticHemi = 0;
+    g.staticGateSteps = 0xFFFFFFFFu;
     g.device = device;
     g.rank = 0;
     g.worldSize = 1;
@@ -396,6 +430,7 @@ static int ensureHostCopy() {
 // stream-ordered, nothing comes back to the host.
 static int refreshSky() {
     g.skyGateSteps = 0xFFFFFFFFu;
+    g.staticGateSteps = 0xFFFFFFFFu;  // the static entry point's table was built from the old tops too
     g.skyShift = (int)g.world.root_shift + 2 - 6;  // torus edge / SKY_GRID
     if (g.skyShift < 2) return RC_OK;  // a brick would straddle blocks: no gating for such a shallow tree
     if (!g.dSkyTops) CUDA_TRY(cudaMalloc((void**)&g.dSkyTops, (size_t)SKY_GRID * SKY_GRID * sizeof(int)));
@@ -1428,6 +1463,109 @@ int rc_render_frame(const rc_frame_params* params) {
             CUDA_TRY(cudaStreamWaitEvent(contexts[0].stream, c.evFrameDone, 0));
         }
     }
+    return RC_OK;
+}
+
+// rc_render_frame without a single allocation (include/rc.h): the frame goes into the caller's device buffer, the scratch
+// is rc_static_scratch (its device address: g.staticScratch, from cudaGetSymbolAddress at rc_init).  No counterpart in the
+// reference.  Leaves the state of the last rc_render_frame (frame buffers, statistics, events) alone.
+int rc_render_frame_static(const rc_frame_params* params, void* rgba8_device, size_t rgba8_bytes) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_render_frame_static: call rc_init first");
+    if (nContexts > 1) return fail(RC_ERR_UNSUPPORTED, "rc_render_frame_static: one device only (rc_init, not rc_init_multi)");
+    if (!g.haveWorld) return fail(RC_ERR_NO_WORLD, "rc_render_frame_static: call rc_upload_world first");
+    if (!params || !rgba8_device) return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame_static: null params / frame");
+    const rc_frame_params& p = *params;
+    if (p.width == 0 || p.height == 0 || p.width > 65536 || p.height > 65536)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame_static: resolution %ux%u", p.width, p.height);
+    const uint64_t pixels = (uint64_t)p.width * p.height;
+    if (pixels > RC_STATIC_MAX_PIXELS)
+        return fail(RC_ERR_INVALID_ARGUMENT,
+                    "rc_render_frame_static: %ux%u = %llu pixels, more than RC_STATIC_MAX_PIXELS = %u (the scratch of this entry "
+                    "point is a fixed array; use rc_render_frame for larger frames)",
+                    p.width, p.height, (unsigned long long)pixels, RC_STATIC_MAX_PIXELS);
+    if (rgba8_bytes < pixels * 4)
+        return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_render_frame_static: the frame needs %llu bytes", (unsigned long long)(pixels * 4));
+    if (p.ao_samples > RC_MAX_AO_SAMPLES)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame_static: ao_samples %u > %u", p.ao_samples, RC_MAX_AO_SAMPLES);
+    if (p.max_steps > 65535 || p.shadow_steps > 65535)
+        return fail(RC_ERR_INVALID_ARGUMENT, "rc_render_frame_static: step limits above 65535");
+    if (p.flags & (RC_F_HITS | RC_F_RGBA32F | RC_F_KERNEL_TIMES))
+        return fail(RC_ERR_UNSUPPORTED, "rc_render_frame_static: RGBA8 frames only (no RC_F_HITS / RC_F_RGBA32F / RC_F_KERNEL_TIMES)");
+    if (g.worldSize != 1) return fail(RC_ERR_UNSUPPORTED, "rc_render_frame_static: unsharded frames only (rc_set_shard(0, 1))");
+    if (!g.staticScratch) return fail(RC_ERR_CUDA, "rc_render_frame_static: the scratch array has no device address");
+    CUDA_TRY(cudaSetDevice(g.device));
+    // a DEVICE address: only offsets are taken from it on the host
+    StaticScratch* const scratch = reinterpret_cast<StaticScratch*>(g.staticScratch);
+
+    if (p.ao_samples > 0) {
+        // the oriented table goes into the scratch; the __constant__ tables (c_hemi, c_aoSeg) are shared with rc_render_frame,
+        // whose own oriented table then no longer matches them: it reloads on its next AO frame (hemiLoaded = 0)
+        const bool constantsMatch = g.hemiLoaded == 0 || g.hemiLoaded == p.ao_samples;
+        if (g.staticHemi != p.ao_samples || !constantsMatch) {
+            float tab[3 * RC_MAX_AO_SAMPLES];
+            hemisphereTable(p.ao_samples, tab);
+            void* table = scratch->aoTable;  // non-null: upload_hemisphere fills it and allocates nothing
+            CUDA_TRY(upload_hemisphere(tab, p.ao_samples, g.stream, &table));
+            g.staticHemi = p.ao_samples;
+            g.hemiLoaded = 0;
+        }
+    }
+
+    FrameArgs a;
+    memset(&a, 0, sizeof(a));
+    a.p = p;
+    a.world = g.world;
+    a.rank = 0;
+    a.world_size = 1;
+    a.inv_width = 1.0f / (float)p.width;
+    a.inv_height = 1.0f / (float)p.height;
+    {
+        // free flight: the conditions of rc_render_frame, the gate table in the scratch
+        const float oy = floorf(p.origin[1]);
+        if (!(p.flags & RC_F_NO_FREE_FLIGHT) && p.max_steps <= 1024u && g.skyShift >= 2 && g.dSkyTops && oy >= 0.0f &&
+            oy + (float)p.max_steps <= (float)g.world.wrap) {
+            if (g.staticGateSteps != p.max_steps) {
+                CUDA_TRY(launch_sky_gates(g.dSkyTops, g.skyShift, p.max_steps, scratch->skyGate, g.stream));
+                g.staticGateSteps = p.max_steps;
+            }
+            a.sky_gate = scratch->skyGate;
+            a.sky_shift = g.skyShift;
+            a.shadow_gate = p.shadow_steps <= p.max_steps ? 1u : 0u;
+            long long manhattan = 0;
+            for (int k = 0; k < 3; k++) manhattan += llabs((long long)p.looking_at[k] - (long long)floorf(p.origin[k]));
+            a.sky_tail = ((p.flags & RC_F_ALWAYS_TAIL) || p.render_pos_data != 0 || manhattan == (long long)p.max_steps) ? 1u : 0u;
+        }
+    }
+    if (!(p.flags & RC_F_NO_COLUMN_REGIONS) && g.skyShift >= 2 && g.dSkyTops) {
+        a.col_tops = g.dSkyTops;
+        a.sky_shift = g.skyShift;
+    }
+    a.n_local_bands = (p.height + BAND_ROWS - 1) / BAND_ROWS;
+    a.local_rows = a.n_local_bands * BAND_ROWS;  // rows beyond the frame's height are never touched (py < height)
+    a.rgba8 = (uchar4*)rgba8_device;
+    a.ao_seeds = p.ao_samples > 0 ? scratch->seeds : nullptr;
+    a.counters = &scratch->counters;
+    a.ao_table = p.ao_samples > 0 ? (const void*)scratch->aoTable : nullptr;
+    a.ao_opts = g.aoOpts;
+    for (int k = 0; k < 3; k++) a.sun_inv[k] = 1.0f / p.sun_dir[k];
+    {
+        // low_res.frag:279-283, one rounded operation at a time (as in rc_render_frame)
+        auto cross = [](const float* u, const float* v, float* r) {
+            volatile float m0 = u[1] * v[2], m1 = v[1] * u[2], m2 = u[2] * v[0], m3 = v[2] * u[0], m4 = u[0] * v[1], m5 = v[0] * u[1];
+            r[0] = m0 - m1;
+            r[1] = m2 - m3;
+            r[2] = m4 - m5;
+        };
+        const float yAxis[3] = {0.0f, 1.0f, 0.0f};
+        cross(p.camera_dir, yAxis, a.cam_left);
+        cross(p.camera_dir, a.cam_left, a.cam_up);
+    }
+
+    // the counters and queue cursors must start at zero; everything else in the scratch is written before it is read
+    static_scratch_clear_kernel<<<1, 256, 0, g.stream>>>();
+    CUDA_TRY(cudaGetLastError());
+    uint32_t launches = 0, used = 0;
+    CUDA_TRY(launch_frame(a, g.schedule, g.numSms, nullptr, g.stream, &launches, &used));
     return RC_OK;
 }
 

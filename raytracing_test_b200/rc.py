@@ -23,6 +23,7 @@ AO_OPT_OCTANT = 1
 RC_RGBA8, RC_RGBA32F = 0, 1
 RC_IPC_HANDLE_BYTES = 64
 RC_ALL_BLOCKS = 0xFFFFFFFF
+RC_STATIC_MAX_PIXELS = 262144
 KIND_SKY, KIND_HIT, KIND_CAMERA_INSIDE, KIND_CROSSHAIR, KIND_HIGHLIGHT, KIND_DEBUG = range(6)
 HF_SHADOWED, HF_REFLECTED, HF_REFRACTED, HF_FACING_SUN = 1, 2, 4, 8
 BAND_ROWS = 16
@@ -144,6 +145,7 @@ ABI = {
     "rc_write_ppm": (ctypes.c_int, [ctypes.c_char_p]),
     "rc_generate_world": (ctypes.c_int, [ctypes.POINTER(GenParams), ctypes.POINTER(GenInfo)]),
     "rc_render_frame": (ctypes.c_int, [ctypes.POINTER(FrameParams)]),
+    "rc_render_frame_static": (ctypes.c_int, [ctypes.POINTER(FrameParams), ctypes.c_void_p, ctypes.c_size_t]),
     "rc_read_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]),
     "rc_read_image_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int)]),
     "rc_wait_image": (ctypes.c_int, [ctypes.c_int]),
@@ -347,6 +349,11 @@ class RayCaster:
     def render_frame(self, params):
         _check(self.lib, self.lib.rc_render_frame(ctypes.byref(params)))
         self._last = (params.width, params.height)
+
+    def render_frame_static(self, params, device_ptr, nbytes):
+        """rc_render_frame_static: the RGBA8 frame into caller-owned DEVICE memory, scratch in the library's fixed array
+        (no allocation; width * height <= RC_STATIC_MAX_PIXELS)."""
+        _check(self.lib, self.lib.rc_render_frame_static(ctypes.byref(params), device_ptr, nbytes))
 
     def sync(self):
         _check(self.lib, self.lib.rc_sync())
