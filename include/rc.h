@@ -112,6 +112,9 @@ typedef struct rc_frame_params {
 #define RC_F_NO_COLUMN_REGIONS 0x100u /* tests / measurements: primary rays above the highest voxel of their 16 x 16 column block
                                          look the empty space up in the tree, cell by cell, instead of taking the whole column
                                          above the terrain as one empty region (same frame, same hit records either way) */
+#define RC_F_NO_DROP_GATES 0x200u /* tests / measurements: only primary rays that step UP can enter free flight; rays that step down
+                                     but lose less height over their remaining steps than separates them from everything they can
+                                     still reach walk on through the tree (same frame, same hit records either way) */
 #define RC_F_KERNEL_TIMES 0x80u /* measurements: also time the primary and the AO kernel separately (rc_frame_stats.primary_ms /
                                    ao_ms).  The event between the two launches keeps the AO grid from becoming resident while
                                    the primary grid drains, and a fused frame (one kernel) has no such split: without this flag

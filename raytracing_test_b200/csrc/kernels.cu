@@ -126,15 +126,36 @@ __device__ __forceinline__ uint4 load_node(const DeviceWorld& W, const Cursor& c
     return __ldg(&W.nodes[idx]);
 }
 
-__device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c, const uint4* top = nullptr, uint32_t ntop = 0u) {
-    c.top = top;
-    c.ntop = ntop;
-    uint4 n = load_node(W, c, 0u);
+// Where a descent starts when the voxel lies outside the cached node.  With the top table (DeviceWorld::top_table): one
+// 4-byte load names the node of the 2^top_shift cell around the voxel -- or says that the cell is empty, and how big the empty
+// cell around it is -- instead of a walk down from the root (one dependent 16-byte load per level: 3 of them to a 16^3 node
+// of the reference's 1024^3 torus).  Returns true when r is already the answer (an empty or uniform cell); else the cursor
+// holds a node that contains the voxel.  Without the table (rc_debug_set_option "top_table" 0, or the top levels staged in
+// shared memory: SCHED_PERSISTENT_STAGED) the descent starts at the root.
+__device__ __forceinline__ void cursor_to_root(const DeviceWorld& W, Cursor& c) {
+    const uint4 n = load_node(W, c, 0u);
     c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
     c.base = n.z;
     c.kind = n.w;
     c.shift = W.root_shift;
-    c.lx = c.ly = c.lz = 0;
+}
+
+// No node cached yet: the first lookup starts at the top (lx is a coordinate no voxel has).
+__device__ __forceinline__ void cursor_reset(const DeviceWorld& W, Cursor& c, const uint4* top = nullptr, uint32_t ntop = 0u) {
+    c.top = top;
+    c.ntop = ntop;
+    c.mask = 0ull;
+    c.base = 0u;
+    c.kind = 0u;
+    c.shift = W.root_shift;
+    c.lx = c.ly = c.lz = 0x40000000;
+}
+
+// Top-table entry of the cell around wrapped voxel (wx, wy, wz): bit 31 set = index of the node of that cell (its children
+// are cells of shift top_shift - 2; a PK_LEAF node = the cell is uniform), else the shift of the empty aligned cell around it.
+__device__ __forceinline__ uint32_t top_entry(const DeviceWorld& W, int wx, int wy, int wz) {
+    const uint32_t cx = (uint32_t)wx >> W.top_shift, cy = (uint32_t)wy >> W.top_shift, cz = (uint32_t)wz >> W.top_shift;
+    return __ldg(&W.top_table[(((cz << W.top_bits) | cy) << W.top_bits) | cx]);
 }
 
 // Voxel coordinate -> tree coordinate. The reference spreads a coordinate into its Morton code with
@@ -152,11 +173,24 @@ __device__ __forceinline__ int wrap_coord(const DeviceWorld& W, int v) {
 __device__ __forceinline__ uint32_t lookup(const DeviceWorld& W, Cursor& c, int x, int y, int z, int& cellShift) {
     const int wx = wrap_coord(W, x), wy = wrap_coord(W, y), wz = wrap_coord(W, z);
     if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
-        uint4 n = load_node(W, c, 0u);
-        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
-        c.base = n.z;
-        c.kind = n.w;
-        c.shift = W.root_shift;
+        if (W.top_table && c.ntop == 0u) {
+            const uint32_t e = top_entry(W, wx, wy, wz);
+            if (!(e & 0x80000000u)) {  // empty: the cursor keeps its node
+                cellShift = (int)e;
+                return 0u;
+            }
+            const uint4 n = __ldg(&W.nodes[e & 0x7FFFFFFFu]);
+            if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+                cellShift = W.top_shift;
+                return n.z;
+            }
+            c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+            c.base = n.z;
+            c.kind = n.w;
+            c.shift = W.top_shift - 2;
+        } else {
+            cursor_to_root(W, c);
+        }
     }
     c.lx = wx;
     c.ly = wy;
@@ -205,11 +239,30 @@ struct Region {
 // Region around wrapped voxel (wx,wy,wz); descends from the deepest cached node that contains it.
 __device__ __forceinline__ void fetch_region(const DeviceWorld& W, Cursor& c, int wx, int wy, int wz, Region& r) {
     if ((((wx ^ c.lx) | (wy ^ c.ly) | (wz ^ c.lz)) >> (c.shift + 2)) != 0) {
-        uint4 n = load_node(W, c, 0u);
-        c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
-        c.base = n.z;
-        c.kind = n.w;
-        c.shift = W.root_shift;
+        if (W.top_table && c.ntop == 0u) {
+            const uint32_t e = top_entry(W, wx, wy, wz);
+            if (!(e & 0x80000000u)) {  // empty: the cursor keeps its node
+                r.mask = 0ull;
+                r.base = 0u;
+                r.info = 0u;
+                r.shift = (int)e;
+                return;
+            }
+            const uint4 n = __ldg(&W.nodes[e & 0x7FFFFFFFu]);
+            if ((n.w & PK_KIND_MASK) == PK_LEAF) {
+                r.mask = ~0ull;
+                r.base = n.z;
+                r.info = BR_UNIFORM | ((word_flags(n.z) & 0x10u) ? BR_LIQUID : 0u);
+                r.shift = W.top_shift;
+                return;
+            }
+            c.mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+            c.base = n.z;
+            c.kind = n.w;
+            c.shift = W.top_shift - 2;
+        } else {
+            cursor_to_root(W, c);
+        }
     }
     c.lx = wx;
     c.ly = wy;
@@ -527,6 +580,45 @@ __device__ __forceinline__ int sky_gate_distance(const FrameArgs& A, int x, int 
     return d;
 }
 
+// The same question for a ray that steps DOWN (FrameArgs::drop_gate): a grazing ray that loses only a few voxels of height
+// over its whole step budget is above everything it can still reach long before it has taken its steps -- the 6 % of the
+// benchmark frame's pixels just under the horizon walk more than half of all the steps the kernel walks.  `left` events are
+// still to fire.  Events fire in time order (merge of three arithmetic sequences, see free_flight.h), so by the time tau of
+// the last of them every axis a has fired at least (tau - now) / absDelta[a] - 1: left >= (tau - now) * (|dx| + |dy| + |dz|)
+// - 3, and y has fired at most (tau - now) / absDelta.y + 1 <= (left + 3) * |dy| / (|dx| + |dy| + |dz|) + 1 -- the ray's
+// whole drop (`total`, with 1 more for the rounding of the sums: the additions are off by half an ulp of t < 2048 each,
+// far less than one event over 1024 steps).  And while the ray is still within d blocks (Chebyshev) of this one it has
+// stepped fewer than (d + 1) * B times along x and along z, so less time than (d + 1) * B * min(absDelta.x, absDelta.z) has
+// passed since its next x / z event was due (itself at most one absDelta after now), in which y fires at most
+// (d + 1) * B * min(absDelta.x, absDelta.z) / absDelta.y + 1 times: the drop inside ring 0-1 uses d + 1 = 2, ring 2-3 4,
+// ring 4-7 8, ring 8-15 16, the last ring the whole drop.  > 0: y less that drop clears every ring's gate (and stays on the
+// torus: gates are >= 0).  The caller makes sure x, y and z are on the torus and that no deltaPos is NaN.
+__device__ __forceinline__ int sky_drop_distance(const FrameArgs& A, int x, int y, int z, bool sxNeg, bool szNeg, float adx, float adz,
+                                                 float dx, float dy, float dz, uint32_t left) {
+    const uint32_t q = (sxNeg ? 1u : 0u) | (szNeg ? 2u : 0u);
+    const uint4 g = __ldg(&A.sky_gate[(q * SKY_GRID + ((uint32_t)z >> A.sky_shift)) * SKY_GRID + ((uint32_t)x >> A.sky_shift)]);
+    const float rate = FDIV(fabsf(dy), FADD(FADD(fabsf(dx), fabsf(dy)), fabsf(dz)));
+    const float total = floorf(FMUL((float)(left + 3u), rate)) + 2.0f;
+    // per block of horizontal travel; inf / NaN (an axis that never steps) fall back to the whole drop in fminf below
+    const float slope = FMUL(fminf(adx, adz), fabsf(dy)) * (float)(1 << A.sky_shift);
+    const int y1 = y + 1;
+#ifdef RC_MUTATE_DROP  // mutation check (tools/mutation_check.sh): the drop up to the NEAR edge of each ring, no slack
+    int d = y1 - (int)(g.x & 0xFFFFu);
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 2.0f)) - (int)(g.x >> 16));
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 4.0f)) - (int)(g.y & 0xFFFFu));
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 8.0f)) - (int)(g.y >> 16));
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 16.0f)) - (int)g.z);
+#else
+    int d = y1 - (int)fminf(total, floorf(slope * 2.0f) + 2.0f) - (int)(g.x & 0xFFFFu);
+    if (d <= 0) return d;  // rays on their way into the terrain leave here
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 4.0f) + 2.0f) - (int)(g.x >> 16));
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 8.0f) + 2.0f) - (int)(g.y & 0xFFFFu));
+    d = min(d, y1 - (int)fminf(total, floorf(slope * 16.0f) + 2.0f) - (int)(g.y >> 16));
+    d = min(d, y1 - (int)total - (int)g.z);
+#endif
+    return d;
+}
+
 // The copy of the frame statistics this CTA adds to (FrameCounterBlock: spread over lines so that the atomics of 65 k warps
 // do not queue on one).
 __device__ __forceinline__ FrameCounters& counter_slot(const FrameArgs& A) {
@@ -659,10 +751,18 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 // nothing left to hit: the remaining steps only move it, and run after this loop without cells, countdowns
                 // or the tree.
                 int gateDist = -0x10000;
-                if (A.sky_gate && ray.sy > 0 && (uint32_t)pos.x <= W.wrap && (uint32_t)pos.z <= W.wrap) {
-                    gateDist = sky_gate_distance(A, pos.x, pos.y, pos.z, ray.sx < 0, ray.sz < 0, ray.adx, ray.adz, ray.dy,
-                                                 pos.ty == pos.ty && pos.tz == pos.tz);
-                    if (gateDist > 0) {
+                if (A.sky_gate && (uint32_t)pos.x <= W.wrap && (uint32_t)pos.z <= W.wrap) {
+                    if (ray.sy > 0) {
+                        gateDist = sky_gate_distance(A, pos.x, pos.y, pos.z, ray.sx < 0, ray.sz < 0, ray.adx, ray.adz, ray.dy,
+                                                     pos.ty == pos.ty && pos.tz == pos.tz);
+                        if (gateDist > 0) {
+                            freeFlight = true;
+                            break;
+                        }
+                    } else if (A.drop_gate && (uint32_t)pos.y <= W.wrap && pos.tx == pos.tx && pos.ty == pos.ty && pos.tz == pos.tz &&
+                               sky_drop_distance(A, pos.x, pos.y, pos.z, ray.sx < 0, ray.sz < 0, ray.adx, ray.adz, ray.dx, ray.dy, ray.dz,
+                                                 numSteps - steps) > 0) {
+                        // a ray that steps down, but not as far down as anything it can still reach
                         freeFlight = true;
                         break;
                     }
@@ -1910,6 +2010,31 @@ __global__ void __launch_bounds__(128) world_tops_kernel(DeviceWorld W, int bs, 
     }
 }
 
+// Top table (DeviceWorld::top_table): thread = one aligned cell of shift top_shift; walks down from the root to the node of
+// that cell and leaves its index (bit 31 set), or the shift of the empty cell it ran into on the way.  A uniform cell
+// (PK_LEAF) met on the way is entered with its own node index: the lookup reads the material word from it.
+__global__ void __launch_bounds__(128) top_table_kernel(DeviceWorld W, uint32_t* __restrict__ table) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t dimMask = (1u << W.top_bits) - 1u;
+    if ((t >> (3 * W.top_bits)) != 0u) return;
+    const uint32_t x = (t & dimMask) << W.top_shift, y = ((t >> W.top_bits) & dimMask) << W.top_shift,
+                   z = ((t >> (2 * W.top_bits)) & dimMask) << W.top_shift;
+    uint32_t ni = 0u;
+    uint4 n = __ldg(&W.nodes[0]);
+    for (int s = W.root_shift; s >= W.top_shift; s -= 2) {
+        const unsigned long long mask = (unsigned long long)n.x | ((unsigned long long)n.y << 32);
+        const uint32_t idx = (((z >> s) & 3u) << 4) | (((y >> s) & 3u) << 2) | ((x >> s) & 3u);
+        if (!((mask >> idx) & 1ull)) {
+            table[t] = (uint32_t)s;
+            return;
+        }
+        ni = n.z + (uint32_t)__popcll(mask & ((1ull << idx) - 1ull));
+        n = __ldg(&W.nodes[ni]);
+        if ((n.w & PK_KIND_MASK) == PK_LEAF) break;
+    }
+    table[t] = 0x80000000u | ni;
+}
+
 // Gate table for one step budget (FrameArgs::sky_gate): thread = (quadrant, block); rings of Chebyshev block distance
 // 0-1, 2-3, 4-7, 8-15, 16+ inside the window a ray can cross in maxSteps steps.
 __global__ void __launch_bounds__(128) sky_gate_kernel(const int* __restrict__ tops, int bs, uint32_t maxSteps, uint4* __restrict__ gates) {
@@ -2151,6 +2276,12 @@ cudaError_t launch_world_tops(const DeviceWorld& world, int skyShift, int* tops,
     cudaError_t e = cudaMemsetAsync(tops, 0xFF, SKY_GRID * SKY_GRID * sizeof(int), stream);  // -1: empty
     if (e != cudaSuccess) return e;
     world_tops_kernel<<<64 * 64 * 64 / 128, 128, 0, stream>>>(world, skyShift, tops);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_top_table(const DeviceWorld& world, uint32_t* table, cudaStream_t stream) {
+    const uint32_t cells = 1u << (3 * world.top_bits);
+    top_table_kernel<<<(cells + 127u) / 128u, 128, 0, stream>>>(world, table);
     return cudaGetLastError();
 }
 

@@ -22,6 +22,12 @@ struct DeviceWorld {
     int root_shift;          // cell shift of the root's children: 2*(max_depth-2)
     uint32_t wrap;           // (1 << 2*(max_depth-1)) - 1
     uint32_t leak;           // 0x300 for max_depth 6 (the reference's Morton-spread quirk), else 0
+    // Top table: for every aligned cell of shift top_shift (2^top_bits cells per axis, at most 64: 16^3 cells for the
+    // reference's 1024^3 torus) the index of the node of that cell | 0x80000000, or the shift of the empty cell around it.
+    // A lookup that has left its cached node starts here instead of at the root.  Null: descents start at the root
+    // (trees of depth 2; rc_debug_set_option "top_table" 0).  Rebuilt on the device after every world change.
+    const uint32_t* top_table;
+    int top_shift, top_bits;
 };
 
 // Per-hit-pixel record handed from the primary kernel to the AO kernel.
@@ -82,6 +88,7 @@ struct FrameArgs {
     uint32_t sky_tail;       // 1: a free ray's final voxel / last face are needed (hit records, position debug output, or the
                              // looked-at voxel lies exactly max_steps steps from the camera's); 0: nobody can see them
     uint32_t shadow_gate;    // the table also covers the shadow rays' reach (shadow_steps <= max_steps, flags allow it)
+    uint32_t drop_gate;      // rays that step DOWN are tested against the table too (sky_drop_distance; RC_F_NO_DROP_GATES: off)
     uint32_t local_rows;     // rows stored locally = owned bands * BAND_ROWS (last band may be partial)
     uint32_t n_local_bands;
     uchar4* rgba8;           // [local_rows][width]
@@ -150,6 +157,9 @@ cudaError_t launch_pick(const DeviceWorld& world, const float* cam_pos3, const f
 // block edge = 2^sky_shift voxels.  One depth-first walk per 64^3 subtree.
 constexpr int SKY_GRID = 64;
 cudaError_t launch_world_tops(const DeviceWorld& world, int sky_shift, int* tops, cudaStream_t stream);
+// Fills world.top_table (TOP_TABLE_MAX_CELLS entries at most) from the packed tree: one thread per cell.
+constexpr uint32_t TOP_TABLE_MAX_CELLS = 64u * 64u * 64u;
+cudaError_t launch_top_table(const DeviceWorld& world, uint32_t* table, cudaStream_t stream);
 // tops -> the gate table of FrameArgs::sky_gate for a step budget (4 * SKY_GRID * SKY_GRID entries of 16 bytes).
 cudaError_t launch_sky_gates(const int* tops, int sky_shift, uint32_t max_steps, uint4* gates, cudaStream_t stream);
 

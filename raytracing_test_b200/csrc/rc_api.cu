@@ -81,6 +81,8 @@ struct Context {
     FrameCounterBlock* dCounters = nullptr;
     // sky gates (kernels.h, FrameArgs::sky_gate): column-block tops of the current world, the gate table built from them
     int* dSkyTops = nullptr;
+    uint32_t* dTopTable = nullptr;  // DeviceWorld::top_table (kernels.h), TOP_TABLE_MAX_CELLS entries, rebuilt with the tops
+    bool useTopTable = true;        // rc_debug_set_option "top_table"
     uint4* dSkyGate = nullptr;
     int skyShift = 0;
     uint32_t skyGateSteps = 0xFFFFFFFFu;  // max_steps the table on the device was built for (none)
@@ -306,6 +308,8 @@ static void one_shutdown(void) {
     g.aoTable = nullptr;
     if (g.dCounters) cudaFree(g.dCounters);
     if (g.dSkyTops) cudaFree(g.dSkyTops);
+    if (g.dTopTable) cudaFree(g.dTopTable);
+    g.dTopTable = nullptr;
     if (g.dSkyGate) cudaFree(g.dSkyGate);
     g.dSkyTops = nullptr;
     g.dSkyGate = nullptr;
@@ -431,6 +435,19 @@ static int ensureHostCopy() {
 static int refreshSky() {
     g.skyGateSteps = 0xFFFFFFFFu;
     g.staticGateSteps = 0xFFFFFFFFu;  // the static entry point's table was built from the old tops too
+    {
+        // top table: cells of shift max(root_shift - 4, 4), at most 64 per axis; trees of depth 2 have none
+        DeviceWorld& w = g.world;
+        w.top_table = nullptr;
+        w.top_shift = w.root_shift - 4 > 4 ? w.root_shift - 4 : 4;
+        w.top_bits = w.root_shift + 2 - w.top_shift;
+        if (w.top_bits >= 0 && w.top_bits <= 6) {
+            if (!g.dTopTable) CUDA_TRY(cudaMalloc((void**)&g.dTopTable, (size_t)TOP_TABLE_MAX_CELLS * sizeof(uint32_t)));
+            w.top_table = g.dTopTable;
+            CUDA_TRY(launch_top_table(w, g.dTopTable, g.stream));
+            if (!g.useTopTable) w.top_table = nullptr;
+        }
+    }
     g.skyShift = (int)g.world.root_shift + 2 - 6;  // torus edge / SKY_GRID
     if (g.skyShift < 2) return RC_OK;  // a brick would straddle blocks: no gating for such a shallow tree
     if (!g.dSkyTops) CUDA_TRY(cudaMalloc((void**)&g.dSkyTops, (size_t)SKY_GRID * SKY_GRID * sizeof(int)));
@@ -799,6 +816,7 @@ static int one_render_frame(const rc_frame_params* params) {
             a.sky_gate = g.dSkyGate;
             a.sky_shift = g.skyShift;
             a.shadow_gate = p.shadow_steps <= p.max_steps ? 1u : 0u;
+            a.drop_gate = (p.flags & RC_F_NO_DROP_GATES) ? 0u : 1u;
             // where a free ray ends matters only to the hit records, to render_pos_data = 2 (pos.round as colour) and to
             // the highlight test (low_res.frag:347-350) -- which a ray that has taken all max_steps steps can only pass
             // if the looked-at voxel is exactly that many steps (|dx| + |dy| + |dz|) from the camera's
@@ -1281,6 +1299,12 @@ static int one_debug_set_option(const char* name, int value) {
         g.schedule = (uint32_t)value;
     } else if (!strcmp(name, "ao_opts")) {
         g.aoOpts = (uint32_t)value & AO_OPT_DEFAULT;
+    } else if (!strcmp(name, "top_table")) {  // A/B: 0 = every descent that leaves its cached node starts at the root
+        g.useTopTable = value != 0;
+        if (g.haveWorld) {
+            CUDA_TRY(cudaStreamSynchronize(g.stream));
+            g.world.top_table = g.useTopTable && g.dTopTable && g.world.top_bits >= 0 && g.world.top_bits <= 6 ? g.dTopTable : nullptr;
+        }
     } else if (!strcmp(name, "primary_smem")) {  // A/B probe: see FrameArgs::debug_primary_smem
         if (value < 0 || value > 200 * 1024) return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: primary_smem %d", value);
         g.debugPrimarySmem = (uint32_t)value;
@@ -1531,6 +1555,7 @@ int rc_render_frame_static(const rc_frame_params* params, void* rgba8_device, si
             a.sky_gate = scratch->skyGate;
             a.sky_shift = g.skyShift;
             a.shadow_gate = p.shadow_steps <= p.max_steps ? 1u : 0u;
+            a.drop_gate = (p.flags & RC_F_NO_DROP_GATES) ? 0u : 1u;
             long long manhattan = 0;
             for (int k = 0; k < 3; k++) manhattan += llabs((long long)p.looking_at[k] - (long long)floorf(p.origin[k]));
             a.sky_tail = ((p.flags & RC_F_ALWAYS_TAIL) || p.render_pos_data != 0 || manhattan == (long long)p.max_steps) ? 1u : 0u;

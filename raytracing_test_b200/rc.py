@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("RC_LIBRC") or os.path.join(PKG_DIR, "librc.so")  # RC
 RC_F_CROSSHAIR, RC_F_SHADOWS, RC_F_HITS, RC_F_RGBA32F, RC_F_NO_FREE_FLIGHT, RC_F_NO_LEAP, RC_F_ALWAYS_TAIL = 1, 2, 4, 8, 16, 32, 64
 RC_F_KERNEL_TIMES = 128
 RC_F_NO_COLUMN_REGIONS = 256
+RC_F_NO_DROP_GATES = 512
 # rc_debug_set_option("schedule", ...): how a frame is scheduled on the device (csrc/kernels.h FrameSchedule)
 SCHED_TWO_KERNELS, SCHED_AO_PERSISTENT, SCHED_FUSED, SCHED_PERSISTENT, SCHED_PERSISTENT_STAGED, SCHED_AUTO = range(6)
 SCHEDULES = {"two_kernels": 0, "ao_persistent": 1, "fused": 2, "persistent": 3, "persistent_staged": 4, "auto": 5}
@@ -255,7 +256,7 @@ def default_proj_plane(width, height):
 def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao_samples=0, ao_steps=5,
                  ao_strength=1.0, mouse_pos=None, looking_at=(1 << 30, 1 << 30, 1 << 30), delta_time=0.0,
                  render_pos_data=0, max_steps=300, shadow_steps=75, hits=False, rgba32f=False, proj_plane=None, free_flight=True, leap=True,
-                 always_tail=False, kernel_times=False, column_regions=True):
+                 always_tail=False, kernel_times=False, column_regions=True, drop_gates=True):
     p = FrameParams()
     p.origin[:] = [float(v) for v in origin]
     p.camera_dir[:] = [float(v) for v in camera_dir]
@@ -280,6 +281,8 @@ def frame_params(width, height, origin, camera_dir, sun_dir, *, shadows=True, ao
         flags |= RC_F_KERNEL_TIMES
     if not column_regions:
         flags |= RC_F_NO_COLUMN_REGIONS
+    if not drop_gates:
+        flags |= RC_F_NO_DROP_GATES
     pp = default_proj_plane(width, height) if proj_plane is None else proj_plane
     p.proj_plane[:] = [float(pp[0]), float(pp[1])]
     p.delta_time, p.ao_strength = delta_time, ao_strength

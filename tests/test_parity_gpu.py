@@ -81,7 +81,7 @@ def test_free_flight_changes_nothing(rcmod, caster, defaults):
     pos, d, sun = defaults
     # ... and with the column regions of loop A (the whole 16 x 16 column above the terrain as one empty region, found
     # in the tops table instead of the tree) off, alone and together with free flight: "plain" is the tree-only walk
-    modes = {"on": {}, "walk": {"leap": False}, "nocol": {"column_regions": False},
+    modes = {"on": {}, "walk": {"leap": False}, "nocol": {"column_regions": False}, "nodrop": {"drop_gates": False},
              "plain": {"free_flight": False, "column_regions": False}, "off": {"free_flight": False}}
     frames = {}
     for name, kw in modes.items():
@@ -89,7 +89,7 @@ def test_free_flight_changes_nothing(rcmod, caster, defaults):
         frames[name] = (caster.read_image().copy(), caster.read_image(fmt=rcmod.RC_RGBA32F).copy(), caster.read_hits().copy(),
                         caster.stats())
     b = frames["plain"]
-    for name in ("on", "walk", "nocol", "off"):
+    for name in ("on", "walk", "nocol", "nodrop", "off"):
         a = frames[name]
         assert a[2].tobytes() == b[2].tobytes(), name
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), name
@@ -98,6 +98,9 @@ def test_free_flight_changes_nothing(rcmod, caster, defaults):
         if name != "off":
             assert a[3].free_flight_rays > 0.5 * sky, (name, a[3].free_flight_rays, sky)
     assert b[3].free_flight_rays == 0 and frames["off"][3].free_flight_rays == 0
+    # rays that step DOWN but not as far as anything they can still reach (the grazing rays under the horizon, 300 steps
+    # each before) are set free too: sky_drop_distance
+    assert frames["on"][3].free_flight_rays > frames["nodrop"][3].free_flight_rays + 80_000
     # Without hit records (and without the position debug output) nobody can see where a free ray ends, and the tail is not
     # worked out at all -- unless the looked-at voxel lies exactly max_steps steps from the camera's, the one case in which
     # the highlight test (low_res.frag:347-350) could fire on a ray that ran out of steps.  Same frame in every case.

@@ -82,7 +82,7 @@ def test_sky_gates_random_worlds(ob, rcmod, caster, world_desc):
     from raytracing_test_b200 import voxel_host as vh
 
     modes = {"plain": dict(free_flight=False, column_regions=False), "on": {}, "walk": dict(leap=False),
-             "no_columns": dict(column_regions=False), "no_free_flight": dict(free_flight=False)}
+             "no_columns": dict(column_regions=False), "no_free_flight": dict(free_flight=False), "no_drop_gates": dict(drop_gates=False)}
     W, H = 160, 90
     free = cases = oracle_cases = 0
     try:

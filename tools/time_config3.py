@@ -11,7 +11,7 @@ c = rc.RayCaster(0)
 c.upload_world(host.describe())
 w, h = (int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "1920x1080").split("x"))
 ao_steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5  # 32 = the stress row of SURVEY 8d (config 3)
-p = rc.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=64, ao_steps=ao_steps)
+p = rc.frame_params(w, h, pos, d, sun, shadows=True, ao_samples=64, ao_steps=ao_steps, kernel_times=True)
 for _ in range(5):
     c.render_frame(p)
 c.sync()

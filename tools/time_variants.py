@@ -69,6 +69,13 @@ _, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True, column_reg
 print(f"two kernels, column regions off: primary {pr:.4f} ms")
 _, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True, column_regions=True)
 print(f"two kernels, column regions on : primary {pr:.4f} ms")
+for tt in (0, 1):
+    c.set_option("top_table", tt)
+    med, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True)
+    print(f"two kernels, top table {'on ' if tt else 'off'}: primary {pr:.4f} + ao {aos:.4f} ms")
+for dg in (False, True):
+    _, _, pr, aos, _, _ = run(rc.SCHED_TWO_KERNELS, 1, kernel_times=True, drop_gates=dg)
+    print(f"two kernels, drop gates {'on ' if dg else 'off'}: primary {pr:.4f} ms")
 med, mn, _, _, rays, _ = run(rc.SCHED_FUSED, 1, always_tail=True)
 print(f"fused, free-flight tail forced: {med:.4f} ms")
 med, mn, _, _, rays, _ = run(rc.SCHED_FUSED, 1, hits=True)
