@@ -654,6 +654,7 @@ def run_b200_arm(args, workload):
             torch.cuda.synchronize(dev)
 
         sink = {"frames": None, "next": 0}
+        copy_only = {}
 
         def run_host_direct():
             # N>1, no device-side gather at all: every rank reads ITS bands back into one shared, page-locked host
@@ -713,6 +714,17 @@ def run_b200_arm(args, workload):
             if sink["frames"] is not None:
                 run_host_direct()
                 e2e_s = timed(run_host_direct)
+                # copy-only ceiling of this path: every rank copies ITS bands of the last frame into the shared host frame,
+                # back to back, all ranks at once, with no rendering -- (a) the POSIX-shm frame registered in every process,
+                # (b) a page-locked frame of each process's own (cudaHostAlloc): what the host's memory system and the PCIe
+                # links can take, whatever the devices do
+                reps = max(args.steps, 20)
+                for key, dst in (("shared_posix_shm_frame", sink["frames"].frames[0]), ("own_cudaHostAlloc_frame", None)):
+                    barrier()
+                    t0c = time.perf_counter()
+                    sc.caster.reread_image_ms(dst, reps)
+                    barrier()
+                    copy_only[key] = max_over_ranks(time.perf_counter() - t0c) / reps * 1e3
                 if rank == 0:
                     for i, f in enumerate(sink["frames"].frames):
                         checked.append((f"frame assembled in shared host memory by every rank's own read-back, slot {i}", sha256_of(f)))
@@ -725,6 +737,9 @@ def run_b200_arm(args, workload):
                "ms_per_step": e2e_s / args.steps * 1e3,
                "sync_ms_per_step": sync_s / args.steps * 1e3,
                **({"via_rank0_ms_per_step": rank0_s / args.steps * 1e3} if rank0_s is not None else {}),
+               **({"copy_only_ms_per_frame": copy_only,
+                   "copy_only_what": "every rank's band read-backs alone (no rendering), all ranks at once, back to back: the "
+                                     "ceiling of the shared-host-frame path"} if copy_only else {}),
                "sync_value": frame_rays * args.steps / sync_s / 1e6,
                "what": how + ("; includes the NCCL band gather + compose on rank 0"
                               if world_size > 1 and sc.mode == "gather" else "")}

@@ -379,6 +379,9 @@ int rc_wait_image(int ticket);
  * memory over all the GPUs' PCIe links at once, with no device-side gather at all. */
 int rc_host_register(void* ptr, size_t bytes);
 int rc_host_unregister(void* ptr);
+/* Full memory fence (std::atomic_thread_fence, seq_cst) for hosts whose processes signal "my bands have landed" through
+ * counters that live next to the shared frame: fence before the counter store, fence after the counter load.  No device. */
+void rc_host_fence(void);
 
 /* Parity records of the last frame rendered with RC_F_HITS; n >= width*height. */
 int rc_read_hits(rc_hit* dst, size_t n);

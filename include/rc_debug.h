@@ -54,6 +54,11 @@ int rc_debug_load_host(const char* path, rc_world_info* info);
  *   "ao_opts" : bit 0 empty sample octants skipped (default 1) */
 int rc_debug_set_option(const char* name, int value);
 
+/* Copy-only ceiling of the read-back path (measurements): copies the last frame's RGBA8 rows -- this rank's bands of a
+ * sharded frame, at their place in the whole frame -- to dst `repeats` times back to back, as rc_read_image_async copies
+ * them, with no rendering in between; *ms = wall-clock time of the batch.  dst NULL: a page-locked frame of the call's own. */
+int rc_debug_reread_image(void* dst, size_t dst_bytes, uint32_t repeats, float* ms);
+
 /* sizeof of the ABI structs as the library was compiled: rc_world_desc, rc_world_info,
  * rc_frame_params, rc_hit, rc_frame_stats (bindings check their layouts against it). */
 int rc_debug_struct_sizes(uint32_t out[5]);

@@ -709,27 +709,11 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     float refrIndex = 1.0f;
 
     // :299-307
+    // (the camera's own voxel is looked up by the first pass of loop A below: the region code is inlined, and one call
+    // site for all of loop A keeps the kernel's hot code inside the instruction cache)
     RegionAt rg;
-    int colNy;  // > 0: rg is the column above the terrain (enter_region_a), this many steps along y left in it
-    enter_region_a(A, cur, rg, pos, ray.sy, colNy);
+    int colNy = 0;  // > 0: rg is the column above the terrain (enter_region_a), this many steps along y left in it
     uint32_t word = 0u;
-    {
-        const int idx = brick_bit(pos.x, pos.y, pos.z);
-        if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
-    }
-    if (live && word != 0u) {
-        if (word_flags(word) & 0x4u) {
-            refrIndex = 1.1f;
-        } else {
-            const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
-            out.color = decode_color((unsigned long long)pe.x | ((unsigned long long)pe.y << 32));
-            out.hit.kind = RC_KIND_CAMERA_INSIDE;
-            out.hit.x = pos.x;
-            out.hit.y = pos.y;
-            out.hit.z = pos.z;
-            live = false;
-        }
-    }
 
     // :309-315  loop A: to the first non-empty voxel.  pos.exact is not needed to FIND it, so this
     // pass leaves it alone (sky rays, ~300 steps each, never need it); rays that do hit replay their
@@ -743,9 +727,36 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     {
         StepAxis ax;
         ax.x = ax.y = false;
-        bool act = live && word == 0u && numSteps != 0u;
         bool freeFlight = false;
-        while (act) {
+        bool reenter = true, first = true;
+        for (;;) {
+            if (reenter) enter_region_a(A, cur, rg, pos, ray.sy, colNy);
+            if (rg.r.mask != 0ull) {
+                const int idx = brick_bit(pos.x, pos.y, pos.z);
+                if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
+            }
+            bool act;
+            if (first) {
+                // :299-307  the camera's own voxel
+                first = false;
+                if (live && word != 0u) {
+                    if (word_flags(word) & 0x4u) {
+                        refrIndex = 1.1f;
+                    } else {
+                        const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
+                        out.color = decode_color((unsigned long long)pe.x | ((unsigned long long)pe.y << 32));
+                        out.hit.kind = RC_KIND_CAMERA_INSIDE;
+                        out.hit.x = pos.x;
+                        out.hit.y = pos.y;
+                        out.hit.z = pos.z;
+                        live = false;
+                    }
+                }
+                act = live && word == 0u && numSteps != 0u;
+            } else {
+                act = word == 0u && steps < numSteps;
+            }
+            if (!act) break;
             if (rg.r.mask == 0ull) {
                 // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach has
                 // nothing left to hit: the remaining steps only move it, and run after this loop without cells, countdowns
@@ -829,7 +840,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 pos.z += ray.sz * (n.nz - (int)fnz) + 4 * ((int)((cell >> 16) & 0xFFu) - (int)((cell0 >> 16) & 0xFFu));
                 steps += (uint32_t)(rem0 - rem);
                 if (outOfSteps) break;
-                enter_region_a(A, cur, rg, pos, ray.sy, colNy);
+                reenter = true;
             } else {
                 // Brick (or uniform solid cell): step until the ray leaves it, enters an occupied voxel or runs out of
                 // steps -- all inside this one pass of the outer loop, so that a lane walking a brick does not make the
@@ -840,13 +851,8 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                     steps++;
                     leftBrick = left_region(rg, pos);
                 } while (!leftBrick && !((rg.r.mask >> brick_bit(pos.x, pos.y, pos.z)) & 1ull) && steps < numSteps);
-                if (leftBrick) enter_region_a(A, cur, rg, pos, ray.sy, colNy);
+                reenter = leftBrick;
             }
-            if (rg.r.mask != 0ull) {
-                const int idx = brick_bit(pos.x, pos.y, pos.z);
-                if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
-            }
-            act = word == 0u && steps < numSteps;
         }
         if (freeFlight) {
             // same comparisons, same additions (nextIntersectDDA, low_res.frag:446-491); nothing else per step
@@ -1078,7 +1084,15 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         uint32_t k = P.shadow_steps;
         uint32_t state = 0u;  // block = (-1,-1): "empty"; 1 = LIQUID (the ray goes on), 2 = opaque
         uint32_t ssteps = 0;
-        enter_region(W, cur, rg, sp);
+        // no region yet: a one-voxel stand-in around the start, which the first step leaves (the one call site of the
+        // region code in this loop is the one behind the step)
+        rg.x = sp.x;
+        rg.y = sp.y;
+        rg.z = sp.z;
+        rg.r.mask = 0ull;
+        rg.r.base = 0u;
+        rg.r.info = 0u;
+        rg.r.shift = 0;
         // the sun is up: a shadow ray that has risen above everything it can still reach (sky gates, as in loop A) stays
         // unoccluded and runs out of steps -- asked when it enters an empty region and every 8th step inside one
         const bool gated = A.shadow_gate && sr.sy > 0 && sp.ty == sp.ty && sp.tz == sp.tz;
@@ -1118,6 +1132,10 @@ __device__ __forceinline__ uint32_t frame_pixel_of(const FrameArgs& A, uint32_t 
 }
 __device__ __forceinline__ void store_pixel(const FrameArgs& A, uint32_t idx, uint32_t framePixel, F3 c) {
     const uchar4 v = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+#ifdef RC_CHECKED
+    // a pixel outside this rank's buffer, or a peer store outside the composing GPU's frame
+    if (idx >= A.local_rows * A.p.width || (A.frame_target && framePixel >= A.p.width * A.p.height)) __trap();
+#endif
     A.rgba8[idx] = v;
     if (A.frame_target) A.frame_target[framePixel] = v;
     if (A.rgba32f) A.rgba32f[idx] = make_float4(c.x, c.y, c.z, 0.0f);
@@ -1291,6 +1309,17 @@ struct AoDir {
     float lx, ly;       // absDelta[face] when the face is x (lx) or y (ly), else 0: what deltaPos[face] is lowered by
 };
 static_assert(sizeof(AoDir) == 32, "AoDir is two 128-bit loads");
+#ifdef RC_AO_TABLE_CONSTANT
+// A/B variant (tools/build_variants.sh): the oriented table in __constant__ memory.  The entry a lane needs
+// depends on ITS pixel's face and normal sign, so a warp whose pixels see more than one orientation reads several
+// addresses per load -- which the constant cache serialises, where the L1 serves a 128-bit __ldg of any 32 addresses at once.
+__constant__ AoDir c_aoTable[6 * RC_MAX_AO_SAMPLES];
+#define AO_DIR_V0(dirs, orient, k) (*reinterpret_cast<const float4*>(&c_aoTable[(orient) * RC_MAX_AO_SAMPLES + (k)]))
+#define AO_DIR_FIRST(dirs, orient, k) (c_aoTable[(orient) * RC_MAX_AO_SAMPLES + (k)])
+#else
+#define AO_DIR_V0(dirs, orient, k) __ldg(reinterpret_cast<const float4*>((dirs) + (k)))
+#define AO_DIR_FIRST(dirs, orient, k) ((dirs)[k])
+#endif
 
 __device__ __forceinline__ int aow_stride_y(int face) { return face == 0 ? 8 : 16; }
 __device__ __forceinline__ int aow_stride_z(int face) { return face == 0 ? 96 : (face == 1 ? 128 : 192); }
@@ -1343,7 +1372,7 @@ __device__ __forceinline__ uint32_t aow_occ(uint32_t q) {
 // skip: bit g set = no voxel that a ray of sample group g can still enter is occupied, for any pixel of the warp
 // (AO_OPT_OCTANT): those rays are not cast; they are occluded iff one of the voxels already crossed was.
 template <bool BYTES, bool FOUR>
-__device__ __forceinline__ uint32_t aow_cast_rays(const AoDir* __restrict__ dirs, float qSf, uint32_t acc0, float a0x, float a1x,
+__device__ __forceinline__ uint32_t aow_cast_rays(const AoDir* __restrict__ dirs, uint32_t orient, float qSf, uint32_t acc0, float a0x, float a1x,
                                                   float a0y, float a1y, float a0z, float a1z, bool move, bool fourth, uint32_t skip) {
     uint32_t occluded = 0;
     for (uint32_t g = 0; g < 4u; g++) {
@@ -1354,12 +1383,12 @@ __device__ __forceinline__ uint32_t aow_cast_rays(const AoDir* __restrict__ dirs
             continue;
         }
         // every sample of the group steps the same way along each axis: the strides and (exact - round) are the group's
-        const AoDir first = dirs[kBegin];
+        const AoDir first = AO_DIR_FIRST(dirs, orient, kBegin);
         const float qx = move ? first.qx : 0.0f, qy = move ? first.qy : 0.0f, qz = move ? first.qz : 0.0f;
         const float q4x = fourth ? qx : 0.0f, q4y = fourth ? qy : 0.0f, q4z = fourth ? qz : 0.0f;
         const float ax = first.qx < 0 ? a1x : a0x, ay = first.qy < 0 ? a1y : a0y, az = first.qz < 0 ? a1z : a0z;
         for (uint32_t k = kBegin; k < kEnd; k++) {
-            const float4 v0 = __ldg(reinterpret_cast<const float4*>(dirs + k));
+            const float4 v0 = AO_DIR_V0(dirs, orient, k);
             const float ix = v0.x, iy = v0.y, iz = v0.z;  // ray.delta = 1 / dir, |.| = absDelta
             const float adx = fabsf(ix), ady = fabsf(iy), adz = fabsf(iz);
             // deltaPos = absDelta - (exact - round) * delta (low_res.frag:379); (exact - round)[face] comes in as 0
@@ -1598,15 +1627,16 @@ __device__ __forceinline__ void aow_warp(const FrameArgs& A, const AoSeed& s, bo
         if (f0) a0x = a1x = 0.0f;
         else if (f1) a0y = a1y = 0.0f;
         else a0z = a1z = 0.0f;
-        const AoDir* dirs = table + (size_t)(face * 2 + (negNormal ? 1 : 0)) * RC_MAX_AO_SAMPLES;
+        const uint32_t orient = (uint32_t)(face * 2 + (negNormal ? 1 : 0));
+        const AoDir* dirs = table + (size_t)orient * RC_MAX_AO_SAMPLES;
         const float qSf = __uint_as_float(qS);
         const bool fourth = !negNormal;
         if (byteMode)
-            occluded = four ? aow_cast_rays<true, true>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
-                            : aow_cast_rays<true, false>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
+            occluded = four ? aow_cast_rays<true, true>(dirs, orient, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
+                            : aow_cast_rays<true, false>(dirs, orient, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
         else
-            occluded = four ? aow_cast_rays<false, true>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
-                            : aow_cast_rays<false, false>(dirs, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
+            occluded = four ? aow_cast_rays<false, true>(dirs, orient, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip)
+                            : aow_cast_rays<false, false>(dirs, orient, qSf, acc0, a0x, a1x, a0y, a1y, a0z, a1z, fast, fourth, skip);
     }
     // The other pixels, one at a time: their samples dealt to the lanes, each ray on the tree itself (castAo as it stands)
     unsigned slow = __ballot_sync(0xffffffffu, valid && !fast);
@@ -2156,6 +2186,10 @@ cudaError_t upload_hemisphere(const float* dirs, uint32_t n, cudaStream_t stream
     }
     e = cudaMemcpyAsync(*table, host, sizeof(host), cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
+#ifdef RC_AO_TABLE_CONSTANT
+    e = cudaMemcpyToSymbolAsync(c_aoTable, host, sizeof(host), 0, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
+#endif
     return cudaStreamSynchronize(stream);  // inv[] lives on this stack frame
 }
 

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <string>
 #include <vector>
@@ -1012,6 +1013,11 @@ int rc_host_register(void* ptr, size_t bytes) {
     return RC_OK;
 }
 
+// Full memory fence for hosts that publish "frame complete" counters next to frames in shared host memory (one frame
+// assembled by several processes): fence, then store the counter (release); load the counter, then fence (acquire).  A plain
+// store / load is enough on x86 only.
+void rc_host_fence(void) { std::atomic_thread_fence(std::memory_order_seq_cst); }
+
 int rc_host_unregister(void* ptr) {
     if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_host_unregister: call rc_init first");
     if (!ptr) return fail(RC_ERR_INVALID_ARGUMENT, "rc_host_unregister: null");
@@ -1312,6 +1318,35 @@ static int one_debug_set_option(const char* name, int value) {
         return fail(RC_ERR_INVALID_ARGUMENT, "rc_debug_set_option: unknown option %s", name);
     }
     return RC_OK;
+}
+
+// Copy-only ceiling of the read-back path: the last frame's rows (this rank's bands of a sharded frame) are copied to dst
+// `repeats` times, back to back on the copy stream, exactly as rc_read_image / rc_read_image_async copy them, with no
+// rendering in between; *ms = wall-clock time of the whole batch.  dst = NULL: into a page-locked frame the call allocates
+// itself (cudaHostAlloc, portable) and frees again.
+int rc_debug_reread_image(void* dst, size_t dst_bytes, uint32_t repeats, float* ms) {
+    if (!g.initialized) return fail(RC_ERR_NOT_INITIALIZED, "rc_debug_reread_image: call rc_init first");
+    if (!g.haveFrame) return fail(RC_ERR_NO_FRAME, "rc_debug_reread_image: no frame rendered");
+    const size_t bytes = (size_t)g.frame.width * g.frame.height * 4;
+    if (dst && dst_bytes < bytes) return fail(RC_ERR_BUFFER_TOO_SMALL, "rc_debug_reread_image: need %zu bytes", bytes);
+    CUDA_TRY(cudaSetDevice(g.device));
+    void* own = nullptr;
+    if (!dst) {
+        CUDA_TRY(cudaHostAlloc(&own, bytes, cudaHostAllocPortable));
+        dst = own;
+    }
+    cudaStream_t st = nullptr;
+    CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));
+    int rcode = copyRowsToHost(dst, g.dRgba8, 4, st, true);  // warm-up
+    const auto t0 = std::chrono::steady_clock::now();
+    for (uint32_t i = 0; i < repeats && rcode == RC_OK; i++) rcode = copyRowsToHost(dst, g.dRgba8, 4, st, false);
+    if (rcode == RC_OK && cudaStreamSynchronize(st) != cudaSuccess) rcode = fail(RC_ERR_CUDA, "rc_debug_reread_image: copy failed");
+    const auto t1 = std::chrono::steady_clock::now();
+    cudaStreamDestroy(st);
+    if (own) cudaFreeHost(own);
+    if (ms) *ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    return rcode;
 }
 
 int rc_debug_struct_sizes(uint32_t out[5]) {

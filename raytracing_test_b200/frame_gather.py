@@ -18,6 +18,8 @@ torch is plumbing here: process group, handle exchange, streams.  The gather / c
 runs on the gloo backend with CPU tensors (tests/test_multi_gpu_cpu.py), where the per-rank bands
 come from the test's renderer instead of librc.
 """
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -321,7 +323,9 @@ class SharedHostFrames:
     rank reads its own bands back into the shared frame (rc_read_image_async scatters a sharded frame's rows to
     their place), so a frame assembles itself in host memory over all the GPUs' PCIe links at once.
 
-    Protocol (single writer per counter, so plain stores are enough on one coherent host):
+    Protocol (single writer per counter; a full fence -- rc_host_fence -- orders each counter store after the frame bytes
+    that were waited for, and each counter load before the frame bytes read afterwards, so hosts weaker than x86 TSO see
+    them in order too; waiting loops yield the core between polls):
       landed[r]  = number of frames rank r has completely delivered        (written by rank r)
       consumed   = number of frames the consumer (rank 0) has released      (written by rank 0)
     Rank r may start delivering frame i (into slot i % slots) once consumed >= i - slots + 1; the consumer owns
@@ -375,7 +379,11 @@ class SharedHostFrames:
         if ready():
             return
         deadline = time.monotonic() + self.SPIN_TIMEOUT_S
+        polls = 0
         while not ready():
+            polls += 1
+            if polls & 15 == 0:
+                os.sched_yield()  # the cores are shared with the other ranks' read-backs
             if time.monotonic() > deadline:
                 raise TimeoutError(f"SharedHostFrames rank {self.rank}: {what} (landed {self.landed.tolist()}, "
                                    f"consumed {int(self.consumed[0])})")
@@ -384,17 +392,21 @@ class SharedHostFrames:
         """Producer side, before delivering frame i."""
         need = i - self.slots + 1
         self._spin(lambda: int(self.consumed[0]) >= need, f"frame {i}: its slot was never released")
+        rc.host_fence()  # acquire: the consumer's reads of the old frame are done before this rank overwrites the slot
 
     def mark_landed(self, i):
         """Producer side, after frame i is complete in host memory (rc_wait_image returned)."""
+        rc.host_fence()  # release: the frame bytes (device DMA, waited for by rc_wait_image) before the counter
         self.landed[self.rank] = i + 1
 
     def acquire(self, i):
         """Consumer (rank 0): blocks until frame i is complete; returns it (valid until release(i))."""
         self._spin(lambda: int(self.landed.min()) >= i + 1, f"frame {i} never completed")
+        rc.host_fence()  # acquire: the counters before the frame bytes
         return self.frames[i % self.slots]
 
     def release(self, i):
+        rc.host_fence()
         self.consumed[0] = i + 1
 
     def close(self):

@@ -152,6 +152,7 @@ ABI = {
     "rc_wait_image": (ctypes.c_int, [ctypes.c_int]),
     "rc_host_register": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
     "rc_host_unregister": (ctypes.c_int, [ctypes.c_void_p]),
+    "rc_host_fence": (None, []),
     "rc_frame_target_create": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
     "rc_frame_target_open": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]),
     "rc_frame_target_close": (ctypes.c_int, []),
@@ -187,6 +188,7 @@ ABI = {
     "rc_debug_palette": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_void_p]),
     "rc_debug_struct_sizes": (ctypes.c_int, [ctypes.c_void_p]),
     "rc_debug_set_option": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int]),
+    "rc_debug_reread_image": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_void_p]),
     "rc_debug_detmath": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
 }
 
@@ -499,11 +501,24 @@ class RayCaster:
         _check(self.lib, self.lib.rc_debug_lookup_device(xyz.ctypes.data, len(xyz), words.ctypes.data, shifts.ctypes.data))
         return words, shifts
 
+    def reread_image_ms(self, out, repeats):
+        """rc_debug_reread_image: wall-clock ms of `repeats` back-to-back copies of the last frame's rows into `out` (a uint8
+        array over page-locked memory; None = a page-locked frame of the call's own)."""
+        ms = ctypes.c_float(0.0)
+        _check(self.lib, self.lib.rc_debug_reread_image(out.ctypes.data if out is not None else None, out.nbytes if out is not None else 0,
+                                                        int(repeats), ctypes.byref(ms)))
+        return float(ms.value)
+
     def detmath(self, x):
         x = np.ascontiguousarray(x, dtype=np.float32)
         s, e = np.zeros_like(x), np.zeros_like(x)
         _check(self.lib, self.lib.rc_debug_detmath(x.ctypes.data, x.size, s.ctypes.data, e.ctypes.data))
         return s, e
+
+
+def host_fence():
+    """rc_host_fence: a full memory fence (release before a counter store, acquire after a counter load). Needs no device."""
+    load_library().rc_host_fence()
 
 
 def shard_layout(height, rank, world_size):
