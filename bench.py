@@ -461,7 +461,10 @@ def run_b200_arm(args, workload):
     dev = torch.device("cuda", local_rank)
     if world_size > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+
+        # a mismatched collective must not hold eight GPUs for NCCL's default ten minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
 
     w, h, shadows, ao, case = WORKLOADS[workload]
     golden = golden_case(case)
@@ -745,13 +748,15 @@ def run_b200_arm(args, workload):
                               if world_size > 1 and sc.mode == "gather" else "")}
         if rank == 0:
             assert host_img.any(), "e2e frame is empty"
-    elif rank == 0:
-        if world_size == 1:
-            sc.caster.render_frame(params)
-            checked.append(("rc_read_image, synchronous", sha256_of(sc.caster.read_image())))
-        else:
-            sc.render(params)
-            torch.cuda.synchronize(dev)
+    elif world_size == 1:
+        sc.caster.render_frame(params)
+        checked.append(("rc_read_image, synchronous", sha256_of(sc.caster.read_image())))
+    else:
+        # every rank renders: a frame is a collective act (completion signal / gather); rank 0 alone would wait for ever
+        sc.render(params)
+        torch.cuda.synchronize(dev)
+        barrier()
+        if rank == 0:
             checked.append(("rank 0's composed frame", sha256_of(sc.frame().cpu().numpy())))
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None

@@ -709,11 +709,27 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     float refrIndex = 1.0f;
 
     // :299-307
-    // (the camera's own voxel is looked up by the first pass of loop A below: the region code is inlined, and one call
-    // site for all of loop A keeps the kernel's hot code inside the instruction cache)
     RegionAt rg;
-    int colNy = 0;  // > 0: rg is the column above the terrain (enter_region_a), this many steps along y left in it
+    int colNy;  // > 0: rg is the column above the terrain (enter_region_a), this many steps along y left in it
+    enter_region_a(A, cur, rg, pos, ray.sy, colNy);
     uint32_t word = 0u;
+    {
+        const int idx = brick_bit(pos.x, pos.y, pos.z);
+        if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
+    }
+    if (live && word != 0u) {
+        if (word_flags(word) & 0x4u) {
+            refrIndex = 1.1f;
+        } else {
+            const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
+            out.color = decode_color((unsigned long long)pe.x | ((unsigned long long)pe.y << 32));
+            out.hit.kind = RC_KIND_CAMERA_INSIDE;
+            out.hit.x = pos.x;
+            out.hit.y = pos.y;
+            out.hit.z = pos.z;
+            live = false;
+        }
+    }
 
     // :309-315  loop A: to the first non-empty voxel.  pos.exact is not needed to FIND it, so this
     // pass leaves it alone (sky rays, ~300 steps each, never need it); rays that do hit replay their
@@ -727,36 +743,9 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
     {
         StepAxis ax;
         ax.x = ax.y = false;
+        bool act = live && word == 0u && numSteps != 0u;
         bool freeFlight = false;
-        bool reenter = true, first = true;
-        for (;;) {
-            if (reenter) enter_region_a(A, cur, rg, pos, ray.sy, colNy);
-            if (rg.r.mask != 0ull) {
-                const int idx = brick_bit(pos.x, pos.y, pos.z);
-                if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
-            }
-            bool act;
-            if (first) {
-                // :299-307  the camera's own voxel
-                first = false;
-                if (live && word != 0u) {
-                    if (word_flags(word) & 0x4u) {
-                        refrIndex = 1.1f;
-                    } else {
-                        const uint4 pe = __ldg(&W.palette[word & MATERIAL_INDEX_MASK]);
-                        out.color = decode_color((unsigned long long)pe.x | ((unsigned long long)pe.y << 32));
-                        out.hit.kind = RC_KIND_CAMERA_INSIDE;
-                        out.hit.x = pos.x;
-                        out.hit.y = pos.y;
-                        out.hit.z = pos.z;
-                        live = false;
-                    }
-                }
-                act = live && word == 0u && numSteps != 0u;
-            } else {
-                act = word == 0u && steps < numSteps;
-            }
-            if (!act) break;
+        while (act) {
             if (rg.r.mask == 0ull) {
                 // Free flight: a ray that steps up and is above every occupied voxel of the columns it can still reach has
                 // nothing left to hit: the remaining steps only move it, and run after this loop without cells, countdowns
@@ -840,7 +829,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                 pos.z += ray.sz * (n.nz - (int)fnz) + 4 * ((int)((cell >> 16) & 0xFFu) - (int)((cell0 >> 16) & 0xFFu));
                 steps += (uint32_t)(rem0 - rem);
                 if (outOfSteps) break;
-                reenter = true;
+                enter_region_a(A, cur, rg, pos, ray.sy, colNy);
             } else {
                 // Brick (or uniform solid cell): step until the ray leaves it, enters an occupied voxel or runs out of
                 // steps -- all inside this one pass of the outer loop, so that a lane walking a brick does not make the
@@ -851,8 +840,13 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
                     steps++;
                     leftBrick = left_region(rg, pos);
                 } while (!leftBrick && !((rg.r.mask >> brick_bit(pos.x, pos.y, pos.z)) & 1ull) && steps < numSteps);
-                reenter = leftBrick;
+                if (leftBrick) enter_region_a(A, cur, rg, pos, ray.sy, colNy);
             }
+            if (rg.r.mask != 0ull) {
+                const int idx = brick_bit(pos.x, pos.y, pos.z);
+                if ((rg.r.mask >> idx) & 1ull) word = region_word(W, rg.r, idx);
+            }
+            act = word == 0u && steps < numSteps;
         }
         if (freeFlight) {
             // same comparisons, same additions (nextIntersectDDA, low_res.frag:446-491); nothing else per step
@@ -1084,15 +1078,7 @@ __device__ __forceinline__ void shade_pixel(const FrameArgs& A, bool valid, uint
         uint32_t k = P.shadow_steps;
         uint32_t state = 0u;  // block = (-1,-1): "empty"; 1 = LIQUID (the ray goes on), 2 = opaque
         uint32_t ssteps = 0;
-        // no region yet: a one-voxel stand-in around the start, which the first step leaves (the one call site of the
-        // region code in this loop is the one behind the step)
-        rg.x = sp.x;
-        rg.y = sp.y;
-        rg.z = sp.z;
-        rg.r.mask = 0ull;
-        rg.r.base = 0u;
-        rg.r.info = 0u;
-        rg.r.shift = 0;
+        enter_region(W, cur, rg, sp);
         // the sun is up: a shadow ray that has risen above everything it can still reach (sky gates, as in loop A) stays
         // unoccluded and runs out of steps -- asked when it enters an empty region and every 8th step inside one
         const bool gated = A.shadow_gate && sr.sy > 0 && sp.ty == sp.ty && sp.tz == sp.tz;

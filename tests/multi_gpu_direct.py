@@ -27,7 +27,9 @@ from raytracing_test_b200 import frame_gather as fg, rc, voxel_host as vh  # noq
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import datetime
+
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
     host = vh.World.default()
     pos, _, sun = vh.default_camera()
     direct = fg.ShardedRayCaster(local, rank, world, mode="direct")

@@ -5,32 +5,32 @@ import sys
 
 rows = list(csv.reader(open(sys.argv[1])))
 only = sys.argv[2] if len(sys.argv) > 2 else "primary_kernel"
-GROUPS = [  # (first line, last line, label) in kernels.cu; anything else: "other"
+GROUPS = [  # (first line, last line, label) in kernels.cu as of rc_build_id 71fcfeb4 (round 2); anything else: "other"
     (37, 107, "fp helpers, det_sin / det_exp"),
-    (112, 187, "cursor, wrap_coord, lookup"),
-    (190, 262, "fetch_region / region_word"),
-    (263, 272, "occlusion_state"),
-    (276, 332, "build_ray, init_delta_pos, count_cell"),
-    (334, 374, "dda_step (loop B)"),
-    (376, 392, "dda_step_bl"),
-    (393, 415, "dda_step_exact_bl (replay)"),
-    (416, 431, "left_region / enter_region"),
-    (432, 458, "enter_region_a (column regions)"),
-    (459, 503, "after_lookup, colours, sky"),
-    (504, 535, "sky_gate_distance, counter_slot"),
-    (553, 641, "shade_pixel: set-up, camera ray, first lookup"),
-    (642, 694, "loop A: gate test, empty-cell set-up"),
-    (695, 707, "loop A: empty-cell step loop"),
-    (708, 732, "loop A: sibling walk, position recovery"),
-    (733, 750, "loop A: brick walk, word"),
-    (751, 778, "free flight hand-over"),
-    (779, 805, "ratios + replay loop"),
-    (806, 881, "loop B"),
-    (882, 958, "shading"),
-    (959, 1005, "shadow ray"),
-    (1007, 1025, "store_pixel"),
-    (1556, 1647, "trace_tile: stores, seeds, counters"),
-    (1648, 1674, "kernel prologue"),
+    (112, 220, "cursor, top table, wrap_coord, lookup"),
+    (221, 317, "fetch_region / region_word"),
+    (318, 327, "occlusion_state"),
+    (329, 386, "build_ray, init_delta_pos, count_cell"),
+    (387, 430, "dda_step (loop B)"),
+    (431, 445, "dda_step_bl"),
+    (446, 470, "dda_step_exact_bl (replay)"),
+    (471, 485, "left_region / enter_region"),
+    (486, 511, "enter_region_a (column regions)"),
+    (512, 563, "after_lookup, colours, sky"),
+    (564, 627, "sky_gate_distance, sky_drop_distance, counter_slot"),
+    (648, 733, "shade_pixel: set-up, camera ray, first lookup"),
+    (734, 794, "loop A: gate tests, empty-cell set-up"),
+    (795, 807, "loop A: empty-cell step loop"),
+    (808, 832, "loop A: sibling walk, position recovery"),
+    (833, 850, "loop A: brick walk, word"),
+    (851, 878, "free flight hand-over"),
+    (879, 905, "ratios + replay loop"),
+    (906, 990, "loop B"),
+    (991, 1058, "shading"),
+    (1059, 1106, "shadow ray"),
+    (1107, 1132, "store_pixel"),
+    (1672, 1777, "trace_tile: stores, seeds, counters"),
+    (1778, 1797, "kernel prologue"),
 ]
 sections, cur, path = [], None, None
 for r in rows:
