@@ -9,8 +9,9 @@
  *
  * Conventions
  *  - plain C: pointers, sizes, PODs; no C++/torch types cross this boundary
- *  - one process drives one GPU (process-global state, like the reference's GL
- *    context and globals); not thread-safe, one caller thread
+ *  - process-global state, like the reference's GL context and globals; not
+ *    thread-safe, one caller thread.  rc_init drives one GPU; rc_init_multi
+ *    drives several from that one thread (the library shards every frame)
  *  - every int-returning call returns RC_OK (0) or a negative rc_status; the
  *    text of the last failure is rc_last_error().  Nothing ever calls exit()
  *    (the reference does: src/globals.hpp:32-43)
