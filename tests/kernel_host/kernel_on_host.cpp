@@ -1,24 +1,26 @@
 // kernel_on_host.cpp -- TEST INFRASTRUCTURE (tests/test_kernel_source_cpu.py builds and drives it).
 //
-// The device code of raytracing_test_b200/csrc/kernels.cu, compiled by g++ through tests/kernel_host/cuda_on_host.h and run
-// one "CUDA thread" at a time on the host: the table kernels (world_tops_kernel, top_table_kernel, sky_gate_kernel) exactly as
-// rc_api.cu launches them, then shade_pixel() for every pixel of a frame -- camera ray, loop A over tree regions / column
-// regions / the top table, sky gates and drop gates, free flight with the closed-form leap, replay of pos.exact, loop B
-// (mirrors, refraction), shading, the shadow ray -- and the stores of trace_tile.  What reaches g++ is kernels.cu itself up to
-// the first host-side launch helper, with the five inline-PTX lines blanked (KERNEL_SOURCE, written by the test: the file
-// has kernel launches further down that only nvcc can parse).  Nothing here is used by the product.
-//
-// Not covered: the warp-cooperative AO window code (a warp of one lane is not a warp) -- frames are rendered with
-// ao_samples = 0; AO parity is the GPU suite's.
+// The device code of raytracing_test_b200/csrc/kernels.cu, compiled by g++ through tests/kernel_host/cuda_on_host.h and run on
+// the host.  What reaches g++ is kernels.cu itself up to its first host-side launch helper, with its five inline-PTX lines
+// rewritten (KERNEL_SOURCE, written by the test: further down the file has kernel launches that only nvcc can parse).
+//   per-pixel mode (khost_render): the table kernels (world_tops_kernel, top_table_kernel, sky_gate_kernel) exactly as rc_api.cu
+//     launches them, then shade_pixel() for every pixel -- camera ray, loop A over tree regions / column regions / the top
+//     table, sky gates and drop gates, free flight with the closed-form leap, replay of pos.exact, loop B (mirrors,
+//     refraction), shading, the shadow ray -- and the stores of trace_tile.  Whole 1080p frames in seconds.
+//   kernel mode (khost_render_kernels): the __global__ functions themselves (primary_kernel<false / true>, ao_window_kernel,
+//     ao_window_persistent_kernel, ao_cached_kernel, frame_persistent_kernel<false / true>), CTA by CTA as launch_frame
+//     schedules them, every warp as 32 coroutines that meet at each *_sync intrinsic, the CTA's shared memory a plain array.
+// Nothing here is used by the product.  Not modelled: concurrency between warps (they run one after the other).
 #include "cuda_on_host.h"
 
 #include KERNEL_SOURCE  // namespace rc { ... device code of kernels.cu ... }
 #undef __noinline__
 
-// the kernels' `extern __shared__ uint32_t smem[]` (never touched here: no kernel that uses shared memory is run)
+// the kernels' `extern __shared__ uint32_t smem[]`: the shared memory of the one CTA that is being emulated
 namespace rc {
-uint32_t smem[4];
+alignas(16) uint32_t smem[48 * 1024];
 }
+unsigned char* kh_shared_base = reinterpret_cast<unsigned char*>(rc::smem);
 
 using namespace rc;
 
@@ -110,17 +112,8 @@ void khost_lookup(void* world, const int32_t* xyz, uint32_t n, uint32_t* words, 
     }
 }
 
-// rc_render_frame (one_render_frame of rc_api.cu: the same FrameArgs) + primary_kernel<false> for every pixel, on the host.
-// hits: width * height records (or null), rgba8: width * height * 4 bytes bottom-up, rgba32f: width * height * 4 floats or
-// null.  stats[0] = rays that ended in free flight, stats[1] = hit pixels, stats[2] = shadow rays.
-int khost_render(void* world, const rc_frame_params* params, rc_hit* hits, uint8_t* rgba8, float* rgba32f, uint64_t* stats) {
-    HostWorld* hw = static_cast<HostWorld*>(world);
-    const rc_frame_params& p = *params;
-    if (p.ao_samples != 0) {
-        lastError = "khost_render: the AO window code is warp-cooperative and is not run on the host (ao_samples must be 0)";
-        return RC_ERR_UNSUPPORTED;
-    }
-    FrameArgs a;
+// The FrameArgs rc_render_frame builds (one_render_frame of rc_api.cu), for an unsharded frame.
+static void frameArgs(HostWorld* hw, const rc_frame_params& p, FrameArgs& a) {
     memset(&a, 0, sizeof(a));
     a.p = p;
     a.world = hw->W;
@@ -171,7 +164,20 @@ int khost_render(void* world, const rc_frame_params* params, rc_hit* hits, uint8
         cross(p.camera_dir, yAxis, a.cam_left);
         cross(p.camera_dir, a.cam_left, a.cam_up);
     }
+}
 
+// Per-pixel mode: shade_pixel for every pixel + the stores of trace_tile, no warps (fast: whole 1080p frames in seconds).
+// hits: width * height records (or null), rgba8: width * height * 4 bytes bottom-up, rgba32f: width * height * 4 floats or
+// null.  stats[0] = rays that ended in free flight, stats[1] = hit pixels, stats[2] = shadow rays.
+int khost_render(void* world, const rc_frame_params* params, rc_hit* hits, uint8_t* rgba8, float* rgba32f, uint64_t* stats) {
+    HostWorld* hw = static_cast<HostWorld*>(world);
+    const rc_frame_params& p = *params;
+    if (p.ao_samples != 0) {
+        lastError = "khost_render: per-pixel mode runs shade_pixel only (ao_samples must be 0); khost_render_kernels runs the kernels";
+        return RC_ERR_UNSUPPORTED;
+    }
+    FrameArgs a;
+    frameArgs(hw, p, a);
     uint64_t hitPixels = 0, shadowRays = 0;
     for (uint32_t py = 0; py < p.height; py++)
         for (uint32_t px = 0; px < p.width; px++) {
@@ -203,6 +209,105 @@ int khost_render(void* world, const rc_frame_params* params, rc_hit* hits, uint8
         stats[0] = free;
         stats[1] = hitPixels;
         stats[2] = shadowRays;
+    }
+    return RC_OK;
+}
+
+// ---- kernel mode: the __global__ functions themselves, CTA by CTA, every warp as 32 coroutines (cuda_on_host.h, KhWarp) ------
+namespace {
+struct KernelCall {
+    void (*kernel)(const FrameArgs);
+    const FrameArgs* args;
+};
+void warpBody(void* p) {
+    const KernelCall* c = static_cast<const KernelCall*>(p);
+    c->kernel(*c->args);
+}
+KhWarp warp;
+
+// <<<grid, threads, (shared memory), stream>>> on the host: CTAs one after the other, their warps one after the other (none
+// of these kernels synchronises across warps)
+void launch(void (*kernel)(const FrameArgs), const FrameArgs& a, unsigned gx, unsigned gy, unsigned threads) {
+    KernelCall call{kernel, &a};
+    gridDim.x = gx;
+    gridDim.y = gy;
+    blockDim.x = threads;
+    for (unsigned by = 0; by < gy; by++)
+        for (unsigned bx = 0; bx < gx; bx++) {
+            blockIdx.x = bx;
+            blockIdx.y = by;
+            for (unsigned w = 0; w < threads / 32u; w++) warp.run(32u * w, warpBody, &call);
+        }
+    blockIdx.x = blockIdx.y = 0;
+    threadIdx.x = 0;
+    gridDim.x = gridDim.y = 1;
+}
+}  // namespace
+
+// rc_render_frame as launch_frame (kernels.cu) schedules it, on the host.  schedule: 0 primary_kernel<false> + ao_window_kernel
+// (ao_cached_kernel when ao_steps != 5), 1 + ao_window_persistent_kernel, 2 primary_kernel<true> (fused), 3 / 4
+// frame_persistent_kernel<false / true>.  hemi: rc_hemisphere_table(ao_samples) (3 floats per sample) when ao_samples > 0.
+// schedule | 0x100: the AO octant skip off.  stats[0] = free-flight rays, [1] = hit pixels, [2] = shadow rays, [3] = AO seeds.
+int khost_render_kernels(void* world, const rc_frame_params* params, uint32_t schedule, const float* hemi, rc_hit* hits, uint8_t* rgba8,
+                         float* rgba32f, uint64_t* stats) {
+    HostWorld* hw = static_cast<HostWorld*>(world);
+    const rc_frame_params& p = *params;
+    FrameArgs a;
+    frameArgs(hw, p, a);
+    const size_t pixels = (size_t)a.local_rows * p.width;
+    std::vector<uchar4> img(pixels);
+    std::vector<float4> f32(rgba32f ? pixels : 0);
+    std::vector<rc_hit> hit(hits ? pixels : 0);
+    std::vector<AoSeed> seeds(p.ao_samples ? pixels : 0);
+    a.rgba8 = img.data();
+    a.rgba32f = rgba32f ? f32.data() : nullptr;
+    a.hits = hits ? hit.data() : nullptr;
+    a.ao_seeds = p.ao_samples ? seeds.data() : nullptr;
+    void* table = nullptr;
+    if (p.ao_samples) {
+        if (!hemi || upload_hemisphere(hemi, p.ao_samples, nullptr, &table) != cudaSuccess) {
+            lastError = "khost_render_kernels: upload_hemisphere failed";
+            return RC_ERR_INVALID_ARGUMENT;
+        }
+        a.ao_table = table;
+    }
+    const bool ao = p.ao_samples > 0;
+    const bool window = ao && p.ao_steps == AOW_STEPS;
+    if (schedule & 0x100u) a.ao_opts = 0u;  // A/B: AO_OPT_OCTANT off
+    schedule &= 0xFFu;
+    if (schedule >= 2 && ao && !window) schedule = 0;
+    if (schedule == 1 && !window) schedule = 0;
+    const unsigned gx = (p.width + PRIMARY_TILE_W - 1u) / PRIMARY_TILE_W, gy = (a.local_rows + PRIMARY_TILE_H - 1u) / PRIMARY_TILE_H;
+    if (schedule == 3 || schedule == 4) {
+        if (schedule == 4) a.world.n_top = hw->pw.level_begin.size() > 3 ? hw->pw.level_begin[3] : 0u;
+        launch(schedule == 4 ? frame_persistent_kernel<true> : frame_persistent_kernel<false>, a, 8, 1, 32 * PERSISTENT_WARPS);
+    } else if (schedule == 2) {
+        launch(primary_kernel<true>, a, gx, gy, 32 * RC_PRIMARY_WARPS);
+    } else {
+        launch(primary_kernel<false>, a, gx, gy, 32 * RC_PRIMARY_WARPS);
+        if (ao) {
+            const unsigned maxSeeds = a.local_rows * p.width;
+            if (schedule == 1)
+                launch(ao_window_persistent_kernel, a, 8, 1, AO_THREADS);
+            else
+                launch(window ? ao_window_kernel : ao_cached_kernel, a, (maxSeeds + AO_THREADS - 1u) / AO_THREADS, 1, AO_THREADS);
+        }
+    }
+    if (table) release_hemisphere(table);
+    for (uint32_t y = 0; y < p.height; y++) {
+        memcpy(rgba8 + (size_t)y * p.width * 4, &img[(size_t)y * p.width], (size_t)p.width * 4);
+        if (rgba32f) memcpy(rgba32f + (size_t)y * p.width * 4, &f32[(size_t)y * p.width], (size_t)p.width * 16);
+        if (hits) memcpy(hits + (size_t)y * p.width, &hit[(size_t)y * p.width], (size_t)p.width * sizeof(rc_hit));
+    }
+    if (stats) {
+        stats[0] = stats[1] = stats[2] = 0;
+        stats[3] = hw->counters.seed_cursor.next;
+        for (uint32_t k = 0; k < COUNTER_SLOTS; k++) {
+            stats[0] += hw->counters.slot[k].free_flight_rays;
+            stats[1] += hw->counters.slot[k].hit_pixels;
+            stats[2] += hw->counters.slot[k].shadow_rays;
+            stats[3] += hw->counters.slot[k].ao_seed_count;
+        }
     }
     return RC_OK;
 }
