@@ -3,6 +3,8 @@
 # step too deep; sky gates without their slack; drop gates that count the drop to the near edge of a ring only) and runs the randomised test against each on the GPU box: both must FAIL.
 #   here:        tools/mutation_check.sh build
 #   on the box:  tools/mutation_check.sh run   (under gpurun; writes gpurun_out/mutation_check.log)
+# Without a GPU: KHOST_DEFINES=-DRC_MUTATE_DROP python -m pytest tests/test_kernel_source_cpu.py -x -q  (the same three mutants in
+# the host build of kernels.cu: each fails at the first frame).
 set -u
 cd "$(dirname "$0")/.."
 if [ "${1:-}" = build ]; then
