@@ -168,6 +168,8 @@ struct KhWarp {
     unsigned gen = 0;       // rendezvous being assembled
     int cur = -1;           // lane running now
     unsigned threadBase = 0;
+    int order = 0;          // lane order between rendezvous (see run)
+    unsigned pass = 0;
     void (*body)(void*) = nullptr;
     void* bodyArg = nullptr;
 
@@ -201,7 +203,12 @@ struct KhWarp {
         }
         for (;;) {
             bool any = false;
-            for (int l = 0; l < N; l++) {
+            pass++;
+            for (int i = 0; i < N; i++) {
+                // the order in which the lanes run between two rendezvous: 0 ascending, 1 descending, 2 shuffled anew in every
+                // pass.  Results must not depend on it: whatever one lane writes for another to read has to be separated
+                // from the read by a rendezvous (__syncwarp or any *_sync), or be an atomic whose order does not matter
+                const int l = order == 0 ? i : (order == 1 ? N - 1 - i : (int)((i * 13u + pass * 7u + (pass >> 3) * 5u) & 31u));
                 if (done[l] || waiting[l]) continue;
                 any = true;
                 cur = l;

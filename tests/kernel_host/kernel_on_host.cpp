@@ -247,7 +247,8 @@ void launch(void (*kernel)(const FrameArgs), const FrameArgs& a, unsigned gx, un
 // rc_render_frame as launch_frame (kernels.cu) schedules it, on the host.  schedule: 0 primary_kernel<false> + ao_window_kernel
 // (ao_cached_kernel when ao_steps != 5), 1 + ao_window_persistent_kernel, 2 primary_kernel<true> (fused), 3 / 4
 // frame_persistent_kernel<false / true>.  hemi: rc_hemisphere_table(ao_samples) (3 floats per sample) when ao_samples > 0.
-// schedule | 0x100: the AO octant skip off.  stats[0] = free-flight rays, [1] = hit pixels, [2] = shadow rays, [3] = AO seeds.
+// schedule | 0x100: the AO octant skip off; | 0x200 / 0x400: the lanes of a warp run in descending / shuffled order between
+// two rendezvous (a race check: results must not depend on it).  stats[0] = free-flight rays, [1] = hit pixels, [2] = shadow rays, [3] = AO seeds.
 int khost_render_kernels(void* world, const rc_frame_params* params, uint32_t schedule, const float* hemi, rc_hit* hits, uint8_t* rgba8,
                          float* rgba32f, uint64_t* stats) {
     HostWorld* hw = static_cast<HostWorld*>(world);
@@ -274,6 +275,7 @@ int khost_render_kernels(void* world, const rc_frame_params* params, uint32_t sc
     const bool ao = p.ao_samples > 0;
     const bool window = ao && p.ao_steps == AOW_STEPS;
     if (schedule & 0x100u) a.ao_opts = 0u;  // A/B: AO_OPT_OCTANT off
+    warp.order = (schedule >> 9) & 3u;      // 0x200: lanes run in descending order between rendezvous, 0x400: shuffled
     schedule &= 0xFFu;
     if (schedule >= 2 && ao && !window) schedule = 0;
     if (schedule == 1 && !window) schedule = 0;
