@@ -425,7 +425,7 @@ def test_camera_sweep_with_ao(khost, ob, rcmod, default_world, cam):
     with LIQUID in their window and pixels off their hit face take ao_ray_general, the rest the window code in byte and bit mode."""
     _, _, sun = default_world["camera"]
     origin, yaw, pitch = CAMERAS[cam]
-    ref, got = both_kernels(khost, ob, rcmod, default_world["kw"], default_world["oracle"], 240, 135, origin, camera_dir(yaw, pitch), sun,
+    ref, got = both_kernels(khost, ob, rcmod, default_world["kw"], default_world["oracle"], 192, 108, origin, camera_dir(yaw, pitch), sun,
                             schedule=(0, 2, 1, 3)[cam % 4], shadows=True, ao_samples=20, delta_time=0.75)
     assert_identical(ref, got, f"camera {cam} with AO")
 
@@ -456,11 +456,11 @@ def test_zoo_world_kernels_with_ao(khost, ob, rcmod, default_world):
         occluded = 0
         for i, (origin, yaw, pitch) in enumerate([((96.5, 40.5, 96.5), 30.0, 25.0), ((20.5, 100.5, 30.5), 60.0, 40.0),
                                                   ((64.5, 5.5, 64.5), 135.0, -35.0), ((100.2, 70.7, 33.3), 200.0, -20.0)]):
-            ref, got = both_kernels(khost, ob, rcmod, kw, ow, 320, 180, origin, camera_dir(yaw, pitch), sun, schedule=(0, 2)[i % 2],
+            ref, got = both_kernels(khost, ob, rcmod, kw, ow, 256, 144, origin, camera_dir(yaw, pitch), sun, schedule=(0, 2)[i % 2],
                                     shadows=True, ao_samples=24, delta_time=0.75)
             assert_identical(ref, got, f"zoo view {i} with AO")
             occluded += int(got["hits"]["ao_occluded"].astype(np.int64).sum())
-        assert occluded > 10_000
+        assert occluded > 5_000
     finally:
         khost.free(kw)
         host.close()
@@ -479,6 +479,6 @@ def test_results_do_not_depend_on_the_order_of_the_lanes(khost, ob, rcmod, defau
     for order in (1, 2):
         for schedule in range(5):
             o, dd = views[schedule % len(views)]
-            ref, got = both_kernels(khost, ob, rcmod, kw, ow, 240, 135, o, dd, sun, schedule=schedule, lane_order=order, shadows=True,
-                                    ao_samples=32, delta_time=0.75)
+            ref, got = both_kernels(khost, ob, rcmod, kw, ow, 208, 117, o, dd, sun, schedule=schedule, lane_order=order, shadows=True,
+                                    ao_samples=16, delta_time=0.75)
             assert_identical(ref, got, f"lane order {order}, schedule {schedule}")
