@@ -41,7 +41,9 @@ def device_part_of_kernels_cu():
     and upload_hemisphere, which builds the AO tables), verbatim but for the inline-PTX statements (one line each: the two
     shared-memory byte loads become the same load in C, the other three are blanked), plus the brace that closes namespace rc."""
     out, changed = [], []
-    with open(os.path.join(CSRC, "kernels.cu")) as f:
+    # KHOST_KERNELS=<file>: another version of kernels.cu (a kernel change under development, held to the oracle before it
+    # ever reaches a GPU)
+    with open(os.environ.get("KHOST_KERNELS") or os.path.join(CSRC, "kernels.cu")) as f:
         for n, line in enumerate(f.read().split("\n"), 1):
             if line.startswith(MARKER):
                 break
@@ -171,7 +173,7 @@ def assert_identical(ref, got, label, hits=True):
 
 def test_what_reaches_gpp_is_kernels_cu_but_for_the_inline_ptx():
     text, changed = device_part_of_kernels_cu()
-    src = open(os.path.join(CSRC, "kernels.cu")).read()
+    src = open(os.environ.get("KHOST_KERNELS") or os.path.join(CSRC, "kernels.cu")).read()
     cut = src.index(MARKER)
     # five single-line PTX statements: the optimisation fence of the empty-cell loop and the two griddepcontrol statements of
     # the kernel prologues (blanked: no effect on results), the two shared-memory byte loads of the AO window code (the same
